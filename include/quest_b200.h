@@ -1,0 +1,162 @@
+/*
+ * quest_b200.h -- C ABI of libquest_b200.so, the sm_100a implementation of Quest's
+ * query-aware sparse decode-attention path.
+ *
+ * Every entry point replaces one function of the reference's pybind module `quest._kernels`
+ * (reference: quest/ops/csrc/bsk_ops.h:23-117, bsk_ops.cu:4-20).  The boundary is plain C:
+ * raw device pointers, explicit sizes, a CUDA stream as `void*`; no torch types, no exceptions.
+ *
+ * Conventions
+ *   - return value: 0 = success, >0 = a cudaError_t from the launch, <0 = QUEST_ERR_* below.
+ *   - all tensors are fp16 (the reference dispatches Half only,
+ *     quest/ops/csrc/pytorch_extension_utils.h:25-35) unless stated; page ids are int32.
+ *   - paged pools use the reference's NHD layout (quest/utils/kv_cache.py:20-23):
+ *       pool[page][2][page_size][num_kv_heads][head_dim]; slab 0 = K (metadata: per-dim max),
+ *       slab 1 = V (metadata: per-dim min)   (kernels/include/decode/decode_page.cuh:196-239,443-446)
+ *   - `stream` is a cudaStream_t; kernels are enqueued, never synchronised.
+ *   - head_dim in {64, 128, 256}; page_size >= 1; num_qo_heads % num_kv_heads == 0.
+ */
+#ifndef QUEST_B200_H_
+#define QUEST_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QUEST_OK 0
+#define QUEST_ERR_BAD_ARG (-1)      /* null pointer / zero size / inconsistent sizes            */
+#define QUEST_ERR_UNSUPPORTED (-2)  /* head_dim / group size / length outside the built variants */
+#define QUEST_ERR_WORKSPACE (-3)    /* caller-provided workspace too small                       */
+
+/* Library identification: "quest_b200 <version> sm_100a". */
+const char* quest_version(void);
+
+/* ---- RoPE ------------------------------------------------------------------------------------
+ * Replaces apply_rope_in_place (bsk_ops.h:23-27, page.cu:212-253, decode_page.cuh:644-728).
+ * q: [seq_len, num_qo_heads, head_dim], k: [seq_len, num_kv_heads, head_dim], rotated in place with
+ * Llama rotate-half at positions past_kv_len + i. */
+int quest_rope_inplace(void* q, void* k, uint32_t seq_len, uint32_t past_kv_len,
+                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                       float rope_scale, float rope_theta, void* stream);
+
+/* ---- RMSNorm ---------------------------------------------------------------------------------
+ * Replaces rms_norm_forward (bsk_ops.h:29-32, rms_norm.cu:160-212). in/out: [rows, cols]. */
+int quest_rms_norm(const void* in, const void* weight, void* out, uint32_t rows, uint32_t cols,
+                   float epsilon, void* stream);
+
+/* ---- append_kv + per-page min/max metadata -----------------------------------------------------
+ * Replaces append_kv_cache_decode (bsk_ops.h:64-76, page.cu:6-99, decode_page.cuh:398-449).
+ * Writes the new token's K,V row (k, v: [1, num_heads, head_dim]) at
+ * (kv_indices[num_kv_pages-1], kv_last_page_len-1) and folds K into the metadata entry
+ * (meta_indices[num_meta_pages-1], meta_last_page_len-1): max=hmax(max,k), min=hmin(min,k);
+ * the entry is initialised to -/+65504 first when kv_last_page_len == 1. */
+int quest_append_decode(const void* k, const void* v,
+                        void* kv_data, const int32_t* kv_indices, uint32_t num_kv_pages,
+                        uint32_t kv_last_page_len,
+                        void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                        uint32_t meta_last_page_len,
+                        uint32_t num_heads, uint32_t head_dim, uint32_t page_size, void* stream);
+
+/* Replaces append_kv_cache_prefill (bsk_ops.h:50-62, page.cu:101-210, decode_page.cuh:471-562).
+ * k, v: [append_len, num_heads, head_dim] are the LAST append_len tokens of a sequence that now
+ * occupies num_kv_pages pages with kv_last_page_len tokens in the last one.  Scatters the rows into
+ * their pages and writes per-page per-dim min/max into metadata entry
+ * (meta_indices[j / page_size], j % page_size) for every touched KV page j; a page that already
+ * held tokens before this call resumes from its stored min/max. */
+int quest_append_prefill(const void* k, const void* v, uint32_t append_len,
+                         void* kv_data, const int32_t* kv_indices, uint32_t num_kv_pages,
+                         uint32_t kv_last_page_len,
+                         void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                         uint32_t num_heads, uint32_t head_dim, uint32_t page_size, void* stream);
+
+/* ---- estimate ----------------------------------------------------------------------------------
+ * Replaces estimate_attn_score (bsk_ops.h:41-48, estimate.cu:6-84, decode_attn.cuh:137-168,245-401).
+ * o[h, p] = fp16( sum_d max(q[h,d]*max[p,h/g,d], q[h,d]*min[p,h/g,d]) ) for the first `len`
+ * KV pages (the caller excludes the last page: len = num_kv_pages - 1).  fp32 products/sums in the
+ * reference's order (8 dims per lane sequentially, then xor-butterfly over head_dim/8 lanes), so
+ * scores are bit-identical to the reference kernel.  q: [num_qo_heads, head_dim]; o: [num_qo_heads, len]. */
+int quest_estimate(const void* q, void* o, uint32_t len,
+                   const void* meta_data, const int32_t* meta_indices,
+                   uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                   uint32_t page_size, void* stream);
+
+/* ---- top-k -------------------------------------------------------------------------------------
+ * Replaces topk_filtering (bsk_ops.h:34-39, topk.cu:7-46, kernels/include/topk/decode_select_k.cuh:25-62,
+ * raft select_radix.cuh radix_topk_one_block_kernel).  Per head: the k largest of `len` fp16 scores
+ * and their payload ids.  Deterministic: every score > tau (the k-th largest) is selected, ties at
+ * tau are taken lowest position first, and the output is in ascending input position.
+ * in_idx: [num_heads, len] with row stride in_idx_row_stride elements (0 = one row shared by all
+ * heads); NULL = payload is the position itself.  out_val: [num_heads, k] fp16 (may be NULL),
+ * out_idx: [num_heads, k].  Needs no scratch for len <= quest_topk_max_len(). */
+uint32_t quest_topk_max_len(void);
+int quest_topk(const void* scores, const int32_t* in_idx, uint32_t in_idx_row_stride,
+               void* out_val, int32_t* out_idx, uint32_t num_heads, uint32_t len, uint32_t k,
+               void* stream);
+
+/* ---- sparse paged decode attention -------------------------------------------------------------
+ * Replaces BatchDecodeWithPagedKVCachePyTorchWrapper::{BeginForward,Forward,EndForward}
+ * (bsk_ops.h:88-117, approx_attn.cu:27-151, decode_handler.cuh:39-244, decode_attn.cuh:440-646,
+ * 675-1005, flashinfer cascade.cuh:279-340).  The stateful handler becomes a pure host plan plus a
+ * caller-owned workspace.
+ *
+ * quest_decode_plan: chooses pages_per_chunk for num_sel_pages selected pages (+1 forced last page)
+ * so that num_qo_heads * num_chunks fills the GPU; no device access, no sync. */
+int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, uint32_t num_kv_heads,
+                      uint32_t head_dim, uint32_t page_size, uint32_t num_sms,
+                      uint32_t* pages_per_chunk, uint32_t* num_chunks);
+/* Bytes of workspace for a plan; the workspace must be zero-filled once before first use
+ * (the kernel restores its arrival counters to zero). */
+size_t quest_decode_workspace_bytes(uint32_t num_qo_heads, uint32_t head_dim, uint32_t num_chunks);
+/* q, o: [num_qo_heads, head_dim]; indices: [num_qo_heads, num_sel_pages] page ids with row stride
+ * idx_row_stride; the page last_page_idx holding last_page_len tokens is always attended in
+ * addition.  lse (fp32 [num_qo_heads], base-2, may be NULL). */
+int quest_decode_run(const void* q, void* o, float* lse,
+                     const void* kv_data, const int32_t* indices, uint32_t idx_row_stride,
+                     uint32_t num_sel_pages, uint32_t last_page_idx, uint32_t last_page_len,
+                     uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                     uint32_t page_size, uint32_t pages_per_chunk,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- fused layer step: estimate -> top-k -> sparse decode ---------------------------------------
+ * The three calls QuestAttention.forward makes per layer per token (quest/models/QuestAttention.py:
+ * 135-158) behind one entry; kernels are chained with programmatic dependent launch.  scores
+ * ([num_qo_heads, len] fp16) and topk_idx ([num_qo_heads, k] int32) are caller-provided
+ * intermediates and hold the same values the separate calls would produce.
+ * kv_indices: the sequence's page table (device, first `len` entries are the scored pages);
+ * last_page_idx: id of the always-attended last page (host value, reference controller.py:86). */
+int quest_sparse_decode_step(const void* q, void* o,
+                             const void* kv_data, const int32_t* kv_indices, uint32_t len,
+                             uint32_t last_page_idx, uint32_t last_page_len,
+                             const void* meta_data, const int32_t* meta_indices,
+                             void* scores, int32_t* topk_idx, uint32_t k,
+                             uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                             uint32_t page_size, uint32_t pages_per_chunk,
+                             void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- paged causal prefill ----------------------------------------------------------------------
+ * Replaces prefill_with_paged_kv_cache (bsk_ops.h:78-86, batch_prefill.cu:27-117, prefill.cuh:674-1115).
+ * q, o: [qo_len, num_qo_heads, head_dim]; the KV sequence is the num_kv_pages pages of kv_indices
+ * with kv_last_page_len tokens in the last; query i sits at position kv_len - qo_len + i. */
+int quest_prefill(const void* q, void* o, uint32_t qo_len,
+                  const void* kv_data, const int32_t* kv_indices, uint32_t num_kv_pages,
+                  uint32_t kv_last_page_len, int causal,
+                  uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                  uint32_t page_size, void* stream);
+
+/* ---- combine of partial attention states (sequence-sharded multi-GPU path) ----------------------
+ * Merges n partial states (o_i fp32 [n, num_heads, head_dim] normalised, lse_i fp32 [n, num_heads]
+ * base-2) into o fp16 [num_heads, head_dim]: flashinfer state.cuh:53-62 / cascade.cuh:279-340. */
+int quest_merge_states(const float* o_parts, const float* lse_parts, uint32_t n,
+                       void* o, float* lse, uint32_t num_heads, uint32_t head_dim, void* stream);
+
+/* Counters for bench/tests: number of kernels this library has launched since load / last reset. */
+uint64_t quest_launch_count(void);
+void quest_launch_count_reset(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QUEST_B200_H_ */

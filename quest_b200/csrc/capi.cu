@@ -1,0 +1,31 @@
+// Library-level entry points: identification, launch counter, and the fused layer step that chains
+// estimate -> top-k -> sparse decode with programmatic dependent launch (one call per layer per token;
+// reference call sites quest/models/QuestAttention.py:135-158).
+#include "common.cuh"
+
+namespace quest {
+unsigned long long g_launch_count = 0;
+}
+
+extern "C" const char* quest_version(void) { return "quest_b200 0.1.0 sm_100a"; }
+extern "C" uint64_t quest_launch_count(void) { return quest::g_launch_count; }
+extern "C" void quest_launch_count_reset(void) { quest::g_launch_count = 0; }
+
+extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_data, const int32_t* kv_indices,
+                                        uint32_t len, uint32_t last_page_idx, uint32_t last_page_len,
+                                        const void* meta_data, const int32_t* meta_indices, void* scores,
+                                        int32_t* topk_idx, uint32_t k, uint32_t num_qo_heads,
+                                        uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                                        uint32_t pages_per_chunk, void* workspace, size_t workspace_bytes,
+                                        void* stream) {
+  if (!kv_indices || !scores || !topk_idx) return QUEST_ERR_BAD_ARG;
+  if (k > len) return QUEST_ERR_BAD_ARG;
+  int rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+                          stream);
+  if (rc) return rc;
+  // payload ids = the sequence's page table, shared by all heads (row stride 0)
+  rc = quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
+  if (rc) return rc;
+  return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, last_page_idx, last_page_len, num_qo_heads,
+                          num_kv_heads, head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
+}

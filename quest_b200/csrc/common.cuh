@@ -1,0 +1,69 @@
+// Shared device helpers for the quest_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/quest_b200.h"
+
+namespace quest {
+
+extern unsigned long long g_launch_count;  // defined in capi.cu
+
+// 16-byte vector of 8 halves: the reference's vec_t<half, 8> (vec_size = max(16/sizeof(half), D/32)).
+struct alignas(16) H8 {
+  __half2 h[4];
+};
+
+// Streaming 128-bit load that bypasses L1 allocation (data is touched once).
+__device__ __forceinline__ H8 ld_stream(const void* p) {
+  H8 r;
+  uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3])
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ H8 ld_plain(const void* p) { return *reinterpret_cast<const H8*>(p); }
+__device__ __forceinline__ void st_plain(void* p, const H8& v) { *reinterpret_cast<H8*>(p) = v; }
+
+__device__ __forceinline__ void h8_to_float(const H8& v, float* f) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __half22float2(v.h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lg2(float x) {
+  float y;
+  asm volatile("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Programmatic dependent launch: wait for the producer grid / release the consumer grid.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// NHD pool addressing (reference decode_page.cuh:196-239): element offset of (page, slab, entry, head, 0).
+__device__ __forceinline__ size_t nhd_off(size_t page, uint32_t slab, uint32_t entry, uint32_t head,
+                                          uint32_t P, uint32_t H, uint32_t D) {
+  return (((page * 2 + slab) * P + entry) * H + head) * (size_t)D;
+}
+
+constexpr float kLog2e = 1.44269504088896340736f;
+
+}  // namespace quest
+
+#define QUEST_RETURN_LAUNCH()                         \
+  do {                                                \
+    ++quest::g_launch_count;                          \
+    cudaError_t e__ = cudaGetLastError();             \
+    return e__ == cudaSuccess ? QUEST_OK : (int)e__;  \
+  } while (0)
