@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""Headline benchmark: Quest sparse decode attention (append_kv -> estimate -> top-k -> sparse decode) for the
+LongChat-7B-v1.5-32K shape at 32K context, token budget 2048, batch 1 per GPU (BASELINE.json configs[1]).
+
+A step = one generated token's attention path over all 32 layers (each layer has its own 512 MiB KV pool and
+32 MiB metadata pool, so consecutive launches never find their inputs in the 126 MB L2).  Prints ONE JSON line.
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+N > 1: launched under torchrun, one rank per GPU, one sequence per rank (weak scaling, no collective on the path).
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+L, H, D, P = 32, 32, 128, 16          # LongChat-7B: layers, heads (MHA), head_dim; Quest page size
+CTX, TOKEN_BUDGET = 32768, 2048
+N_PAGES = CTX // P                    # 2048 KV pages, last one full after the decode append
+PAGE_BUDGET = TOKEN_BUDGET // P       # 128 incl. the last page
+K_SEL = PAGE_BUDGET - 1               # 127 selected among N_PAGES - 1 scored pages
+N_SCORED = N_PAGES - 1
+# algorithmic bytes per layer-step (DESIGN.md "Algorithmic bytes")
+BYTES_ESTIMATE = N_SCORED * H * D * 2 * 2 + H * D * 2 + N_SCORED * H * 2
+BYTES_TOPK = N_SCORED * H * 2 + K_SEL * H * 4
+BYTES_DECODE = PAGE_BUDGET * P * 2 * H * D * 2 + K_SEL * H * 4 + 2 * H * D * 2
+BYTES_APPEND = 2 * H * D * 2 * 2 + 2 * H * D * 2 * 2
+BYTES_STEP = BYTES_ESTIMATE + BYTES_TOPK + BYTES_DECODE + BYTES_APPEND
+METRIC, UNIT = "sparse_decode_attn_hbm_GBps", "GB/s"
+WORKLOAD = "LongChat-7B-v1.5-32K shape (32 layers x 32 heads x 128, fp16), 32K ctx, page 16, budget 2048, batch 1/GPU"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        out = self.p.communicate()[0]
+        sm, mx, reasons = [], [], set()
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])), mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the oracle's port of the reference's PyTorch CPU path (evaluation/quest_attention.py)
+# --------------------------------------------------------------------------------------------------------------
+def cpu_layer_step_inputs():
+    g = torch.Generator().manual_seed(1234)
+    q = torch.randn(1, H, 1, D, generator=g)
+    k = torch.randn(1, H, CTX, D, generator=g)
+    v = torch.randn(1, H, CTX, D, generator=g)
+    return q, k, v
+
+
+def run_cpu_port(steps, warmup):
+    from oracle import torch_path
+    q, k, v = cpu_layer_step_inputs()
+    for _ in range(warmup):
+        torch_path.quest_torch_decode(q, k, v, TOKEN_BUDGET, P, 1)
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        torch_path.quest_torch_decode(q, k, v, TOKEN_BUDGET, P, 1)
+        ts.append(time.perf_counter() - t0)
+    return ts
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ts = run_cpu_port(args.steps, args.warmup)
+    sec = sum(ts) / len(ts)
+    val = BYTES_STEP / sec / 1e9
+    sample = "1 layer-step per step (1/32 of a token's attention path), fp32, 32K ctx, budget 2048, torch CPU"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "us_per_layer": sec * 1e6, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "reference's evaluation/quest_attention.py decode path (oracle/torch_path.py port, "
+                   "pinned to the reference by tests/golden/torch_path.npz); algorithmic bytes of the sparse path / wall time"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# --------------------------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------------------------
+class Workload:
+    """32 layer pools filled through append_kv (prefill) with N(0,1) keys/values, plus per-layer q/k/v for the step."""
+
+    def __init__(self, dev, seed):
+        import quest_b200.utils as qu
+        self.qu, self.dev = qu, dev
+        torch.manual_seed(seed)
+        self.ic = qu.InferenceController(L, H, D, P, PAGE_BUDGET, CTX, torch.float16, dev)
+        ic = self.ic
+        ic.prepare_metadata(CTX - 1)
+        ic.begin_forward(CTX - 1)
+        for layer in range(L):
+            k = torch.randn(CTX - 1, H, D, dtype=torch.float16, device=dev)
+            v = torch.randn(CTX - 1, H, D, dtype=torch.float16, device=dev)
+            qu.append_kv(k, v, ic, layer)
+        ic.end_forward()
+        ic.prepare_metadata(1)
+        ic.begin_forward(1)
+        assert len(ic.kv_cache.indicies) == N_PAGES and ic.need_estimate() and ic.inference_page_budget == PAGE_BUDGET
+        # host (pinned) and device copies of the step inputs: q, k, v for every layer
+        self.h_qkv = torch.randn(3, L, 1, H, D).half().pin_memory()
+        self.d_qkv = self.h_qkv.to(dev)
+        self.h_out = torch.empty(L, 1, H, D, dtype=torch.float16).pin_memory()
+        self.d_out = torch.empty(L, 1, H, D, dtype=torch.float16, device=dev)
+        self.scores = torch.empty(L, H, N_SCORED, dtype=torch.float16, device=dev)
+        self.topk = torch.zeros(L, H, K_SEL, dtype=torch.int32, device=dev)
+        torch.cuda.synchronize()
+
+    # -- device-resident path: straight C-ABI calls, pointers precomputed, capturable in a CUDA graph
+    def make_raw_step(self, parts=("append", "estimate", "topk", "decode")):
+        import quest_b200._kernels as K
+        lib = K.load_library()
+        ic = self.ic
+        ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
+        assert lib.quest_decode_plan(K_SEL, H, H, D, P, torch.cuda.get_device_properties(self.dev).multi_processor_count,
+                                     ctypes.byref(ppc), ctypes.byref(nch)) == 0
+        self.plan = (ppc.value, nch.value)
+        self.ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, nch.value), dtype=torch.uint8, device=self.dev)
+        kvi, mi = ic.kv_indices_with_last, ic.metadata_indices
+        n_meta = mi.numel()
+        kv_last_len, meta_last_len = ic.kv_cache.last_page_len, ic.metadata_cache.last_page_len
+        last_idx = ic.kv_last_page_idx
+        calls = []
+        for l in range(L):
+            kvp, mp = ic.kv_cache.buf_layer(l).data_ptr(), ic.metadata_cache.buf_layer(l).data_ptr()
+            q, k, v = (self.d_qkv[i, l].data_ptr() for i in range(3))
+            o, s, ti = self.d_out[l].data_ptr(), self.scores[l].data_ptr(), self.topk[l].data_ptr()
+            if "append" in parts:
+                calls.append((lib.quest_append_decode, (k, v, kvp, kvi.data_ptr(), N_PAGES, kv_last_len, mp, mi.data_ptr(),
+                                                        n_meta, meta_last_len, H, D, P)))
+            if "estimate" in parts:
+                calls.append((lib.quest_estimate, (q, s, N_SCORED, mp, mi.data_ptr(), H, H, D, P)))
+            if "topk" in parts:
+                calls.append((lib.quest_topk, (s, kvi.data_ptr(), 0, None, ti, H, N_SCORED, K_SEL)))
+            if "decode" in parts:
+                calls.append((lib.quest_decode_run, (q, o, None, kvp, ti, K_SEL, K_SEL, last_idx, kv_last_len, H, H, D, P,
+                                                     ppc.value, self.ws.data_ptr(), self.ws.numel())))
+
+        def step():
+            st = torch.cuda.current_stream().cuda_stream
+            for f, a in calls:
+                rc = f(*a, st)
+                if rc:
+                    raise RuntimeError(f"{f.__name__} rc={rc}")
+        return step, len(calls)
+
+    # -- end-to-end path: host buffers in, host result out, through the public operator surface
+    def e2e_step(self):
+        qu, ic = self.qu, self.ic
+        self.d_qkv.copy_(self.h_qkv, non_blocking=True)
+        ic.begin_forward(1)
+        for l in range(L):
+            q, k, v = self.d_qkv[0, l], self.d_qkv[1, l], self.d_qkv[2, l]
+            qu.append_kv(k, v, ic, l)
+            s = qu.decode_estimate(q, ic, l)
+            qu.decode_topk(s, ic)
+            self.d_out[l] = qu.decode_sparse_attn(q, ic, l, ic.topk_dindices_buffer)
+        ic.end_forward()
+        self.h_out.copy_(self.d_out, non_blocking=True)
+
+
+def timed(fn, steps, warmup, dist_on):
+    """Device time of `steps` calls of fn, bracketed by barrier + synchronize; returns seconds (max over ranks)."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist_on:
+        torch.distributed.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    sec = e0.elapsed_time(e1) / 1e3
+    if dist_on:
+        t = torch.tensor([sec], device="cuda")
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        sec = float(t.item())
+    return sec
+
+
+def graph_of(step, warm=3):
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(warm):
+            step()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        step()
+    return g
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    dist_on = world > 1
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if dist_on:
+        torch.distributed.init_process_group("nccl", device_id=dev)
+
+    import quest_b200._kernels as K
+    lib = K.load_library()  # fails loudly if the CUDA library is missing
+    wl = Workload(dev, 1234 + rank)
+
+    step, launches_per_step = wl.make_raw_step()
+    step()  # eager once: validates return codes
+    torch.cuda.synchronize()
+    g = graph_of(step)
+    sampler = ClockSampler(local) if rank == 0 else None
+    lib.quest_launch_count_reset()
+    sec = timed(g.replay, args.steps, args.warmup, dist_on)
+    clocks = sampler.stop() if sampler else None
+    sec_eager = timed(step, args.steps, args.warmup, dist_on)
+    gpu_launches = launches_per_step * args.steps  # graph replays of the captured launches
+
+    # per-kernel device time (graph of that kernel alone over the 32 layer pools), for the roofline
+    kern = {}
+    for name, nbytes in (("estimate", BYTES_ESTIMATE), ("topk", BYTES_TOPK), ("decode", BYTES_DECODE), ("append", BYTES_APPEND)):
+        st, n = wl.make_raw_step(parts=(name,))
+        gk = graph_of(st)
+        t = timed(gk.replay, args.steps, 3, dist_on) / (args.steps * n)
+        kern[name] = {"us": t * 1e6, "GBps": nbytes / t / 1e9}
+    peak, peak_kind = peaks()
+    dom = max(("estimate", "decode"), key=lambda k_: kern[k_]["us"])
+    dom_bytes = {"estimate": BYTES_ESTIMATE, "decode": BYTES_DECODE}[dom]
+
+    sec_e2e = timed(wl.e2e_step, max(3, args.steps // 5), 3, dist_on) / max(3, args.steps // 5)
+
+    if rank != 0:
+        if dist_on:
+            torch.distributed.destroy_process_group()
+        return
+    ms_step = sec / args.steps * 1e3
+    us_layer = ms_step * 1e3 / L
+    value = world * BYTES_STEP * L / (sec / args.steps) / 1e9
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "us_per_layer": us_layer, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "step": "one token: 32 layers x (append_kv + estimate + top-k + sparse decode), "
+                   "decode position 32768 repeated", "l2": "inputs larger than L2: 32 layer pools (17.4 GB) rotated every launch",
+                   "launch": "CUDA graph of 128 C-ABI launches, PDL-chained", "parallelism": f"batch-sharded x{world}, no collective",
+                   "algorithmic_bytes_per_layer": BYTES_STEP, "decode_plan_pages_per_chunk": wl.plan[0]},
+        "frac_of_hbm_peak": BYTES_STEP / (us_layer * 1e-6) / 1e9 / peak,
+        "eager_us_per_layer": sec_eager / args.steps * 1e6 / L,
+        "kernels": kern,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "peak_kind": peak_kind,
+                     "unit": "GB/s", "frac": kern[dom]["GBps"] / peak, "traffic": None,
+                     "algorithmic_bytes_per_launch": dom_bytes},
+        "e2e": {"value": world * BYTES_STEP * L / sec_e2e / 1e9, "unit": UNIT, "ms_per_step": sec_e2e * 1e3,
+                "h2d_bytes_per_step": wl.h_qkv.numel() * 2, "d2h_bytes_per_step": wl.h_out.numel() * 2,
+                "path": "quest_b200.utils operator surface (controller + 4 ops/layer), pinned host q/k/v in, o out"},
+        "gpu_launches": gpu_launches,
+        "clocks": clocks,
+    }
+    if not args.no_cpu_baseline:
+        ts = run_cpu_port(3, 1)
+        s_cpu = sum(ts) / len(ts)
+        out["cpu_baseline"] = {"value": BYTES_STEP / s_cpu / 1e9, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": "3 layer-steps (after 1 warm-up) of the reference's torch CPU decode path at the same "
+                                         "shape in fp32 (oracle/torch_path.py); a full step is 32 of these", "sec_per_layer": s_cpu}
+    print(json.dumps(out))
+    if dist_on:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

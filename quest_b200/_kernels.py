@@ -1,0 +1,300 @@
+"""Drop-in for the reference's pybind module ``quest._kernels`` (reference quest/ops/csrc/bsk_ops.cu:4-20).
+
+Same seven function names, same argument order and meaning, same ``RuntimeError`` behaviour on shape /
+dtype violations (the reference's ``TORCH_CHECK`` macros, quest/ops/csrc/pytorch_extension_utils.h:37-66),
+plus the ``BatchDecodeWithPagedKVCachePyTorchWrapper`` class.  Everything forwards raw device pointers to
+``libquest_b200.so`` (C ABI in include/quest_b200.h) on torch's current stream.  There is no CPU path:
+importing works anywhere (symbol checks), calling an op without the library or with CPU tensors raises.
+"""
+import ctypes
+import os
+from typing import Optional
+
+import torch
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libquest_b200.so")
+
+_c = ctypes
+_vp, _u32, _i32p, _f32, _sz = _c.c_void_p, _c.c_uint32, _c.c_void_p, _c.c_float, _c.c_size_t
+
+# name -> (restype, argtypes); mirrors include/quest_b200.h one to one.
+SIGNATURES = {
+    "quest_version": (_c.c_char_p, []),
+    "quest_rope_inplace": (_c.c_int, [_vp, _vp, _u32, _u32, _u32, _u32, _u32, _f32, _f32, _vp]),
+    "quest_rms_norm": (_c.c_int, [_vp, _vp, _vp, _u32, _u32, _f32, _vp]),
+    "quest_append_decode": (_c.c_int, [_vp, _vp, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _vp]),
+    "quest_append_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _vp]),
+    "quest_estimate": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _vp]),
+    "quest_topk_max_len": (_u32, []),
+    "quest_topk": (_c.c_int, [_vp, _i32p, _u32, _vp, _i32p, _u32, _u32, _u32, _vp]),
+    "quest_decode_plan": (_c.c_int, [_u32, _u32, _u32, _u32, _u32, _u32, _c.POINTER(_u32), _c.POINTER(_u32)]),
+    "quest_decode_workspace_bytes": (_sz, [_u32, _u32, _u32]),
+    "quest_decode_run": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
+    "quest_sparse_decode_step": (_c.c_int, [_vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
+    "quest_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _c.c_int, _u32, _u32, _u32, _u32, _vp]),
+    "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _vp, _vp, _u32, _u32, _vp]),
+    "quest_launch_count": (_c.c_uint64, []),
+    "quest_launch_count_reset": (None, []),
+}
+
+_lib = None
+
+
+def load_library():
+    """Load libquest_b200.so and bind every symbol of include/quest_b200.h.  Raises if it is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise RuntimeError(
+                f"{_LIB_PATH} not found: build it with quest_b200/csrc/build.sh (no CPU fallback exists)")
+        lib = ctypes.CDLL(_LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the .so is stale
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def _check(cond, msg):
+    if not cond:
+        raise RuntimeError(msg)
+
+
+def _check_input(x, name):
+    _check(isinstance(x, torch.Tensor), f"{name} must be a tensor")
+    _check(x.is_cuda, f"{name} must be a CUDA tensor")
+    _check(x.is_contiguous(), f"{name} must be contiguous")
+
+
+def _check_rows(x, name):
+    """2-D index tensor: contiguous, or one row broadcast to all heads (stride 0 view)."""
+    _check(isinstance(x, torch.Tensor) and x.is_cuda, f"{name} must be a CUDA tensor")
+    _check(x.dim() == 2, f"{name} must be a 2D tensor")
+    _check(x.size(1) <= 1 or x.stride(1) == 1, f"{name} must be contiguous")
+    _check(x.size(0) <= 1 or x.stride(0) in (0, x.size(1)), f"{name} must be contiguous")
+    return 0 if (x.size(0) > 1 and x.stride(0) == 0) else x.size(1)
+
+
+def _check_half(x, op):
+    _check(x.dtype == torch.float16, f"{op} failed to dispatch with dtype {x.dtype}")
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _rc(code, op):
+    if code != 0:
+        if code > 0:
+            raise RuntimeError(f"{op} failed with CUDA error code {code}")
+        raise RuntimeError(f"{op} failed with argument error {code} "
+                           "(-1 bad argument, -2 unsupported shape, -3 workspace too small)")
+
+
+_NHD = 0
+
+
+def _check_layout(layout, op):
+    _check(int(layout) == _NHD, f"{op}: only the NHD layout is built (the reference controller always uses NHD, "
+                                "quest/utils/controller.py:38)")
+
+
+def apply_rope_in_place(q, k, past_kv_len, rope_scale, rope_theta):
+    """reference quest/ops/csrc/page.cu:212-253"""
+    _check_input(q, "q"), _check_input(k, "k")
+    _check(q.dim() == 3, "q must be a 3D tensor"), _check(k.dim() == 3, "k must be a 3D tensor")
+    _check(q.size(0) == k.size(0), "CHECK_EQ(q.size(0), k.size(0)) failed")
+    _check(q.size(2) == k.size(2), "CHECK_EQ(q.size(2), k.size(2)) failed")
+    _check_half(q, "apply_rope_in_place")
+    _rc(load_library().quest_rope_inplace(q.data_ptr(), k.data_ptr(), q.size(0), int(past_kv_len), q.size(1),
+                                          k.size(1), q.size(2), float(rope_scale), float(rope_theta), _stream()),
+        "apply_rope_in_place")
+
+
+def rms_norm_forward(input, weight, output, epsilon):
+    """reference quest/ops/csrc/rms_norm.cu:160-212"""
+    _check_input(input, "input"), _check_input(weight, "weight"), _check_input(output, "output")
+    _check_half(input, "rms_norm_forward")
+    cols = input.size(-1)
+    _check(weight.numel() == cols, "CHECK_EQ(weight.size(0), cols) failed")
+    _rc(load_library().quest_rms_norm(input.data_ptr(), weight.data_ptr(), output.data_ptr(), input.numel() // cols,
+                                      cols, float(epsilon), _stream()), "rms_norm_forward")
+
+
+def topk_filtering(estimated_value, estimated_indices, d_out, indices_out, buf, page_budget):
+    """reference quest/ops/csrc/topk.cu:7-46.  ``buf`` (raft scratch) is accepted and unused."""
+    _check_input(estimated_value, "estimated_value")
+    _check(estimated_value.dim() == 2, "estimated_value must be a 2D tensor")
+    in_stride = _check_rows(estimated_indices, "estimated_indices")
+    H, n = estimated_value.shape
+    _check(estimated_indices.size(1) == n, "CHECK_EQ(num_pages, estimated_indices.size(1)) failed")
+    _check(estimated_indices.size(0) == H, "CHECK_EQ(num_heads, estimated_indices.size(0)) failed")
+    _check(n >= page_budget, f"CHECK_GE(num_pages, page_budget) failed. {n} vs {page_budget}")
+    _check(estimated_indices.dtype == torch.int32, "CHECK_EQ(estimated_indices.scalar_type(), torch::kInt32) failed")
+    _check(d_out.size(1) == page_budget, "CHECK_EQ(page_budget, d_out.size(1)) failed")
+    _check(indices_out.size(1) == page_budget, "CHECK_EQ(page_budget, indices_out.size(1)) failed")
+    _check_input(d_out, "d_out"), _check_input(indices_out, "indices_out")
+    _check(indices_out.dtype == torch.int32, "indices_out must be int32")
+    _check_half(estimated_value, "Top-k filtering")
+    _rc(load_library().quest_topk(estimated_value.data_ptr(), estimated_indices.data_ptr(), in_stride, d_out.data_ptr(),
+                                  indices_out.data_ptr(), H, n, int(page_budget), _stream()), "topk_filtering")
+
+
+def _pool_dims(data, name):
+    _check(data.dim() == 5, f"{name} must be a 5D tensor")
+    _check(data.size(1) == 2, f"CHECK_EQ({name}.size(1), 2) failed")
+    return data.size(2), data.size(3), data.size(4)  # page_size, heads, head_dim (NHD)
+
+
+def estimate_attn_score(q, o, metadata_data, metadata_indices, metadata_indptr, metadata_last_page_len,
+                        metadata_last_page_idx, layout):
+    """reference quest/ops/csrc/estimate.cu:6-84.  Scores the first o.size(1) KV pages (the caller leaves out
+    the last one: quest/utils/__init__.py:193-194)."""
+    _check_layout(layout, "estimate_attn_score")
+    _check_input(q, "q"), _check_input(metadata_data, "metadata_data"), _check_input(metadata_indices, "metadata_indices")
+    _check_input(o, "o")
+    _check(q.dim() == 3, "q must be a 3D tensor"), _check(q.size(0) == 1, "CHECK_EQ(q.size(0), 1) failed")
+    _check(metadata_indices.dim() == 1, "metadata_indices must be a 1D tensor")
+    _check(metadata_indices.dtype == torch.int32, "CHECK_EQ(metadata_indices.scalar_type(), torch::kInt32) failed")
+    P, Hkv, D = _pool_dims(metadata_data, "metadata_data")
+    Hq = q.size(1)
+    _check(q.size(2) == D, "CHECK_EQ(metadata_data.size(4), head_dim) failed")
+    _check(Hq % Hkv == 0, "num_qo_heads must be a multiple of num_kv_heads")
+    _check(o.dim() == 2 and o.size(0) == Hq, "o must be [num_heads, num_pages - 1]")
+    n_entries = (metadata_indices.size(0) - 1) * P + int(metadata_last_page_len) - 1
+    _check(o.size(1) == n_entries, f"o.size(1) must equal the number of scored pages {n_entries}")
+    _check_half(q, "Estimate_attn_score")
+    _rc(load_library().quest_estimate(q.data_ptr(), o.data_ptr(), o.size(1), metadata_data.data_ptr(),
+                                      metadata_indices.data_ptr(), Hq, Hkv, D, P, _stream()), "estimate_attn_score")
+
+
+def _append_checks(k, v, kv_data, kv_indices, kv_indptr, metadata_data, metadata_indices, metadata_indptr, layout, op):
+    _check_layout(layout, op)
+    for t, n in ((k, "k"), (v, "v"), (kv_data, "kv_data"), (kv_indices, "kv_indices"),
+                 (metadata_data, "metadata_data"), (metadata_indices, "metadata_indices")):
+        _check_input(t, n)
+    _check(kv_indices.dim() == 1, "kv_indices must be a 1D tensor")
+    _check(metadata_indices.dim() == 1, "metadata_indices must be a 1D tensor")
+    _check(k.dim() == 3, "k must be a 3D tensor"), _check(v.dim() == 3, "v must be a 3D tensor")
+    for t, n in ((kv_indices, "kv_indices"), (metadata_indices, "metadata_indices"), (kv_indptr, "kv_indptr"),
+                 (metadata_indptr, "metadata_indptr")):
+        _check(t.dtype == torch.int32, f"CHECK_EQ({n}.scalar_type(), torch::kInt32) failed")
+    P, H, D = _pool_dims(kv_data, "kv_data")
+    _check(_pool_dims(metadata_data, "metadata_data") == (P, H, D), "metadata_data must share page_size/heads/dim with kv_data")
+    _check(k.size(1) == H, f"CHECK_EQ(kv_data.size(3), num_heads) failed. {H} vs {k.size(1)}")
+    _check(k.size(2) == D, f"CHECK_EQ(kv_data.size(4), head_dim) failed. {D} vs {k.size(2)}")
+    _check(v.shape == k.shape, "CHECK_EQ(seq_len, v.size(0)) failed")
+    _check_half(k, op)
+    return P, H, D
+
+
+def append_kv_cache_decode(k, v, kv_data, kv_indices, kv_indptr, kv_last_page_len, kv_last_page_idx, metadata_data,
+                           metadata_indices, metadata_indptr, metadata_last_page_len, metadata_last_page_idx, layout):
+    """reference quest/ops/csrc/page.cu:6-99"""
+    P, H, D = _append_checks(k, v, kv_data, kv_indices, kv_indptr, metadata_data, metadata_indices, metadata_indptr,
+                             layout, "Append_kv_cache_decode")
+    _check(k.size(0) == 1, f"CHECK_EQ(k.size(0), 1) failed. {k.size(0)} vs 1")
+    _rc(load_library().quest_append_decode(k.data_ptr(), v.data_ptr(), kv_data.data_ptr(), kv_indices.data_ptr(),
+                                           kv_indices.size(0), int(kv_last_page_len), metadata_data.data_ptr(),
+                                           metadata_indices.data_ptr(), metadata_indices.size(0),
+                                           int(metadata_last_page_len), H, D, P, _stream()), "append_kv_cache_decode")
+
+
+def append_kv_cache_prefill(k, v, kv_data, kv_indices, kv_indptr, kv_last_page_len, kv_last_page_idx, metadata_data,
+                            metadata_indices, metadata_indptr, metadata_last_page_len, metadata_last_page_idx, layout):
+    """reference quest/ops/csrc/page.cu:101-210"""
+    P, H, D = _append_checks(k, v, kv_data, kv_indices, kv_indptr, metadata_data, metadata_indices, metadata_indptr,
+                             layout, "Append_kv_cache_prefill")
+    _check(k.size(0) >= 2, f"CHECK_GE(k.size(0), 2) failed. {k.size(0)} vs 2")
+    _rc(load_library().quest_append_prefill(k.data_ptr(), v.data_ptr(), k.size(0), kv_data.data_ptr(),
+                                            kv_indices.data_ptr(), kv_indices.size(0), int(kv_last_page_len),
+                                            metadata_data.data_ptr(), metadata_indices.data_ptr(),
+                                            metadata_indices.size(0), H, D, P, _stream()), "append_kv_cache_prefill")
+
+
+def prefill_with_paged_kv_cache(q, kv_data, kv_indices, kv_last_page_len, causal, layout, allow_fp16_qk_reduction,
+                                rope_scale, rope_theta):
+    """reference quest/ops/csrc/batch_prefill.cu:27-117 (allocates and returns o)."""
+    _check_layout(layout, "prefill_with_paged_kv_cache")
+    _check_input(q, "q"), _check_input(kv_data, "kv_data"), _check_input(kv_indices, "kv_indices")
+    _check(q.dim() == 3, "q must be a 3D tensor"), _check(kv_indices.dim() == 1, "kv_indices must be a 1D tensor")
+    _check(kv_indices.dtype == torch.int32, "CHECK_EQ(kv_indices.scalar_type(), torch::kInt32) failed")
+    P, Hkv, D = _pool_dims(kv_data, "kv_data")
+    _check(q.size(2) == D, "CHECK_EQ(q.size(2), kv_data.size(4)) failed")
+    _check_half(q, "BatchPrefillWithPagedKVCache")
+    o = torch.empty_like(q)
+    _rc(load_library().quest_prefill(q.data_ptr(), o.data_ptr(), q.size(0), kv_data.data_ptr(), kv_indices.data_ptr(),
+                                     kv_indices.size(0), int(kv_last_page_len), 1 if causal else 0, q.size(1), Hkv, D,
+                                     P, _stream()), "prefill_with_paged_kv_cache")
+    return o
+
+
+_NUM_SMS = {}
+
+
+def _num_sms(device):
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _NUM_SMS:
+        _NUM_SMS[idx] = torch.cuda.get_device_properties(idx).multi_processor_count
+    return _NUM_SMS[idx]
+
+
+class BatchDecodeWithPagedKVCachePyTorchWrapper:
+    """reference quest/ops/csrc/approx_attn.cu:27-151 + kernels/include/decode/decode_handler.cuh:39-244.
+    The split-KV plan is pure host arithmetic and the temporary buffer is a torch tensor owned by this object
+    between begin_forward and end_forward (the reference's cudaMallocAsync'ed handler buffers)."""
+
+    def __init__(self, layout):
+        _check_layout(layout, "BatchDecodeWithPagedKVCachePyTorchWrapper")
+        self._plan = None
+        self._ws = None
+
+    def begin_forward(self, indptr, num_qo_heads, num_kv_heads, head_dim, page_size, empty_data, num_pages=None):
+        """``num_pages`` (host int) lets a caller that already knows indptr[1] skip the device read the reference
+        does in BeginForward (decode_attn.cuh:866-873)."""
+        _check(empty_data.dtype == torch.float16,
+               f"BatchDecodeWithPagedKVCache failed to dispatch with dtype {empty_data.dtype}")
+        if num_pages is None:
+            _check(indptr.dim() == 1 and indptr.dtype == torch.int32, "indptr must be a 1D int32 tensor")
+            num_pages = int(indptr[-1].item())
+        self._plan = (int(num_pages), int(num_qo_heads), int(num_kv_heads), int(head_dim), int(page_size))
+        self._chunks = {}
+
+    def end_forward(self):
+        self._plan = None  # the workspace tensor is kept for the next begin_forward (tickets are self-resetting)
+
+    def _planned(self, n_sel, Hq, Hkv, D, P, device):
+        key = (n_sel, Hq, Hkv, D, P)
+        if key not in self._chunks:
+            lib = load_library()
+            ppc, nch = _c.c_uint32(0), _c.c_uint32(0)
+            _rc(lib.quest_decode_plan(n_sel, Hq, Hkv, D, P, _num_sms(device), _c.byref(ppc), _c.byref(nch)),
+                "BatchDecodeWithPagedKVCache plan")
+            self._chunks[key] = (ppc.value, nch.value, lib.quest_decode_workspace_bytes(Hq, D, nch.value))
+        ppc, nch, nbytes = self._chunks[key]
+        if self._ws is None or self._ws.numel() < nbytes or self._ws.device != device:
+            self._ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+        return ppc, nch
+
+    def forward(self, q, o, paged_kv_data, paged_kv_indices, paged_kv_indptr, paged_kv_last_page_len,
+                paged_kv_last_page_idx, rope_scale, rope_theta):
+        if self._plan is None:
+            raise RuntimeError("BatchDecodeWithPagedKVCache: forward() called before begin_forward()")
+        _check_input(q, "q"), _check_input(paged_kv_data, "paged_kv_data")
+        _check_input(o, "o")
+        _check(q.dim() == 3, "q must be a 3D tensor")
+        stride = _check_rows(paged_kv_indices, "paged_kv_indices")
+        P, Hkv, D = _pool_dims(paged_kv_data, "paged_kv_data")
+        Hq = q.size(1)
+        _check(paged_kv_indices.size(0) == Hq, "CHECK_EQ(paged_kv_indices.size(0), num_qo_heads) failed")
+        _check(q.size(2) == D, "CHECK_EQ(paged_kv_data.size(4), head_dim) failed")
+        _check(paged_kv_indices.dtype == torch.int32, "CHECK_EQ(paged_kv_indices.scalar_type(), torch::kInt32) failed")
+        _check_half(q, "BatchDecodeWithPagedKVCache")
+        n_sel = self._plan[0]
+        _check(n_sel <= paged_kv_indices.size(1), "indptr[1] exceeds the width of paged_kv_indices")
+        ppc, _ = self._planned(n_sel, Hq, Hkv, D, P, q.device)
+        _rc(load_library().quest_decode_run(q.data_ptr(), o.data_ptr(), None, paged_kv_data.data_ptr(),
+                                            paged_kv_indices.data_ptr(), stride, n_sel, int(paged_kv_last_page_idx),
+                                            int(paged_kv_last_page_len), Hq, Hkv, D, P, ppc, self._ws.data_ptr(),
+                                            self._ws.numel(), _stream()), "BatchDecodeWithPagedKVCache")

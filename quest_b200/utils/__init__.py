@@ -1,0 +1,132 @@
+"""Python operator surface: mirror of reference quest/utils/__init__.py:11-276 (same names, arguments,
+allocation behaviour), on top of quest_b200._kernels."""
+from typing import Optional
+
+import torch
+
+import quest_b200._kernels as _kernels
+from quest_b200.utils.utils import TensorLayout
+from quest_b200.utils.kv_cache import KvCache
+from quest_b200.utils.controller import InferenceController
+from quest_b200.utils.decode_wrapper import BatchDecodeWithPagedKVCacheWrapper
+
+__all__ = [
+    'TensorLayout',
+    'KvCache',
+    'InferenceController',
+    "BatchDecodeWithPagedKVCacheWrapper",
+    "append_kv",
+    "prefill_forward",
+    "decode_estimate",
+    "decode_topk",
+    "decode_sparse_attn",
+    "rms_norm_forward",
+    "apply_rope_in_place",
+]
+
+
+def apply_rope_in_place(q: torch.Tensor, k: torch.Tensor, past_kv_len: int, rope_scale: Optional[float] = None,
+                        rope_theta: Optional[float] = None):
+    """RoPE in place on q, k ``[N, H, D]`` at positions past_kv_len.. (reference __init__.py:25-52)."""
+    if rope_scale is None:
+        rope_scale = 1.0
+    if rope_theta is None:
+        rope_theta = 1e4
+    _kernels.apply_rope_in_place(q, k, past_kv_len, rope_scale, rope_theta)
+
+
+def rms_norm_forward(input: torch.Tensor, weight: torch.Tensor, epsilon: float) -> torch.Tensor:
+    """reference __init__.py:54-67"""
+    o = torch.empty_like(input, dtype=input.dtype, device=input.device)
+    _kernels.rms_norm_forward(input, weight, o, epsilon)
+    return o
+
+
+def append_kv(k: torch.Tensor, v: torch.Tensor, iController: InferenceController, layer_idx: int):
+    """Append k/v ``[N, H, D]`` to the KV cache and update the page min/max metadata; dispatches to the
+    prefill (N > 1) or decode (N == 1) kernel (reference __init__.py:69-125)."""
+    seq_len = k.size(0)
+    f = _kernels.append_kv_cache_prefill if seq_len > 1 else _kernels.append_kv_cache_decode
+    f(
+        k,
+        v,
+        iController.kv_cache.buf_layer(layer_idx),
+        iController.kv_indices_with_last,
+        iController.kv_indptr_for_append,
+        iController.kv_cache.last_page_len,
+        iController.kv_last_page_idx,
+        iController.metadata_cache.buf_layer(layer_idx),
+        iController.metadata_indices,
+        iController.metadata_indptr_for_append,
+        iController.metadata_cache.last_page_len,
+        iController.metadata_last_page_idx,
+        iController.layout,
+    )
+
+
+def prefill_forward(q: torch.Tensor, iController: InferenceController, layer_idx: int,
+                    rope_scale: Optional[float] = None, rope_theta: Optional[float] = None) -> torch.Tensor:
+    """Causal attention of the new queries over the (already appended) paged cache (reference __init__.py:127-169)."""
+    if rope_scale is None:
+        rope_scale = 1.0
+    if rope_theta is None:
+        rope_theta = 1e4
+    return _kernels.prefill_with_paged_kv_cache(
+        q,
+        iController.kv_cache.buf_layer(layer_idx),
+        iController.kv_indices_with_last,
+        iController.kv_cache.last_page_len,
+        True,  # causal
+        iController.layout,
+        False,  # fp32 QK accumulation
+        rope_scale,
+        rope_theta,
+    )
+
+
+def decode_estimate(q: torch.Tensor, iController: InferenceController, layer_idx: int) -> torch.Tensor:
+    """Upper-bound attention score per page and head, last page excluded (reference __init__.py:171-205)."""
+    o = torch.empty((iController.num_heads, iController.metadata_cache.seqlen - 1), dtype=q.dtype, device=q.device)
+    _kernels.estimate_attn_score(
+        q,
+        o,
+        iController.metadata_cache.buf_layer(layer_idx),
+        iController.metadata_indices,
+        iController.metadata_indptr_for_append,
+        iController.metadata_cache.last_page_len,
+        iController.metadata_last_page_idx,
+        iController.layout,
+    )
+    return o
+
+
+def decode_topk(estimated_attn_score: torch.Tensor, iController: InferenceController):
+    """Select the page_budget-1 highest-scoring pages per head into iController.topk_dindices_buffer
+    (reference __init__.py:207-237)."""
+    page_budet = iController.inference_page_budget - 1  # excluding the last page
+    _kernels.topk_filtering(
+        estimated_attn_score,
+        iController.kv_indices_without_last,
+        iController.topk_dout_buffer,
+        iController.topk_dindices_buffer,
+        iController.topk_buf,
+        page_budet,
+    )
+
+
+def decode_sparse_attn(q: torch.Tensor, iController: InferenceController, layer_idx: int, topk_indices: torch.Tensor,
+                       rope_scale: Optional[float] = None, rope_theta: Optional[float] = None) -> torch.Tensor:
+    """Attention over the selected pages plus the last page (reference __init__.py:239-276)."""
+    o = torch.empty_like(q, dtype=q.dtype, device=q.device)
+    iController._decode_handler.forward(
+        q,
+        o,
+        iController.kv_cache.buf_layer(layer_idx),
+        topk_indices,
+        iController.kv_indptr_for_approx_decode,
+        iController.kv_cache.last_page_len,
+        iController.kv_last_page_idx,
+        rope_scale,
+        rope_theta,
+    )
+    return o

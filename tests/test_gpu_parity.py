@@ -1,0 +1,371 @@
+"""GPU parity tests: the CUDA path (through quest_b200._kernels -> C ABI) against the CPU oracle on the same
+seeded inputs.  Bars: metadata, estimate scores and top-k page sets bit-exact; attention max-abs-err <= 2e-3."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import quest_b200._kernels as K
+import quest_b200.utils as qu
+from oracle import quest_oracle as orc
+from tests.helpers import OracleCache, golden_inputs
+
+pytestmark = pytest.mark.gpu
+ATTN_ATOL = 2e-3  # north_star: fp16 attention output max abs error
+DEV = "cuda:0"
+
+
+def t(x, dtype=None):
+    return torch.from_numpy(np.ascontiguousarray(x)).to(DEV) if dtype is None else torch.from_numpy(np.ascontiguousarray(x)).to(DEV, dtype)
+
+
+def bits(x):
+    return x.detach().cpu().contiguous().view(torch.int16).numpy()
+
+
+class GpuCache:
+    """Device pools driven with the same (shuffled) page tables as an OracleCache."""
+
+    def __init__(self, oc: OracleCache):
+        self.oc = oc
+        self.kv = torch.full(oc.kv_pool.shape, float("nan"), dtype=torch.float16, device=DEV)
+        self.meta = torch.full(oc.meta_pool.shape, float("nan"), dtype=torch.float16, device=DEV)
+
+    def tables(self):
+        oc = self.oc
+        return (torch.tensor(oc.kv_indices, dtype=torch.int32, device=DEV),
+                torch.tensor([0, len(oc.kv_indices)], dtype=torch.int32, device=DEV),
+                torch.tensor(oc.meta_indices, dtype=torch.int32, device=DEV),
+                torch.tensor([0, len(oc.meta_indices)], dtype=torch.int32, device=DEV))
+
+    def append(self, k, v):
+        """Call AFTER oc.append(k, v) so the tables already include the new tokens."""
+        oc = self.oc
+        kvi, kvp, mi, mp = self.tables()
+        f = K.append_kv_cache_prefill if k.shape[0] > 1 else K.append_kv_cache_decode
+        f(t(k), t(v), self.kv, kvi, kvp, oc.last_page_len, oc.kv_indices[-1], self.meta, mi, mp,
+          oc.meta_last_page_len, oc.meta_indices[-1], 0)
+
+    def assert_equal_oracle(self):
+        oc = self.oc
+        for pool_g, pool_o, idx in ((self.kv, oc.kv_pool, oc.kv_indices), (self.meta, oc.meta_pool, oc.meta_indices)):
+            g = pool_g[torch.tensor(idx, device=DEV)].cpu().numpy()
+            o = pool_o[idx]
+            written = ~np.isnan(o)
+            np.testing.assert_array_equal(g.view(np.int16)[written], o.view(np.int16)[written])
+            assert np.isnan(g[~written]).all()  # nothing outside the oracle's footprint was written
+
+
+def rand_kv(rng, n, H, D):
+    return (rng.standard_normal((n, H, D), dtype=np.float32).astype(np.float16),
+            rng.standard_normal((n, H, D), dtype=np.float32).astype(np.float16))
+
+
+def make_pair(kv_len, P, H, D, seed, rounds=None):
+    """Oracle + GPU caches filled with a prefill of kv_len-1 tokens and one decode append (reference
+    quest/tests/test_estimate.py:117-130), or with an explicit list of append sizes."""
+    rng = np.random.default_rng(seed)
+    rounds = [kv_len - 1, 1] if rounds is None else rounds
+    oc = OracleCache((sum(rounds) + P - 1) // P + 2, P, H, D, seed=seed)
+    gc = GpuCache(oc)
+    ks, vs = [], []
+    for n in rounds:
+        k, v = rand_kv(rng, n, H, D)
+        oc.append(k, v)
+        gc.append(k, v)
+        ks.append(k), vs.append(v)
+    return oc, gc, np.concatenate(ks), np.concatenate(vs), rng
+
+
+# ------------------------------------------------------------------ append + metadata (bit-exact)
+@pytest.mark.parametrize("P", [1, 3, 7, 16, 31])
+@pytest.mark.parametrize("kv_len,H,D", [(17, 32, 128), (97, 4, 64), (409, 8, 128), (1100, 2, 256), (4100, 32, 128)])
+def test_append_prefill_then_decode_bitexact(kv_len, H, D, P):
+    if kv_len // P > 600:
+        pytest.skip("oracle too slow")
+    oc, gc, *_ = make_pair(kv_len, P, H, D, seed=kv_len + P)
+    gc.assert_equal_oracle()
+
+
+@pytest.mark.parametrize("P,H,D", [(16, 32, 128), (7, 4, 64), (1, 2, 128)])
+def test_append_multi_round_mixed(P, H, D):
+    """Partial-page resume, page-boundary decodes and back-to-back prefills (reference test_page.cu:381-618)."""
+    rounds = [5, 1, 1, 27, 1, 16, 2, 1, 1, 1, 40, 1]
+    oc, gc, *_ = make_pair(0, P, H, D, seed=3, rounds=rounds)
+    gc.assert_equal_oracle()
+
+
+# ------------------------------------------------------------------ estimate (bit-exact)
+@pytest.mark.parametrize("kv_len", [27, 61, 113, 482, 577, 1110, 1541, 2047, 3330])
+def test_estimate_bitexact_reference_sweep(kv_len):
+    H, D, P = 32, 128, 16
+    oc, gc, k, v, rng = make_pair(kv_len, P, H, D, seed=kv_len)
+    q = rng.standard_normal((1, H, D), dtype=np.float32).astype(np.float16)
+    n = len(oc.kv_indices) - 1
+    o = torch.empty((H, n), dtype=torch.float16, device=DEV)
+    kvi, kvp, mi, mp = gc.tables()
+    K.estimate_attn_score(t(q), o, gc.meta, mi, mp, oc.meta_last_page_len, oc.meta_indices[-1], 0)
+    want = orc.estimate_scores(q[0], oc.meta_pool, oc.meta_indices, n)
+    np.testing.assert_array_equal(bits(o), want.view(np.int16))
+    # and within the reference's own tolerance of its torch restatement
+    np.testing.assert_allclose(o.float().cpu().numpy(), orc.estimate_scores_torch_ref(q[0], k, P).astype(np.float32),
+                               rtol=5e-3, atol=5e-3)
+
+
+@pytest.mark.parametrize("Hq,Hkv,D,P,kv_len", [(8, 8, 64, 16, 300), (4, 4, 256, 16, 200), (32, 8, 128, 16, 1000),
+                                                (8, 2, 128, 7, 150), (6, 3, 64, 1, 40), (32, 32, 128, 32, 2100)])
+def test_estimate_bitexact_shapes_and_gqa(Hq, Hkv, D, P, kv_len):
+    oc, gc, k, v, rng = make_pair(kv_len, P, Hkv, D, seed=kv_len + D)
+    q = rng.standard_normal((1, Hq, D), dtype=np.float32).astype(np.float16)
+    n = len(oc.kv_indices) - 1
+    o = torch.empty((Hq, n), dtype=torch.float16, device=DEV)
+    kvi, kvp, mi, mp = gc.tables()
+    K.estimate_attn_score(t(q), o, gc.meta, mi, mp, oc.meta_last_page_len, oc.meta_indices[-1], 0)
+    np.testing.assert_array_equal(bits(o), orc.estimate_scores(q[0], oc.meta_pool, oc.meta_indices, n, Hq).view(np.int16))
+
+
+# ------------------------------------------------------------------ top-k (exact set, deterministic order)
+def run_topk(scores, payload, k):
+    H, n = scores.shape
+    dout = torch.zeros((H, k), dtype=torch.float16, device=DEV)
+    iout = torch.full((H, k), -1, dtype=torch.int32, device=DEV)
+    K.topk_filtering(t(scores), payload, dout, iout, None, k)
+    return dout.cpu().numpy(), iout.cpu().numpy()
+
+
+@pytest.mark.parametrize("n,k", [(13, 2), (24, 24), (77, 19), (311, 69), (1110, 251), (2047, 127), (2047, 1),
+                                 (8191, 255), (8192, 4095), (65535, 511)])
+@pytest.mark.parametrize("dist", ["normal", "ties", "const"])
+def test_topk_exact(n, k, dist):
+    H = 32 if n < 10000 else 4
+    rng = np.random.default_rng(n * 7 + k)
+    if dist == "normal":
+        s = (rng.standard_normal((H, n)) * 30 + 100).astype(np.float16)
+    elif dist == "ties":  # few distinct values incl. +-0 and negatives: threshold ties everywhere
+        s = rng.choice(np.array([-2.0, -0.0, 0.0, 0.5, 1.0, 1.5, 96.0], dtype=np.float16), size=(H, n))
+    else:
+        s = np.full((H, n), 3.25, dtype=np.float16)
+    perm = rng.permutation(n).astype(np.int32)  # payload = shuffled page table
+    payload = t(perm).unsqueeze(0).expand(H, -1)
+    dout, iout = run_topk(s, payload, k)
+    want_pos = orc.topk_select(s, k)
+    np.testing.assert_array_equal(iout, perm[want_pos])
+    np.testing.assert_array_equal(dout.view(np.int16), np.take_along_axis(s, want_pos.astype(np.int64), 1).view(np.int16))
+    assert orc.topk_contract_ok(s, want_pos, k)
+    # contiguous [H, n] payload (the reference's layout, controller.py:106) gives the same result
+    _, iout2 = run_topk(s, payload.contiguous(), k)
+    np.testing.assert_array_equal(iout2, iout)
+
+
+def test_topk_reference_test_criterion():
+    """quest/tests/test_topk.py:22-64: sum of selected values == torch.topk(...).values.sum()."""
+    torch.manual_seed(0)
+    for kv_len, kb in [(13, 2), (244, 111), (1110, 251)]:
+        w = (torch.randn(32, kv_len, device=DEV) * 3).half()
+        dout = torch.randn(32, kb, dtype=torch.float16, device=DEV)
+        iout = torch.zeros(32, kb, dtype=torch.int32, device=DEV)
+        idx = torch.arange(kv_len, dtype=torch.int32, device=DEV).repeat(32, 1)
+        K.topk_filtering(w, idx, dout, iout, torch.zeros(32, 1024, dtype=torch.float16, device=DEV), kb)
+        torch.testing.assert_close(dout.float().sum(-1), torch.topk(w.float(), kb, dim=-1).values.sum(-1), rtol=5e-3, atol=5e-3)
+
+
+# ------------------------------------------------------------------ sparse decode attention
+def run_decode(q, gc, sel_phys, oc):
+    Hq = q.shape[1]
+    n_sel = sel_phys.shape[1]
+    w = K.BatchDecodeWithPagedKVCachePyTorchWrapper(0)
+    indptr = torch.tensor([0, n_sel], dtype=torch.int32, device=DEV)
+    w.begin_forward(indptr, Hq, gc.kv.shape[3], q.shape[2], gc.kv.shape[2], torch.empty(0, dtype=torch.float16))
+    o = torch.empty((1, Hq, q.shape[2]), dtype=torch.float16, device=DEV)
+    idx = t(sel_phys.astype(np.int32)) if n_sel else torch.zeros((Hq, 0), dtype=torch.int32, device=DEV)
+    w.forward(t(q), o, gc.kv, idx, indptr, oc.last_page_len, oc.kv_indices[-1], 1.0, 1e4)
+    w.end_forward()
+    return o
+
+
+@pytest.mark.parametrize("P", [1, 3, 7, 16, 32])
+@pytest.mark.parametrize("kv_len,budget,Hq,Hkv,D", [(63, 16, 32, 32, 128), (2047, 32, 32, 32, 128), (577, 64, 8, 8, 64),
+                                                   (1541, 128, 32, 8, 128), (300, 4, 4, 4, 256), (33, 1, 32, 32, 128)])
+def test_sparse_decode_random_page_subsets(kv_len, budget, Hq, Hkv, D, P):
+    """Random distinct per-head page subsets (reference test_batch_decode.cu:61-76, sweep :236-257)."""
+    if kv_len // P > 700:
+        pytest.skip("oracle too slow")
+    oc, gc, k, v, rng = make_pair(kv_len, P, Hkv, D, seed=kv_len + P + budget)
+    n_pages = len(oc.kv_indices)
+    n_sel = min(budget, n_pages) - 1
+    logical = np.stack([np.sort(rng.permutation(n_pages - 1)[:n_sel]) for _ in range(Hq)]) if n_sel else np.zeros((Hq, 0), np.int64)
+    phys = np.asarray(oc.kv_indices, dtype=np.int32)[logical] if n_sel else np.zeros((Hq, 0), np.int32)
+    q = rng.standard_normal((1, Hq, D), dtype=np.float32).astype(np.float16)
+    o = run_decode(q, gc, phys, oc)
+    want, _ = orc.sparse_decode_attention(q[0], oc.kv_pool, phys, oc.kv_indices[-1], oc.last_page_len)
+    assert torch.isfinite(o).all()
+    assert np.abs(o[0].float().cpu().numpy() - want).max() <= ATTN_ATOL
+
+
+@pytest.mark.parametrize("kv_len", [27, 61, 113, 482, 577, 1011])
+def test_full_budget_decode_equals_dense(kv_len):
+    """quest/tests/test_decode_attention.py:46-111 through the controller surface."""
+    H, D, P = 32, 128, 16
+    rng = np.random.default_rng(kv_len)
+    q, k, v = golden_inputs(kv_len, kv_len, H, D)
+    ic = qu.InferenceController(1, H, D, P, 1024, 2048, torch.float16, torch.device(DEV))
+    ic.prepare_metadata(kv_len - 1), ic.begin_forward(kv_len - 1)
+    qu.append_kv(t(k[:-1]), t(v[:-1]), ic, 0)
+    ic.end_forward()
+    ic.prepare_metadata(1), ic.begin_forward(1)
+    qu.append_kv(t(k[-1:]), t(v[-1:]), ic, 0)
+    assert not ic.need_estimate()
+    o = qu.decode_sparse_attn(t(q), ic, 0, ic.kv_indices_without_last)
+    ic.end_forward()
+    want = orc.dense_attention(q, k, v, causal=True)
+    assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL
+
+
+# ------------------------------------------------------------------ whole layer step through the operator surface
+@pytest.mark.parametrize("kv_len,budget", [(61, 3), (113, 4), (482, 7), (577, 15), (1011, 31), (1541, 55), (3330, 71)])
+def test_layer_step_matches_oracle(kv_len, budget):
+    """append(prefill) -> append(decode) -> estimate -> topk -> sparse attn, as QuestAttention.forward drives it
+    (quest/models/QuestAttention.py:99-158); page set bit-exact, output within 2e-3."""
+    H, D, P = 32, 128, 16
+    q, k, v = golden_inputs(kv_len * 3 + budget, kv_len, H, D)
+    ic = qu.InferenceController(2, H, D, P, budget, 4096, torch.float16, torch.device(DEV))
+    ic.prepare_metadata(kv_len - 1), ic.begin_forward(kv_len - 1)
+    qu.append_kv(t(k[:-1]), t(v[:-1]), ic, 1)
+    ic.end_forward()
+    ic.prepare_metadata(1), ic.begin_forward(1)
+    qu.append_kv(t(k[-1:]), t(v[-1:]), ic, 1)
+    assert ic.need_estimate()
+    s = qu.decode_estimate(t(q), ic, 1)
+    qu.decode_topk(s, ic)
+    o = qu.decode_sparse_attn(t(q), ic, 1, ic.topk_dindices_buffer)
+    ic.end_forward()
+
+    oc = OracleCache(len(ic.kv_cache.indicies), P, H, D, shuffle=False)
+    oc.append(k[:-1], v[:-1]), oc.append(k[-1:], v[-1:])
+    assert oc.kv_indices == ic.kv_cache.indicies
+    want_o, want_s, want_sel = orc.quest_decode_step(q[0], oc.kv_pool, oc.kv_indices, oc.last_page_len, oc.meta_pool,
+                                                     oc.meta_indices, budget)
+    np.testing.assert_array_equal(bits(s), want_s.view(np.int16))
+    np.testing.assert_array_equal(ic.topk_dindices_buffer.cpu().numpy(), np.asarray(oc.kv_indices, np.int32)[want_sel])
+    assert np.abs(o[0].float().cpu().numpy() - want_o).max() <= ATTN_ATOL
+
+
+def test_fused_step_equals_separate_calls():
+    H, D, P, kv_len, budget = 32, 128, 16, 2500, 32
+    oc, gc, k, v, rng = make_pair(kv_len, P, H, D, seed=11)
+    q = rng.standard_normal((1, H, D), dtype=np.float32).astype(np.float16)
+    n = len(oc.kv_indices) - 1
+    kk = budget - 1
+    kvi, kvp, mi, mp = gc.tables()
+    s1 = torch.empty((H, n), dtype=torch.float16, device=DEV)
+    K.estimate_attn_score(t(q), s1, gc.meta, mi, mp, oc.meta_last_page_len, oc.meta_indices[-1], 0)
+    i1 = torch.zeros((H, kk), dtype=torch.int32, device=DEV)
+    K.topk_filtering(s1, kvi[:-1].unsqueeze(0).expand(H, -1), torch.zeros((H, kk), dtype=torch.float16, device=DEV), i1, None, kk)
+    o1 = run_decode(q, gc, i1.cpu().numpy(), oc)
+
+    lib = K.load_library()
+    import ctypes
+    ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
+    assert lib.quest_decode_plan(kk, H, H, D, P, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0
+    ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, nch.value), dtype=torch.uint8, device=DEV)
+    s2, i2 = torch.empty_like(s1), torch.zeros_like(i1)
+    o2 = torch.empty((1, H, D), dtype=torch.float16, device=DEV)
+    tq = t(q)
+    for _ in range(3):  # repeated launches reuse the self-resetting workspace
+        rc = lib.quest_sparse_decode_step(tq.data_ptr(), o2.data_ptr(), gc.kv.data_ptr(), kvi.data_ptr(), n,
+                                          oc.kv_indices[-1], oc.last_page_len, gc.meta.data_ptr(), mi.data_ptr(),
+                                          s2.data_ptr(), i2.data_ptr(), kk, H, H, D, P, ppc.value, ws.data_ptr(),
+                                          ws.numel(), torch.cuda.current_stream().cuda_stream)
+        assert rc == 0
+    torch.cuda.synchronize()
+    assert torch.equal(s1, s2) and torch.equal(i1, i2) and torch.equal(o1, o2)
+
+
+# ------------------------------------------------------------------ golden vectors from the reference's own code
+def test_kernel_path_against_reference_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "kernel_path.npz"))
+    for i in range(5):
+        seed, kv_len, budget, H, D, P = (int(x) for x in g[f"meta_{i}"])
+        q, k, v = golden_inputs(seed, kv_len, H, D)
+        oc = OracleCache((kv_len + P - 1) // P + 2, P, H, D, seed=seed)
+        gc = GpuCache(oc)
+        oc.append(k[:-1], v[:-1]), gc.append(k[:-1], v[:-1])
+        oc.append(k[-1:], v[-1:]), gc.append(k[-1:], v[-1:])
+        n = len(oc.kv_indices) - 1
+        s = torch.empty((H, n), dtype=torch.float16, device=DEV)
+        kvi, kvp, mi, mp = gc.tables()
+        K.estimate_attn_score(t(q), s, gc.meta, mi, mp, oc.meta_last_page_len, oc.meta_indices[-1], 0)
+        np.testing.assert_allclose(s.float().cpu().numpy(), g[f"est_{i}"].astype(np.float32), rtol=5e-3, atol=5e-3)
+        phys = np.asarray(oc.kv_indices, np.int32)[g[f"apx_topk_{i}"]]
+        o = run_decode(q, gc, phys, oc)
+        np.testing.assert_allclose(o.float().cpu().numpy(), g[f"apx_o_{i}"], rtol=5e-3, atol=5e-3)
+
+
+# ------------------------------------------------------------------ rope / rms_norm / prefill / merge
+@pytest.mark.parametrize("seq,past,Hq,Hkv,D", [(1, 0, 32, 32, 128), (1, 4097, 32, 32, 128), (37, 100, 8, 2, 64), (130, 0, 4, 4, 256)])
+def test_rope(seq, past, Hq, Hkv, D):
+    rng = np.random.default_rng(seq + past)
+    q = rng.standard_normal((seq, Hq, D), dtype=np.float32).astype(np.float16)
+    k = rng.standard_normal((seq, Hkv, D), dtype=np.float32).astype(np.float16)
+    tq, tk = t(q), t(k)
+    qu.apply_rope_in_place(tq, tk, past)
+    np.testing.assert_allclose(tq.float().cpu().numpy(), orc.rope(q, past), rtol=5e-3, atol=5e-3)
+    np.testing.assert_allclose(tk.float().cpu().numpy(), orc.rope(k, past), rtol=5e-3, atol=5e-3)
+
+
+def test_rms_norm():
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((1, 5, 4096), dtype=np.float32).astype(np.float16)
+    w = rng.standard_normal(4096, dtype=np.float32).astype(np.float16)
+    o = qu.rms_norm_forward(t(x), t(w), 1e-5)
+    np.testing.assert_allclose(o.float().cpu().numpy(), orc.rms_norm(x, w, 1e-5), rtol=5e-3, atol=5e-3)
+
+
+@pytest.mark.parametrize("qo_len,kv_len,Hq,Hkv,D,P", [(13, 33, 32, 32, 128, 16), (502, 1110, 8, 8, 128, 16), (64, 64, 8, 2, 64, 8),
+                                                     (47, 111, 4, 1, 128, 1), (200, 333, 4, 4, 64, 16)])
+def test_prefill_matches_dense_causal(qo_len, kv_len, Hq, Hkv, D, P):
+    """quest/tests/test_prefill_attention.py:46-87 + GQA cases of kernels/src/test/test_prefill.cu:407-467."""
+    rng = np.random.default_rng(qo_len + kv_len)
+    rounds = [kv_len - qo_len, qo_len] if kv_len > qo_len else [qo_len]
+    oc, gc, k, v, rng = make_pair(0, P, Hkv, D, seed=qo_len, rounds=[r for r in rounds if r])
+    q = rng.standard_normal((qo_len, Hq, D), dtype=np.float32).astype(np.float16)
+    kvi, *_ = gc.tables()
+    o = K.prefill_with_paged_kv_cache(t(q), gc.kv, kvi, oc.last_page_len, True, 0, False, 1.0, 1e4)
+    want = orc.dense_attention(q, k, v, causal=True)
+    assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL
+
+
+def test_merge_states():
+    rng = np.random.default_rng(1)
+    n, H, D = 5, 32, 128
+    o_parts = rng.standard_normal((n, H, D), dtype=np.float32)
+    lse = (rng.standard_normal((n, H), dtype=np.float32) * 4)
+    o = torch.empty((H, D), dtype=torch.float16, device=DEV)
+    l = torch.empty(H, dtype=torch.float32, device=DEV)
+    lib = K.load_library()
+    to, tl = t(o_parts), t(lse)
+    assert lib.quest_merge_states(to.data_ptr(), tl.data_ptr(), n, o.data_ptr(), l.data_ptr(), H, D,
+                                  torch.cuda.current_stream().cuda_stream) == 0
+    wo, wl = orc.merge_states(o_parts, lse)
+    np.testing.assert_allclose(o.float().cpu().numpy(), wo, rtol=2e-3, atol=2e-3)
+    np.testing.assert_allclose(l.cpu().numpy(), wl, rtol=1e-4, atol=1e-4)
+
+
+def test_error_behaviour_matches_reference_checks():
+    H, D, P = 32, 128, 16
+    kv = torch.zeros(4, 2, P, H, D, dtype=torch.float16, device=DEV)
+    idx = torch.zeros(2, dtype=torch.int32, device=DEV)
+    ptr = torch.tensor([0, 2], dtype=torch.int32, device=DEV)
+    k = torch.zeros(1, H, D, dtype=torch.float16, device=DEV)
+    with pytest.raises(RuntimeError, match="dispatch with dtype"):
+        K.append_kv_cache_decode(k.float(), k.float(), kv, idx, ptr, 1, 0, kv, idx, ptr, 1, 0, 0)
+    with pytest.raises(RuntimeError, match="CHECK_EQ"):
+        K.append_kv_cache_decode(k.repeat(2, 1, 1), k.repeat(2, 1, 1), kv, idx, ptr, 1, 0, kv, idx, ptr, 1, 0, 0)
+    with pytest.raises(RuntimeError, match="kInt32"):
+        K.append_kv_cache_decode(k, k, kv, idx.long(), ptr, 1, 0, kv, idx, ptr, 1, 0, 0)
+    with pytest.raises(RuntimeError, match="contiguous"):
+        K.append_kv_cache_decode(k.transpose(1, 2), k, kv, idx, ptr, 1, 0, kv, idx, ptr, 1, 0, 0)
+    with pytest.raises(RuntimeError, match="CHECK_GE"):
+        K.topk_filtering(torch.zeros(H, 4, dtype=torch.float16, device=DEV), torch.zeros(H, 4, dtype=torch.int32, device=DEV),
+                         torch.zeros(H, 9, dtype=torch.float16, device=DEV), torch.zeros(H, 9, dtype=torch.int32, device=DEV), None, 9)
