@@ -72,7 +72,7 @@ def _check_rows(x, name):
     _check(isinstance(x, torch.Tensor) and x.is_cuda, f"{name} must be a CUDA tensor")
     _check(x.dim() == 2, f"{name} must be a 2D tensor")
     _check(x.size(1) <= 1 or x.stride(1) == 1, f"{name} must be contiguous")
-    _check(x.size(0) <= 1 or x.stride(0) in (0, x.size(1)), f"{name} must be contiguous")
+    _check(x.size(0) <= 1 or x.size(1) == 0 or x.stride(0) in (0, x.size(1)), f"{name} must be contiguous")
     return 0 if (x.size(0) > 1 and x.stride(0) == 0) else x.size(1)
 
 
