@@ -77,11 +77,15 @@ int quest_append_prefill(const void* k, const void* v, uint32_t append_len,
  * o[h, p] = fp16( sum_d max(q[h,d]*max[p,h/g,d], q[h,d]*min[p,h/g,d]) ) for the first `len`
  * KV pages (the caller excludes the last page: len = num_kv_pages - 1).  fp32 products/sums in the
  * reference's order (8 dims per lane sequentially, then xor-butterfly over head_dim/8 lanes), so
- * scores are bit-identical to the reference kernel.  q: [num_qo_heads, head_dim]; o: [num_qo_heads, len]. */
+ * scores are bit-identical to the reference kernel.  q: [num_qo_heads, head_dim]; o: [num_qo_heads, len].
+ * flags: QUEST_EST_META_STABLE promises that the kernel enqueued immediately before this one on `stream`
+ * does not write metadata entries [0, len) (true in the layer step: append only touches the last page's
+ * entry), which lets the metadata stream start before the programmatic dependency on that kernel resolves. */
+#define QUEST_EST_META_STABLE 1u
 int quest_estimate(const void* q, void* o, uint32_t len,
                    const void* meta_data, const int32_t* meta_indices,
                    uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
-                   uint32_t page_size, void* stream);
+                   uint32_t page_size, uint32_t flags, void* stream);
 
 /* ---- top-k -------------------------------------------------------------------------------------
  * Replaces topk_filtering (bsk_ops.h:34-39, topk.cu:7-46, kernels/include/topk/decode_select_k.cuh:25-62,

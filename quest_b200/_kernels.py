@@ -24,7 +24,7 @@ SIGNATURES = {
     "quest_rms_norm": (_c.c_int, [_vp, _vp, _vp, _u32, _u32, _f32, _vp]),
     "quest_append_decode": (_c.c_int, [_vp, _vp, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _vp]),
     "quest_append_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _vp]),
-    "quest_estimate": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _vp]),
+    "quest_estimate": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _vp]),
     "quest_topk_max_len": (_u32, []),
     "quest_topk": (_c.c_int, [_vp, _i32p, _u32, _vp, _i32p, _u32, _u32, _u32, _vp]),
     "quest_decode_plan": (_c.c_int, [_u32, _u32, _u32, _u32, _u32, _u32, _c.POINTER(_u32), _c.POINTER(_u32)]),
@@ -166,7 +166,7 @@ def estimate_attn_score(q, o, metadata_data, metadata_indices, metadata_indptr, 
     _check(o.size(1) == n_entries, f"o.size(1) must equal the number of scored pages {n_entries}")
     _check_half(q, "Estimate_attn_score")
     _rc(load_library().quest_estimate(q.data_ptr(), o.data_ptr(), o.size(1), metadata_data.data_ptr(),
-                                      metadata_indices.data_ptr(), Hq, Hkv, D, P, _stream()), "estimate_attn_score")
+                                      metadata_indices.data_ptr(), Hq, Hkv, D, P, 0, _stream()), "estimate_attn_score")
 
 
 def _append_checks(k, v, kv_data, kv_indices, kv_indptr, metadata_data, metadata_indices, metadata_indptr, layout, op):

@@ -1,10 +1,20 @@
 // Library-level entry points: identification, launch counter, and the fused layer step that chains
 // estimate -> top-k -> sparse decode with programmatic dependent launch (one call per layer per token;
 // reference call sites quest/models/QuestAttention.py:135-158).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace quest {
 unsigned long long g_launch_count = 0;
+int pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("QUEST_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v;
+}
 }
 
 extern "C" const char* quest_version(void) { return "quest_b200 0.1.0 sm_100a"; }
@@ -21,7 +31,7 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
   if (!kv_indices || !scores || !topk_idx) return QUEST_ERR_BAD_ARG;
   if (k > len) return QUEST_ERR_BAD_ARG;
   int rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                          stream);
+                          QUEST_EST_META_STABLE, stream);
   if (rc) return rc;
   // payload ids = the sequence's page table, shared by all heads (row stride 0)
   rc = quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);

@@ -9,6 +9,7 @@
 namespace quest {
 
 extern unsigned long long g_launch_count;  // defined in capi.cu
+int pdl_enabled();  // 1 unless QUEST_PDL=0 in the environment (capi.cu); programmatic dependent launch attribute
 
 // 16-byte vector of 8 halves: the reference's vec_t<half, 8> (vec_size = max(16/sizeof(half), D/32)).
 struct alignas(16) H8 {

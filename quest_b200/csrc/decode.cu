@@ -4,15 +4,15 @@
 // decode_handler.cuh:73-121; flashinfer cascade.cuh:279-340, state.cuh:53-62).
 //
 // Unit of work = (q head, chunk of pages).  Each group of D/8 lanes owns whole 16-byte-per-lane token
-// rows; a tile of kTile tokens issues 2*kTile independent 128-bit loads per lane before any use, so a
-// CTA has its whole chunk in flight at once.  Partials go to a caller-owned workspace; the last CTA to
-// arrive for a head (atomic ticket) merges them -- no separate merge launch.
+// rows; every warp keeps two items (8 independent 128-bit loads per lane) in flight while it consumes the
+// previous one.  Partials go to a caller-owned workspace; the last CTA to arrive for a head (atomic
+// ticket) merges them -- no separate merge launch.
 #include "common.cuh"
 
 namespace quest {
 
 constexpr int kDecThreads = 128;
-constexpr int kTile = 8;
+constexpr int kDecWarps = kDecThreads / 32;
 constexpr float kNegBig = -1e30f;
 
 // workspace layout: [Hq*nchunks*D] fp32 o | [Hq*nchunks*2] fp32 (m,d) | [Hq] u32 tickets
@@ -23,25 +23,43 @@ __host__ __device__ inline size_t ws_ticket_off(uint32_t Hq, uint32_t D, uint32_
   return ws_md_off(Hq, D, nchunks) + (size_t)Hq * nchunks * 2 * sizeof(float);
 }
 
+// t / P for any page size: p_magic = ceil(2^32 / P) (0 for P == 1); exact while t < 2^32 / P.
+__host__ __device__ inline uint32_t div_magic(uint32_t P) { return P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P); }
+__device__ __forceinline__ uint32_t div_p(uint32_t t, uint32_t p_magic) { return p_magic ? __umulhi(t, p_magic) : t; }
+
+// One CTA = (q head, chunk of pages).  Each of the 4 warps walks its share of the chunk's tokens in items of
+// 2 warp-wide K loads + 2 V loads (a lane group of D/8 lanes owns one 16-byte-per-lane token row), with
+// the next item's loads issued before the current item is consumed: 8 independent 128-bit loads per lane
+// stay in flight, ~128 KB per SM at 8 CTAs/SM, and the softmax arithmetic hides under them.
 template <int D>
-__global__ void __launch_bounds__(kDecThreads)
+__global__ void __launch_bounds__(kDecThreads, 8)
 decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __restrict__ lse,
               const __half* __restrict__ kv, const int32_t* __restrict__ indices, uint32_t idx_stride,
               uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len, uint32_t Hkv, uint32_t G,
-              uint32_t P, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws) {
+              uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws) {
   constexpr int LPR = D / 8;
-  constexpr int NG = kDecThreads / LPR;
+  constexpr int TPL = 32 / LPR;           // token rows per warp-wide load
+  constexpr int IT = 2 * TPL;             // tokens per item
+  constexpr int NG = kDecWarps * TPL;     // lane groups per CTA
+  extern __shared__ int32_t s_pages[];    // [pages of this chunk]
   __shared__ float s_o[NG][D];
   __shared__ float s_md[NG][2];
   __shared__ uint32_t s_last;
   const uint32_t chunk = blockIdx.x, nchunks = gridDim.x, h = blockIdx.y, Hq = gridDim.y;
   const uint32_t kvh = h / G;
-  const uint32_t tid = threadIdx.x, gid = tid / LPR, lir = tid % LPR;
+  const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t lir = lane % LPR, sub = lane / LPR, gid = warp * TPL + sub;
   const uint32_t total_pages = n_sel + 1;  // + forced last page
   const uint32_t pg0 = chunk * ppc, pg1 = min(pg0 + ppc, total_pages);
-  const uint32_t ntok = (pg1 - pg0) * P;
+  const uint32_t npg = pg1 - pg0, ntok = npg * P;
+  const uint32_t n_items = (ntok + IT - 1) / IT;
   const size_t slab = (size_t)P * Hkv * D;  // K -> V offset inside a page
+  const size_t row = (size_t)Hkv * D;
 
+  pdl_wait();  // q, the page ids (top-k kernel) and the last page's new row (append) come from earlier kernels
+  const int32_t* idx_row = indices + (size_t)h * idx_stride;
+  for (uint32_t i = tid; i < npg; i += kDecThreads)
+    s_pages[i] = pg0 + i < n_sel ? __ldg(idx_row + pg0 + i) : (int32_t)last_page_idx;
   float qv[8];
   {
     const H8 qh = ld_plain(q + (size_t)h * D + lir * 8);
@@ -49,46 +67,50 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
 #pragma unroll
     for (int i = 0; i < 8; ++i) qv[i] *= sm_scale_log2;
   }
+  __syncthreads();
+  pdl_trigger();
+
   float acc[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) acc[i] = 0.f;
   float m = kNegBig, d = 0.f;
 
-  pdl_wait();  // indices come from the top-k kernel
-  const int32_t* idx_row = indices + (size_t)h * idx_stride;
-
-  // Warp-uniform trip count (the shuffles below use the full mask); out-of-range tokens are masked.
-  for (uint32_t base = 0; base < ntok; base += NG * kTile) {
-    const uint32_t t0 = base + gid * kTile;
-    H8 kk[kTile], vv[kTile];
-    bool ok[kTile];
+  H8 kk[2][2], vv[2][2];
+  auto tok_ok = [&](uint32_t t, uint32_t& pgl, uint32_t& e) {
+    pgl = div_p(t, p_magic);
+    e = t - pgl * P;
+    return t < ntok && (pg0 + pgl < n_sel || e < last_page_len);
+  };
+  auto issue = [&](int st, uint32_t it) {
 #pragma unroll
-    for (int j = 0; j < kTile; ++j) {
-      const uint32_t t = t0 + j;
-      const uint32_t pg = pg0 + t / P, e = t % P;
-      ok[j] = t < ntok && (pg < n_sel || e < last_page_len);
-      if (ok[j]) {
-        const size_t page = pg < n_sel ? (size_t)__ldg(idx_row + pg) : (size_t)last_page_idx;
-        const __half* kp = kv + nhd_off(page, 0, e, kvh, P, Hkv, D) + lir * 8;
-        kk[j] = ld_stream(kp);
-        vv[j] = ld_stream(kp + slab);
+    for (int j = 0; j < 2; ++j) {
+      uint32_t pgl, e;
+      if (it < n_items && tok_ok(it * IT + j * TPL + sub, pgl, e)) {
+        const __half* kp = kv + (((size_t)s_pages[pgl] * 2) * P + e) * row + (size_t)kvh * D + lir * 8;
+        kk[st][j] = ld_stream(kp);
+        vv[st][j] = ld_stream(kp + slab);
       }
     }
-    float s[kTile];
+  };
+  auto consume = [&](int st, uint32_t it) {
+    float sc[2];
+    bool ok[2];
     float mt = m;
 #pragma unroll
-    for (int j = 0; j < kTile; ++j) {
-      float kf[8];
+    for (int j = 0; j < 2; ++j) {
+      uint32_t pgl, e;
+      ok[j] = tok_ok(it * IT + j * TPL + sub, pgl, e);
       float a = 0.f;
       if (ok[j]) {
-        h8_to_float(kk[j], kf);
+        float kf[8];
+        h8_to_float(kk[st][j], kf);
 #pragma unroll
         for (int i = 0; i < 8; ++i) a = fmaf(qv[i], kf[i], a);
       }
 #pragma unroll
       for (int off = LPR / 2; off > 0; off >>= 1) a += __shfl_xor_sync(0xffffffffu, a, off);
-      s[j] = ok[j] ? a : kNegBig;
-      mt = fmaxf(mt, s[j]);
+      sc[j] = ok[j] ? a : kNegBig;
+      mt = fmaxf(mt, sc[j]);
     }
     const float scale = ex2(m - mt);
     m = mt;
@@ -96,15 +118,26 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] *= scale;
 #pragma unroll
-    for (int j = 0; j < kTile; ++j) {
+    for (int j = 0; j < 2; ++j) {
       if (ok[j]) {
-        const float p = ex2(s[j] - m);
+        const float p = ex2(sc[j] - m);
         d += p;
         float vf[8];
-        h8_to_float(vv[j], vf);
+        h8_to_float(vv[st][j], vf);
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[i] = fmaf(p, vf[i], acc[i]);
       }
+    }
+  };
+  // warp-uniform trip count (the shuffles use the full mask); out-of-range tokens are masked
+  issue(0, warp);
+  issue(1, warp + kDecWarps);
+  for (uint32_t it = warp; it < n_items; it += 2 * kDecWarps) {
+    consume(0, it);
+    issue(0, it + 2 * kDecWarps);
+    if (it + kDecWarps < n_items) {
+      consume(1, it + kDecWarps);
+      issue(1, it + 3 * kDecWarps);
     }
   }
 
@@ -189,19 +222,23 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
                          uint32_t idx_stride, uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len,
                          uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t ppc, void* ws, cudaStream_t stream) {
   const uint32_t nchunks = (n_sel + 1 + ppc - 1) / ppc;
+  const uint32_t npg_max = ppc < n_sel + 1 ? ppc : n_sel + 1;
+  const size_t smem = (size_t)npg_max * sizeof(int32_t);
+  if (smem > 32 * 1024) return QUEST_ERR_UNSUPPORTED;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(nchunks, Hq);
   cfg.blockDim = dim3(kDecThreads);
+  cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const float sm_scale_log2 = kLog2e / sqrtf((float)D);
   cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<D>, (const __half*)q, (__half*)o, lse, (const __half*)kv,
                                      indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv, Hq / Hkv, P,
-                                     ppc, sm_scale_log2, (uint8_t*)ws);
+                                     div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -215,10 +252,10 @@ extern "C" int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, 
   if (head_dim != 64 && head_dim != 128 && head_dim != 256) return QUEST_ERR_UNSUPPORTED;
   if (num_sms == 0) num_sms = 148;
   const uint32_t total = num_sel_pages + 1;
-  const uint32_t slots = num_sms * 4;  // resident 128-thread CTAs per SM at ~128 registers/thread
-  // Smallest chunk that keeps every CTA resident in one wave, but at least one kTile per lane group.
-  const uint32_t groups = quest::kDecThreads / (head_dim / 8);
-  uint32_t min_ppc = (groups * quest::kTile + page_size - 1) / page_size;
+  const uint32_t slots = num_sms * 8;  // resident 128-thread CTAs per SM at 64 registers/thread
+  // Smallest chunk that keeps every CTA resident in one wave, but at least two items per warp.
+  const uint32_t item_tokens = 2 * (32 / (head_dim / 8));
+  uint32_t min_ppc = (quest::kDecWarps * item_tokens * 2 + page_size - 1) / page_size;
   if (min_ppc == 0) min_ppc = 1;
   uint32_t ppc = min_ppc;
   while (ppc < total && (uint64_t)num_qo_heads * ((total + ppc - 1) / ppc) > slots) ++ppc;

@@ -68,6 +68,25 @@ __global__ void __launch_bounds__(256) k_ldg_persist(const uint4* __restrict__ s
   if (a == 0x12345678u) *sink = a;
 }
 
+template <int U, int THREADS, int PDL>
+__global__ void __launch_bounds__(THREADS) k_ldg_persist2(const uint4* __restrict__ src, size_t nvec, uint32_t* sink) {
+  uint32_t a = 0;
+  if (PDL) asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (PDL == 2) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  for (size_t base = (size_t)blockIdx.x * THREADS * U + threadIdx.x; base < nvec; base += (size_t)gridDim.x * THREADS * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      size_t i = base + (size_t)u * THREADS;
+      v[u] = make_uint4(0, 0, 0, 0);
+      if (i < nvec) asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(src + i));
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) a ^= v[u].x ^ v[u].y ^ v[u].z ^ v[u].w;
+  }
+  if (a == 0x12345678u) *sink = a;
+}
+
 // ---------------------------------------------------------------------------------------------- ring kernels
 // Unit list: each unit is `unit_bytes` landing in one ring stage.  mode 0: 1-D bulk from src + off[u];
 // mode 1: one TMA 2-D box at (c0,c1) = (colrow[2u], colrow[2u+1]); mode 2: 32 row copies of 256 B at
@@ -77,13 +96,13 @@ struct RingArgs {
   const uint8_t* src;
   const uint64_t* off;
   const int32_t* colrow;
-  uint32_t n_units, unit_bytes, stages, mode, blocked, row_stride;
+  uint32_t n_units, unit_bytes, stages, mode, blocked, row_stride, poll1;
 };
 
 __global__ void __launch_bounds__(288) k_ring(const __grid_constant__ CUtensorMap map, RingArgs a, uint32_t* sink) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-  uint64_t* empty = full + 16;
+  uint64_t* empty = full + 32;
   uint8_t* data = smem + 1024;
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t ncons_warps = (blockDim.x >> 5) - 1;
@@ -120,7 +139,7 @@ __global__ void __launch_bounds__(288) k_ring(const __grid_constant__ CUtensorMa
     uint32_t s = 0, ph = 0, acc = 0;
     const uint32_t nthr = ncons_warps * 32;
     for (uint32_t u = u0; u < u1; u += ustep) {
-      mbar_wait(full + s, ph);
+      if (a.poll1) { if (lane == 0) mbar_wait(full + s, ph); __syncwarp(); } else mbar_wait(full + s, ph);
       const uint4* p = reinterpret_cast<const uint4*>(data + (size_t)s * a.unit_bytes);
       for (uint32_t i = tid; i < a.unit_bytes / 16; i += nthr) { uint4 v = p[i]; acc ^= v.x ^ v.y ^ v.z ^ v.w; }
       __syncwarp();
@@ -154,6 +173,7 @@ __global__ void __launch_bounds__(128) k_gather_ldg(const uint8_t* __restrict__ 
   if (a == 0x12345678u) *sink = a;
 }
 
+static uint32_t g_poll1 = 0;
 typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 int main(int argc, char** argv) {
@@ -206,14 +226,14 @@ int main(int argc, char** argv) {
     CK(cudaMemcpy(d_off, off.data(), off.size() * 8, cudaMemcpyHostToDevice));
     if (!cr.empty()) CK(cudaMemcpy(d_cr, cr.data(), cr.size() * 4, cudaMemcpyHostToDevice));
     size_t smem = 1024 + (size_t)unit_bytes * stages;
-    RingArgs a; a.off = d_off; a.colrow = d_cr; a.n_units = (uint32_t)off.size(); a.unit_bytes = unit_bytes; a.stages = stages; a.mode = mode; a.blocked = blocked; a.row_stride = (uint32_t)ROWB;
+    RingArgs a; a.off = d_off; a.colrow = d_cr; a.n_units = (uint32_t)off.size(); a.unit_bytes = unit_bytes; a.stages = stages; a.mode = mode; a.blocked = blocked; a.row_stride = (uint32_t)ROWB; a.poll1 = g_poll1;
     for (int w = 0; w < 3; ++w) { a.src = d + (w % NBUF) * BUF; k_ring<<<grid, threads, smem, st>>>(maps[w % NBUF], a, sink); }
     CK(cudaGetLastError());
     CK(cudaEventRecord(e0, st));
     for (int i = 0; i < ITERS; ++i) { a.src = d + (i % NBUF) * BUF; k_ring<<<grid, threads, smem, st>>>(maps[i % NBUF], a, sink); }
     CK(cudaEventRecord(e1, st)); CK(cudaEventSynchronize(e1)); CK(cudaGetLastError());
     float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
-    char nm[128]; snprintf(nm, 128, "%s unit=%uK st=%u grid=%d thr=%d %s", name, unit_bytes / 1024, stages, grid, threads, blocked ? "blocked" : "rr");
+    char nm[128]; snprintf(nm, 128, "%s unit=%uK st=%u grid=%d thr=%d %s poll1=%d", name, unit_bytes / 1024, stages, grid, threads, blocked ? "blocked" : "rr", g_poll1);
     report(nm, (size_t)unit_bytes * off.size(), ms);
   };
   std::vector<int32_t> nocr;
@@ -259,6 +279,54 @@ int main(int argc, char** argv) {
     CK(cudaEventRecord(e1, st)); CK(cudaEventSynchronize(e1)); float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); char nm[96]; snprintf(nm, 96, "gather LDG U=%d units/cta=%d grid=%d", U, UPC, grid); report(nm, (size_t)n * 8192, ms); }
     RUN_GLDG(8, 2) RUN_GLDG(8, 4) RUN_GLDG(16, 4) RUN_GLDG(16, 8) RUN_GLDG(8, 8)
   }
+  // ---- second batch: ring with single-lane polling, deeper rings
+  g_poll1 = 1;
+  { std::vector<uint64_t> off; for (size_t o = 0; o + 8192 <= META; o += 8192) off.push_back(o);
+    run_ring("contig bulk1d", off, nocr, 8192, 16, 0, 0, sms, 288);
+    run_ring("contig bulk1d", off, nocr, 8192, 24, 0, 0, sms, 288);
+    run_ring("contig bulk1d", off, nocr, 8192, 24, 0, 1, sms, 288);
+    run_ring("contig bulk1d", off, nocr, 8192, 12, 0, 0, sms * 2, 288);
+    run_ring("contig bulk1d", off, nocr, 8192, 12, 0, 0, sms * 2, 160);
+    run_ring("contig bulk1d", off, nocr, 8192, 6, 0, 0, sms * 4, 160); }
+  { std::vector<uint64_t> off; for (size_t o = 0; o + 16384 <= META; o += 16384) off.push_back(o);
+    run_ring("contig bulk1d", off, nocr, 16384, 12, 0, 0, sms, 288);
+    run_ring("contig bulk1d", off, nocr, 16384, 6, 0, 0, sms * 2, 288); }
+  g_poll1 = 0;
+  // ---- persistent LDG with big CTAs; stream launches, then CUDA graph chains with / without PDL
+#define RUN_P2(U, T, GRID) { size_t nvec = META / 16; \
+    for (int w = 0; w < 3; ++w) k_ldg_persist2<U, T, 0><<<GRID, T, 0, st>>>((const uint4*)(d + (w % NBUF) * BUF), nvec, sink); \
+    CK(cudaEventRecord(e0, st)); for (int i = 0; i < ITERS; ++i) k_ldg_persist2<U, T, 0><<<GRID, T, 0, st>>>((const uint4*)(d + (i % NBUF) * BUF), nvec, sink); \
+    CK(cudaEventRecord(e1, st)); CK(cudaEventSynchronize(e1)); float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); char nm[96]; snprintf(nm, 96, "contig LDG persistent2 U=%d thr=%d grid=%d", U, T, GRID); report(nm, META, ms); }
+  RUN_P2(8, 1024, sms) RUN_P2(4, 1024, sms) RUN_P2(8, 512, sms * 2) RUN_P2(4, 512, sms * 2) RUN_P2(4, 512, sms * 4) RUN_P2(8, 256, sms * 4) RUN_P2(4, 256, sms * 8)
+  // graph chains: 32 kernels per graph, each streaming a different buffer
+#define RUN_GRAPH(PDL, NAME) { size_t nvec = META / 16; cudaGraph_t g; cudaGraphExec_t ge; \
+    CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal)); \
+    for (int i = 0; i < 32; ++i) { cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(sms * 4); cfg.blockDim = dim3(256); cfg.stream = st; \
+      cudaLaunchAttribute at[1]; at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1; \
+      cfg.attrs = at; cfg.numAttrs = PDL ? 1 : 0; const uint4* sp = (const uint4*)(d + (i % NBUF) * BUF); \
+      CK(cudaLaunchKernelEx(&cfg, k_ldg_persist2<8, 256, PDL>, sp, nvec, sink)); } \
+    CK(cudaStreamEndCapture(st, &g)); CK(cudaGraphInstantiate(&ge, g, 0)); \
+    for (int w = 0; w < 3; ++w) CK(cudaGraphLaunch(ge, st)); \
+    CK(cudaEventRecord(e0, st)); for (int i = 0; i < 10; ++i) CK(cudaGraphLaunch(ge, st)); \
+    CK(cudaEventRecord(e1, st)); CK(cudaEventSynchronize(e1)); float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); \
+    printf("%-64s %8.2f us  %8.1f GB/s\n", NAME, ms * 1e3 / 320, META / (ms / 320 * 1e-3) / 1e9); }
+  RUN_GRAPH(0, "graph chain x32, plain edges, LDG persistent U=8 4 ctas/sm")
+  RUN_GRAPH(1, "graph chain x32, PDL edges (wait at top)")
+  RUN_GRAPH(2, "graph chain x32, PDL edges (wait + early trigger)")
+#define RUN_GRAPH_TINY(PDL, NAME) { cudaGraph_t g; cudaGraphExec_t ge; \
+    CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal)); \
+    for (int i = 0; i < 32; ++i) { cudaLaunchConfig_t cfg = {}; cfg.gridDim = dim3(32); cfg.blockDim = dim3(256); cfg.stream = st; \
+      cudaLaunchAttribute at[1]; at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1; \
+      cfg.attrs = at; cfg.numAttrs = PDL ? 1 : 0; const uint4* sp = (const uint4*)(d + (i % NBUF) * BUF); \
+      CK(cudaLaunchKernelEx(&cfg, k_ldg_persist2<1, 256, PDL>, sp, (size_t)8192, sink)); } \
+    CK(cudaStreamEndCapture(st, &g)); CK(cudaGraphInstantiate(&ge, g, 0)); \
+    for (int w = 0; w < 3; ++w) CK(cudaGraphLaunch(ge, st)); \
+    CK(cudaEventRecord(e0, st)); for (int i = 0; i < 10; ++i) CK(cudaGraphLaunch(ge, st)); \
+    CK(cudaEventRecord(e1, st)); CK(cudaEventSynchronize(e1)); float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); \
+    printf("%-64s %8.2f us per kernel\n", NAME, ms * 1e3 / 320); }
+  RUN_GRAPH_TINY(0, "graph chain x32 of tiny kernels (128 KB read), plain edges")
+  RUN_GRAPH_TINY(1, "graph chain x32 of tiny kernels, PDL wait at top")
+  RUN_GRAPH_TINY(2, "graph chain x32 of tiny kernels, PDL wait + trigger")
   // launch floor: empty-ish kernel
   { std::vector<uint64_t> off(1, 0); run_ring("launch floor (1 unit)", off, nocr, 8192, 2, 0, 0, 1, 288); }
   printf("done\n");
