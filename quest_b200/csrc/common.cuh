@@ -25,6 +25,14 @@ __device__ __forceinline__ H8 ld_stream(const void* p) {
                : "l"(p));
   return r;
 }
+// Predicated form: r keeps its previous contents when !pred (no memory access is made).
+__device__ __forceinline__ void ld_stream_if(H8& r, const void* p, bool pred) {
+  uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.u32 p, %5, 0;\n@p ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];\n}"
+      : "+r"(u[0]), "+r"(u[1]), "+r"(u[2]), "+r"(u[3])
+      : "l"(p), "r"((uint32_t)pred));
+}
 __device__ __forceinline__ H8 ld_plain(const void* p) { return *reinterpret_cast<const H8*>(p); }
 __device__ __forceinline__ void st_plain(void* p, const H8& v) { *reinterpret_cast<H8*>(p) = v; }
 

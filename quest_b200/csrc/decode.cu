@@ -32,7 +32,7 @@ __device__ __forceinline__ uint32_t div_p(uint32_t t, uint32_t p_magic) { return
 // the next item's loads issued before the current item is consumed: 8 independent 128-bit loads per lane
 // stay in flight, ~128 KB per SM at 8 CTAs/SM, and the softmax arithmetic hides under them.
 template <int D>
-__global__ void __launch_bounds__(kDecThreads, 8)
+__global__ void __launch_bounds__(kDecThreads, 7)
 decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __restrict__ lse,
               const __half* __restrict__ kv, const int32_t* __restrict__ indices, uint32_t idx_stride,
               uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len, uint32_t Hkv, uint32_t G,
@@ -75,41 +75,59 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
   for (int i = 0; i < 8; ++i) acc[i] = 0.f;
   float m = kNegBig, d = 0.f;
 
+  // Branch-free inner loop.  This lane group's token in sub-load j of the item being issued is kept as
+  // (local page, entry) and advanced by the item stride without divisions; validity of the 2x2 loads in
+  // flight is remembered in okm (bit 2*stage + j).  Invalid rows are not loaded (predicated) and enter the
+  // softmax with weight 0; their stale registers always hold finite halves.
   H8 kk[2][2], vv[2][2];
-  auto tok_ok = [&](uint32_t t, uint32_t& pgl, uint32_t& e) {
-    pgl = div_p(t, p_magic);
-    e = t - pgl * P;
-    return t < ntok && (pg0 + pgl < n_sel || e < last_page_len);
-  };
-  auto issue = [&](int st, uint32_t it) {
+#pragma unroll
+  for (int st = 0; st < 2; ++st)
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) kk[st][j].h[i] = vv[st][j].h[i] = __half2half2(__ushort_as_half(0));
+  const uint32_t S = kDecWarps * IT;  // tokens between consecutive items of one warp
+  const uint32_t dpg = div_p(S, p_magic), de = S - dpg * P;
+  uint32_t pgl[2], en[2], okm = 0;
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const uint32_t t = warp * IT + j * TPL + sub;
+    pgl[j] = div_p(t, p_magic);
+    en[j] = t - pgl[j] * P;
+  }
+  const uint32_t row_bytes = Hkv * D * 2, page_bytes = 2 * P * row_bytes, slab_bytes = P * row_bytes;
+  const uint8_t* kvb = reinterpret_cast<const uint8_t*>(kv) + (size_t)kvh * D * 2 + lir * 16;
+  const uint32_t n_sel_local = n_sel > pg0 ? n_sel - pg0 : 0;  // local pages below this are selected (full) pages
+  auto issue = [&](int st) {
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      uint32_t pgl, e;
-      if (it < n_items && tok_ok(it * IT + j * TPL + sub, pgl, e)) {
-        const __half* kp = kv + (((size_t)s_pages[pgl] * 2) * P + e) * row + (size_t)kvh * D + lir * 8;
-        kk[st][j] = ld_stream(kp);
-        vv[st][j] = ld_stream(kp + slab);
+      const bool ok = pgl[j] < npg && (pgl[j] < n_sel_local || en[j] < last_page_len);
+      const uint32_t page = (uint32_t)s_pages[min(pgl[j], npg - 1)];
+      const uint8_t* kp = kvb + (uint64_t)page * page_bytes + en[j] * row_bytes;
+      ld_stream_if(kk[st][j], kp, ok);
+      ld_stream_if(vv[st][j], kp + slab_bytes, ok);
+      okm = (okm & ~(1u << (2 * st + j))) | ((uint32_t)ok << (2 * st + j));
+      pgl[j] += dpg;
+      en[j] += de;
+      if (en[j] >= P) {
+        en[j] -= P;
+        ++pgl[j];
       }
     }
   };
-  auto consume = [&](int st, uint32_t it) {
+  auto consume = [&](int st) {
     float sc[2];
-    bool ok[2];
     float mt = m;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      uint32_t pgl, e;
-      ok[j] = tok_ok(it * IT + j * TPL + sub, pgl, e);
+      float kf[8];
+      h8_to_float(kk[st][j], kf);
       float a = 0.f;
-      if (ok[j]) {
-        float kf[8];
-        h8_to_float(kk[st][j], kf);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) a = fmaf(qv[i], kf[i], a);
-      }
+      for (int i = 0; i < 8; ++i) a = fmaf(qv[i], kf[i], a);
 #pragma unroll
       for (int off = LPR / 2; off > 0; off >>= 1) a += __shfl_xor_sync(0xffffffffu, a, off);
-      sc[j] = ok[j] ? a : kNegBig;
+      sc[j] = (okm >> (2 * st + j)) & 1u ? a : kNegBig;
       mt = fmaxf(mt, sc[j]);
     }
     const float scale = ex2(m - mt);
@@ -119,26 +137,22 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     for (int i = 0; i < 8; ++i) acc[i] *= scale;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      if (ok[j]) {
-        const float p = ex2(sc[j] - m);
-        d += p;
-        float vf[8];
-        h8_to_float(vv[st][j], vf);
+      const float p = (okm >> (2 * st + j)) & 1u ? ex2(sc[j] - m) : 0.f;
+      d += p;
+      float vf[8];
+      h8_to_float(vv[st][j], vf);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] = fmaf(p, vf[i], acc[i]);
-      }
+      for (int i = 0; i < 8; ++i) acc[i] = fmaf(p, vf[i], acc[i]);
     }
   };
-  // warp-uniform trip count (the shuffles use the full mask); out-of-range tokens are masked
-  issue(0, warp);
-  issue(1, warp + kDecWarps);
+  // warp-uniform trip count (the shuffles use the full mask)
+  issue(0);
+  issue(1);
   for (uint32_t it = warp; it < n_items; it += 2 * kDecWarps) {
-    consume(0, it);
-    issue(0, it + 2 * kDecWarps);
-    if (it + kDecWarps < n_items) {
-      consume(1, it + kDecWarps);
-      issue(1, it + 3 * kDecWarps);
-    }
+    consume(0);
+    issue(0);
+    consume(1);
+    issue(1);
   }
 
   // CTA merge of the NG group states.
@@ -252,7 +266,7 @@ extern "C" int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, 
   if (head_dim != 64 && head_dim != 128 && head_dim != 256) return QUEST_ERR_UNSUPPORTED;
   if (num_sms == 0) num_sms = 148;
   const uint32_t total = num_sel_pages + 1;
-  const uint32_t slots = num_sms * 8;  // resident 128-thread CTAs per SM at 64 registers/thread
+  const uint32_t slots = num_sms * 7;  // resident 128-thread CTAs per SM at 72 registers/thread
   // Smallest chunk that keeps every CTA resident in one wave, but at least two items per warp.
   const uint32_t item_tokens = 2 * (32 / (head_dim / 8));
   uint32_t min_ppc = (quest::kDecWarps * item_tokens * 2 + page_size - 1) / page_size;

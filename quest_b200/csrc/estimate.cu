@@ -20,65 +20,53 @@
 
 namespace quest {
 
-template <int D, int kEstThreads, int kEstDepth>
+// n / d for n < 2^24 and any d >= 1: m = ceil(2^40 / d); exact while n * d < 2^40.
+__host__ __device__ inline uint64_t div40_magic(uint32_t d) { return ((1ull << 40) + d - 1) / d; }
+__device__ __forceinline__ uint32_t div40(uint32_t n, uint64_t m) { return (uint32_t)(((uint64_t)n * m) >> 40); }
+
+template <int D, int kEstThreads, int kEstDepth, int kG>
 __global__ void __launch_bounds__(kEstThreads, 2)
 estimate_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t len,
                 const __half* __restrict__ meta, const int32_t* __restrict__ meta_indices,
-                uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t n_meta_smem, uint32_t meta_stable) {
+                uint32_t Hq, uint32_t Hkv, uint32_t P, uint64_t magic_mp /* 1/(P*Hkv) */,
+                uint64_t magic_h /* 1/Hkv */, uint32_t meta_stable) {
   constexpr int LPR = D / 8;     // lanes per metadata row (reference bdx)
   constexpr int RPL = 32 / LPR;  // rows per warp-wide load
   extern __shared__ __align__(16) uint8_t est_smem[];
   float* q_s = reinterpret_cast<float*>(est_smem);                          // [Hq][D] fp32
   uint32_t* m_s = reinterpret_cast<uint32_t*>(q_s + (size_t)Hq * D);        // [Hq][D/2] 0xffff where q >= 0
-  int32_t* idx_s = reinterpret_cast<int32_t*>(m_s + (size_t)Hq * D / 2);    // [n_meta_smem] metadata page table
-  const uint32_t G = Hq / Hkv;
+  int32_t* idx_s = reinterpret_cast<int32_t*>(m_s + (size_t)Hq * D / 2);    // [ceil(len/P)] metadata page table
+  const uint32_t G = kG ? kG : Hq / Hkv;  // kG = 0: any group size
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lir = lane % LPR, rsub = lane / LPR;
   const uint32_t total_rows = len * Hkv;
-  const uint32_t total_items = (total_rows + RPL - 1) / RPL;
   const uint32_t n_warps = gridDim.x * (kEstThreads / 32);
-  const uint32_t w_global = warp * gridDim.x + blockIdx.x;  // warps of one CTA are gridDim.x items apart
-  const size_t slab = (size_t)P * Hkv * D;
+  const uint32_t step_rows = n_warps * RPL;
+  const uint32_t rows_per_mp = P * Hkv;                       // rows of one metadata page's max slab
+  const uint32_t slab_bytes = rows_per_mp * D * 2;            // max slab -> min slab
+  const uint64_t mp_bytes = 2ull * slab_bytes;                // one metadata page
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + lir * 16;
 
   // In the layer step the kernel that precedes this one (append) only touches the metadata entry of the
   // last page, which is never scored: with meta_stable the pipeline is primed before the
   // programmatic-dependency wait (q is only read after it).  Otherwise wait first.
   if (!meta_stable) pdl_wait();
   const uint32_t n_meta = (len + P - 1) / P;
-  for (uint32_t i = tid; i < n_meta && i < n_meta_smem; i += kEstThreads) idx_s[i] = __ldg(meta_indices + i);
+  for (uint32_t i = tid; i < n_meta; i += kEstThreads) idx_s[i] = __ldg(meta_indices + i);
   __syncthreads();
 
-  // incremental (page, kv head, metadata page, entry) of this lane's row, advanced by n_warps*RPL rows per item
-  const uint32_t step_rows = n_warps * RPL;
-  const uint32_t dp = step_rows / Hkv, dh = step_rows % Hkv;
-  const uint32_t dmp = dp / P, de = dp % P;
-  uint32_t r = w_global * RPL + rsub;
-  uint32_t p = r / Hkv, kvh = r % Hkv, mp = p / P, e = p % P;
-
+  // warps of one CTA are gridDim.x items apart, so neighbouring CTAs stream neighbouring 512-byte runs
+  uint32_t r_ld = (warp * gridDim.x + blockIdx.x) * RPL + rsub;  // this lane's row in the next item to load
+  uint32_t r = r_ld;                                             // ... and in the next item to consume
   H8 mx[kEstDepth], mn[kEstDepth];
-  uint32_t ld_p = p, ld_kvh = kvh, ld_mp = mp, ld_e = e, ld_r = r;
   auto issue = [&](int s) {
-    if (ld_r < total_rows) {
-      const size_t page = (size_t)(ld_mp < n_meta_smem ? idx_s[ld_mp] : __ldg(meta_indices + ld_mp));
-      const __half* a = meta + nhd_off(page, 0, ld_e, ld_kvh, P, Hkv, D) + lir * 8;
-      mx[s] = ld_stream(a);
-      mn[s] = ld_stream(a + slab);
-    }
-    // advance to this lane's row in the next item
-    ld_r += step_rows;
-    ld_kvh += dh;
-    uint32_t carry = 0;
-    if (ld_kvh >= Hkv) {
-      ld_kvh -= Hkv;
-      carry = 1;
-    }
-    ld_p += dp + carry;
-    ld_e += de + carry;
-    ld_mp += dmp;
-    while (ld_e >= P) {
-      ld_e -= P;
-      ++ld_mp;
-    }
+    const uint32_t rc = min(r_ld, total_rows - 1);  // past the end: re-read the last row (never stored)
+    const uint32_t mp = div40(rc, magic_mp);
+    const uint32_t within = rc - mp * rows_per_mp;
+    const uint8_t* a = base + (uint64_t)(uint32_t)idx_s[mp] * mp_bytes + within * (uint32_t)(D * 2);
+    mx[s] = ld_stream(a);
+    mn[s] = ld_stream(a + slab_bytes);
+    r_ld += step_rows;
   };
 #pragma unroll
   for (int s = 0; s < kEstDepth; ++s) issue(s);
@@ -89,43 +77,34 @@ estimate_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t l
     const float2 f = __half22float2(h2);
     q_s[2 * i] = f.x;
     q_s[2 * i + 1] = f.y;
-    // sign-bit test so that -0 selects like the reference's fmaxf on (+-0) products: either choice sums alike
+    // sign-bit test: for q = -0 either choice gives a +-0 product, which cannot change the sum
     const uint32_t bits = *reinterpret_cast<const uint32_t*>(&h2);
     m_s[i] = ((bits & 0x8000u) ? 0u : 0xffffu) | ((bits & 0x80000000u) ? 0u : 0xffff0000u);
   }
   __syncthreads();
   pdl_trigger();
 
-  for (uint32_t it = w_global; it < total_items; it += n_warps * kEstDepth) {
+
+  while (r - rsub < total_rows) {
 #pragma unroll
     for (int s = 0; s < kEstDepth; ++s) {
-      const bool valid = r < total_rows;  // uniform over the LPR lanes of a row
       uint32_t hi[4], lo[4];
-      if (valid) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const __half2 a = __hmax2(mx[s].h[i], mn[s].h[i]);
-          const __half2 b = __hmin2(mx[s].h[i], mn[s].h[i]);
-          hi[i] = *reinterpret_cast<const uint32_t*>(&a);
-          lo[i] = *reinterpret_cast<const uint32_t*>(&b);
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) hi[i] = lo[i] = 0;
+      for (int i = 0; i < 4; ++i) {
+        const __half2 a = __hmax2(mx[s].h[i], mn[s].h[i]);
+        const __half2 b = __hmin2(mx[s].h[i], mn[s].h[i]);
+        hi[i] = *reinterpret_cast<const uint32_t*>(&a);
+        lo[i] = *reinterpret_cast<const uint32_t*>(&b);
       }
-      const uint32_t cur_p = p, cur_kvh = kvh;
       issue(s);  // refill this stage with the item kEstDepth ahead
+      const bool valid = r < total_rows;  // uniform over the LPR lanes of a row
+      const uint32_t rc = min(r, total_rows - 1);
+      const uint32_t p = div40(rc, magic_h);
+      const uint32_t kvh = rc - p * Hkv;
       r += step_rows;
-      kvh += dh;
-      uint32_t carry = 0;
-      if (kvh >= Hkv) {
-        kvh -= Hkv;
-        carry = 1;
-      }
-      p += dp + carry;
-
+#pragma unroll
       for (uint32_t g = 0; g < G; ++g) {
-        const uint32_t h = cur_kvh * G + g;
+        const uint32_t h = kvh * G + g;
         const float4* qp = reinterpret_cast<const float4*>(q_s + h * D + lir * 8);
         const float4 q0 = qp[0], q1 = qp[1];
         const uint4 msk = *reinterpret_cast<const uint4*>(m_s + h * (D / 2) + lir * 4);
@@ -142,10 +121,11 @@ estimate_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t l
         }
 #pragma unroll
         for (int off = LPR / 2; off > 0; off >>= 1) sacc = __fadd_rn(sacc, __shfl_xor_sync(0xffffffffu, sacc, off));
-        if (valid && lir == 0) o[(size_t)h * len + cur_p] = __float2half_rn(sacc);
+        if (valid && lir == 0) o[(size_t)h * len + p] = __float2half_rn(sacc);
       }
     }
   }
+
 }
 
 template <int D, int kEstThreads, int kEstDepth>
@@ -166,9 +146,11 @@ static int launch_estimate(const void* q, void* o, uint32_t len, const void* met
   const uint32_t need = (total_items + warps_per_cta - 1) / warps_per_cta;
   if (grid > need) grid = need;
   const uint32_t n_meta = (len + P - 1) / P;
-  const uint32_t n_meta_smem = n_meta < 8192 ? n_meta : 8192;
-  const size_t smem = (size_t)Hq * D * sizeof(float) + (size_t)Hq * D / 2 * sizeof(uint32_t) + (size_t)n_meta_smem * 4;
-  auto kern = estimate_kernel<D, kEstThreads, kEstDepth>;
+  const size_t smem = (size_t)Hq * D * sizeof(float) + (size_t)Hq * D / 2 * sizeof(uint32_t) + (size_t)n_meta * 4;
+  if (smem > 100 * 1024 || (uint64_t)len * Hkv >= (1u << 24)) return QUEST_ERR_UNSUPPORTED;
+  const uint32_t G = Hq / Hkv;
+  auto kern = G == 1 ? estimate_kernel<D, kEstThreads, kEstDepth, 1> : G == 4 ? estimate_kernel<D, kEstThreads, kEstDepth, 4>
+                                                                       : estimate_kernel<D, kEstThreads, kEstDepth, 0>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -184,7 +166,8 @@ static int launch_estimate(const void* q, void* o, uint32_t len, const void* met
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta,
-                                     meta_indices, Hq, Hkv, P, n_meta_smem, flags & QUEST_EST_META_STABLE);
+                                     meta_indices, Hq, Hkv, P, div40_magic(P * Hkv), div40_magic(Hkv),
+                                     flags & QUEST_EST_META_STABLE);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }

@@ -22,7 +22,7 @@ __device__ __forceinline__ void group_bar(uint32_t id, uint32_t nthreads) {
 
 template <int W>
 struct TopkScratch {
-  uint32_t hist[2][W][16];
+  uint32_t hist[2][W][8];  // per warp: 16 bins as packed 16-bit pairs
   uint32_t wgt[W], weq[W];
 };
 
@@ -39,6 +39,14 @@ __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, ui
   const uint32_t cpt = (n8 + T - 1) / T;            // chunks per thread (blocked ownership)
   const uint32_t c0 = min(t * cpt, n8), c1 = min(c0 + cpt, n8);
   const uint4* kv = reinterpret_cast<const uint4*>(keys);
+
+  // payload ids of this thread's slice, fetched now so the compaction does not wait on them
+  const bool pre = in_idx != nullptr && cpt == 1;
+  int32_t pay[8];
+  if (pre) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) pay[j] = c0 * 8 + j < n ? __ldg(in_idx + c0 * 8 + j) : 0;
+  }
 
   uint32_t prefix = 0, kk = k;
 #pragma unroll 1
@@ -61,19 +69,20 @@ __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, ui
         cw3 += q == 3 ? inc : 0ull;
       }
     }
+    // warp totals: the packed 16-bit fields add without carries (a warp sees < 65536 keys), so 8 REDUX do 16 bins
     uint32_t mine = 0;
 #pragma unroll
-    for (int b = 0; b < 16; ++b) {
-      const uint64_t cw = (b >> 2) == 0 ? cw0 : (b >> 2) == 1 ? cw1 : (b >> 2) == 2 ? cw2 : cw3;
-      const uint32_t tot = __reduce_add_sync(0xffffffffu, (uint32_t)(cw >> ((b & 3) * 16)) & 0xffffu);
-      if (lane == (uint32_t)b) mine = tot;
+    for (int x = 0; x < 8; ++x) {
+      const uint64_t cw = (x >> 1) == 0 ? cw0 : (x >> 1) == 1 ? cw1 : (x >> 1) == 2 ? cw2 : cw3;
+      const uint32_t tot = __reduce_add_sync(0xffffffffu, (uint32_t)(cw >> ((x & 1) * 32)));
+      if (lane == (uint32_t)x) mine = tot;
     }
-    if (lane < 16) sc->hist[pass & 1][warp][lane] = mine;
+    if (lane < 8) sc->hist[pass & 1][warp][lane] = mine;  // word x = bins 2x (low half), 2x+1 (high half)
     group_bar(bar_id, T);
     uint32_t s = 0;
     if (lane < 16) {
 #pragma unroll
-      for (int w2 = 0; w2 < W; ++w2) s += sc->hist[pass & 1][w2][lane];
+      for (int w2 = 0; w2 < W; ++w2) s += (sc->hist[pass & 1][w2][lane >> 1] >> ((lane & 1) * 16)) & 0xffffu;
     }
     // above = sum of bins higher than mine (lanes 16..31 carry zeros)
     uint32_t suf = s;
@@ -137,7 +146,7 @@ __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, ui
       const bool gt = in && key > tau, eq = in && key == tau;
       if (gt || (eq && eq_before < need)) {
         const uint32_t pos = gt_before + min(eq_before, need);
-        out_idx[pos] = in_idx ? __ldg(in_idx + i) : (int32_t)i;
+        out_idx[pos] = pre ? pay[j] : in_idx ? __ldg(in_idx + i) : (int32_t)i;
         if (out_val) out_val[pos] = half_of((uint16_t)key);
       }
       gt_before += gt;

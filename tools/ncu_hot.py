@@ -6,7 +6,8 @@ n = int(sys.argv[3]) if len(sys.argv) > 3 else 25
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kern, "--launch-skip", "0", "--launch-count", "1"], capture_output=True, text=True).stdout
 lines = out.splitlines()
 start = next(i for i, l in enumerate(lines) if l.startswith('"Address"'))
-rows = list(csv.DictReader(io.StringIO("\n".join(lines[start:]))))
+end = next((i for i, l in enumerate(lines) if i > start and l.startswith('"Kernel Name"')), len(lines))
+rows = list(csv.DictReader(io.StringIO("\n".join(lines[start:end]))))
 tot = sum(int(r["# Samples"] or 0) for r in rows)
 print("total samples", tot, "instructions", len(rows))
 stalls = [k for k in rows[0] if k.startswith("stall_") and "Not Issued" not in k]
