@@ -176,7 +176,7 @@ class Workload:
                 calls.append((lib.quest_append_decode, (k, v, kvp, kvi.data_ptr(), N_PAGES, kv_last_len, mp, mi.data_ptr(),
                                                         n_meta, meta_last_len, H, D, P)))
             if "estimate" in parts:
-                calls.append((lib.quest_estimate, (q, s, N_SCORED, mp, mi.data_ptr(), H, H, D, P, 1)))  # 1 = QUEST_EST_META_STABLE
+                calls.append((lib.quest_estimate, (q, s, N_SCORED, mp, mi.data_ptr(), H, H, D, P, 3)))  # QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED
             if "topk" in parts:
                 calls.append((lib.quest_topk, (s, kvi.data_ptr(), 0, None, ti, H, N_SCORED, K_SEL)))
             if "decode" in parts:

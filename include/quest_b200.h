@@ -82,6 +82,9 @@ int quest_append_prefill(const void* k, const void* v, uint32_t append_len,
  * does not write metadata entries [0, len) (true in the layer step: append only touches the last page's
  * entry), which lets the metadata stream start before the programmatic dependency on that kernel resolves. */
 #define QUEST_EST_META_STABLE 1u
+/* QUEST_EST_META_ORDERED promises max >= min elementwise in every scored entry (true for metadata written by
+ * quest_append_*): the per-element max/min pre-pass is skipped; results are identical on such data. */
+#define QUEST_EST_META_ORDERED 2u
 int quest_estimate(const void* q, void* o, uint32_t len,
                    const void* meta_data, const int32_t* meta_indices,
                    uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,

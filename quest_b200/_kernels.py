@@ -147,10 +147,14 @@ def _pool_dims(data, name):
     return data.size(2), data.size(3), data.size(4)  # page_size, heads, head_dim (NHD)
 
 
+EST_META_STABLE, EST_META_ORDERED = 1, 2  # include/quest_b200.h QUEST_EST_*
+
+
 def estimate_attn_score(q, o, metadata_data, metadata_indices, metadata_indptr, metadata_last_page_len,
-                        metadata_last_page_idx, layout):
+                        metadata_last_page_idx, layout, flags=0):
     """reference quest/ops/csrc/estimate.cu:6-84.  Scores the first o.size(1) KV pages (the caller leaves out
-    the last one: quest/utils/__init__.py:193-194)."""
+    the last one: quest/utils/__init__.py:193-194).  flags: promises about the metadata (QUEST_EST_* in
+    include/quest_b200.h); 0 = none, always valid."""
     _check_layout(layout, "estimate_attn_score")
     _check_input(q, "q"), _check_input(metadata_data, "metadata_data"), _check_input(metadata_indices, "metadata_indices")
     _check_input(o, "o")
@@ -166,7 +170,7 @@ def estimate_attn_score(q, o, metadata_data, metadata_indices, metadata_indptr, 
     _check(o.size(1) == n_entries, f"o.size(1) must equal the number of scored pages {n_entries}")
     _check_half(q, "Estimate_attn_score")
     _rc(load_library().quest_estimate(q.data_ptr(), o.data_ptr(), o.size(1), metadata_data.data_ptr(),
-                                      metadata_indices.data_ptr(), Hq, Hkv, D, P, 0, _stream()), "estimate_attn_score")
+                                      metadata_indices.data_ptr(), Hq, Hkv, D, P, int(flags), _stream()), "estimate_attn_score")
 
 
 def _append_checks(k, v, kv_data, kv_indices, kv_indptr, metadata_data, metadata_indices, metadata_indptr, layout, op):

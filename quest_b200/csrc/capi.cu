@@ -31,7 +31,7 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
   if (!kv_indices || !scores || !topk_idx) return QUEST_ERR_BAD_ARG;
   if (k > len) return QUEST_ERR_BAD_ARG;
   int rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                          QUEST_EST_META_STABLE, stream);
+                          QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, stream);
   if (rc) return rc;
   // payload ids = the sequence's page table, shared by all heads (row stride 0)
   rc = quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);

@@ -2,18 +2,24 @@
 // Replaces MaxPossibleSampleWithPagedKVCacheKernel (reference kernels/include/decode/decode_attn.cuh:245-401,
 // inner loop :137-168).
 //
-// HBM-bound stream over the metadata pool, read exactly once.  Persistent warps, each software-pipelined
-// kDepth items deep in registers (an item = one 128-bit load of the max slab + one of the min slab per lane
-// = 32/LPR metadata rows), items interleaved across all warps of the grid so neighbouring warps read
-// neighbouring 512-byte runs.  ~128 KB per SM stay in flight for the whole kernel; the arithmetic of one
-// item hides under the loads of the next kDepth.
+// HBM-bound stream over the metadata pool, read exactly once.  Two kernels:
+//  * estimate_tile_kernel (the product path): a CTA of 16 warps covers 16*32/(D/8) consecutive metadata rows
+//    per pass (for 32 kv heads x 128: one page, all heads = 8 KB contiguous), every lane keeps ONE kv head for
+//    the whole kernel, walks its CTA's contiguous page range through a 4-deep register ring (8 x 128-bit loads
+//    per lane in flight, ~128 KB per SM) and reduces 4 consecutive pages with a transposed butterfly.  About 40
+//    instructions per 1 KB of metadata: the arithmetic hides under the stream (tools/kbench_est.cu measures
+//    the variants that led here; profiles/r01_kbench_est_{a,b,c}.txt).
+//  * estimate_rows_kernel: any shape (kv heads not dividing the tile), same arithmetic, slower addressing.
 //
 // Arithmetic (bit-identical to the reference's fp32 order, 8 sequential adds per lane then an xor butterfly):
 // products of two fp16 values are exact in fp32, and multiplication by q is monotone, so
 //   max(q*kmax, q*kmin) == q * (q >= 0 ? max(kmax,kmin) : min(kmax,kmin))
 // for all finite inputs with no assumption that kmax >= kmin (signed zeros cannot change the running sum,
-// which is never -0).  The select runs on packed halves (HMNMX2 + one LOP3 per pair against a per-head sign
-// mask staged in shared memory), and s + q*x is one FFMA because the product is exact.
+// which is never -0).  The select runs on packed halves (one LOP3 per pair against a sign mask), and
+// s + q*x is one FFMA because the product is exact.  With QUEST_EST_META_ORDERED the caller promises
+// kmax >= kmin elementwise (true for metadata written by append_kv) and the HMNMX2 pair is skipped.
+// The transposed butterfly adds the same operand pairs in the same order as the reference's
+// shfl_xor(8,4,2,1) tree (own + partner at every level), so the fp32 sum is unchanged.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -26,7 +32,7 @@ __device__ __forceinline__ uint32_t div40(uint32_t n, uint64_t m) { return (uint
 
 template <int D, int kEstThreads, int kEstDepth, int kG>
 __global__ void __launch_bounds__(kEstThreads, 2)
-estimate_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t len,
+estimate_rows_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t len,
                 const __half* __restrict__ meta, const int32_t* __restrict__ meta_indices,
                 uint32_t Hq, uint32_t Hkv, uint32_t P, uint64_t magic_mp /* 1/(P*Hkv) */,
                 uint64_t magic_h /* 1/Hkv */, uint32_t meta_stable) {
@@ -128,6 +134,214 @@ estimate_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t l
 
 }
 
+// ---- tile kernel -------------------------------------------------------------------------------------------
+constexpr int kTileWarps = 16;
+
+// Transposed butterfly over the LPR lanes of a row group: 4 per-lane partial sums (rows a[0..3]) -> the lane
+// holds the complete sum of row (lir / (LPR/4)).  Same operand pairs and order as xor(LPR/2 .. 1) on each row.
+template <int LPR>
+__device__ __forceinline__ float reduce4_transposed(const float a[4], uint32_t lir) {
+  const bool b_hi = lir & (LPR / 2), b_lo = lir & (LPR / 4);
+  const float s0 = b_hi ? a[0] : a[2], s1 = b_hi ? a[1] : a[3];
+  const float k0 = b_hi ? a[2] : a[0], k1 = b_hi ? a[3] : a[1];
+  const float r0 = __fadd_rn(k0, __shfl_xor_sync(0xffffffffu, s0, LPR / 2));
+  const float r1 = __fadd_rn(k1, __shfl_xor_sync(0xffffffffu, s1, LPR / 2));
+  const float sd = b_lo ? r0 : r1, kp = b_lo ? r1 : r0;
+  float v = __fadd_rn(kp, __shfl_xor_sync(0xffffffffu, sd, LPR / 4));
+#pragma unroll
+  for (int off = LPR / 8; off > 0; off >>= 1) v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, off));
+  return v;
+}
+
+// kG = 1: MHA, q and sign mask of the lane's head live in registers.  kG = 0: any group size, q/mask in smem.
+template <int D, int kOrdered, int kG>
+__global__ void __launch_bounds__(kTileWarps * 32, 2)
+estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t len,
+                     const __half* __restrict__ meta, const int32_t* __restrict__ meta_indices,
+                     uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_magic /* ceil(2^32/P), 0 for P=1 */,
+                     uint32_t meta_stable) {
+  constexpr int LPR = D / 8, RPL = 32 / LPR, kThreads = kTileWarps * 32, kDepth = 4;
+  constexpr uint32_t T_r = kTileWarps * RPL;  // metadata rows per CTA pass; Hkv divides T_r
+  extern __shared__ __align__(16) uint8_t est_smem[];
+  int32_t* idx_s = reinterpret_cast<int32_t*>(est_smem);                       // [ceil(len/P)]
+  const uint32_t n_meta = (len + P - 1) / P;
+  float* q_s = reinterpret_cast<float*>(est_smem + (((size_t)n_meta * 4 + 15) & ~(size_t)15));  // kG == 0 only
+  uint32_t* m_s = reinterpret_cast<uint32_t*>(q_s + (size_t)Hq * D);
+  const uint32_t G = kG ? kG : Hq / Hkv;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t lir = lane % LPR, rsub = lane / LPR;
+  const uint32_t PPP = T_r / Hkv;                       // pages per CTA pass
+  const uint32_t rt = warp * RPL + rsub;                // this lane's row in the pass
+  const uint32_t pg_in = rt / Hkv, kvh = rt - pg_in * Hkv;
+  // contiguous page range of this CTA, balanced to one page
+  const uint32_t p_begin = (uint32_t)(((uint64_t)blockIdx.x * len) / gridDim.x);
+  const uint32_t p_end = (uint32_t)(((uint64_t)(blockIdx.x + 1) * len) / gridDim.x);
+  const uint32_t row_bytes = Hkv * D * 2, slab_bytes = P * row_bytes;
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + (size_t)kvh * (D * 2) + lir * 16;
+
+  if (!meta_stable) pdl_wait();  // see QUEST_EST_META_STABLE
+  for (uint32_t i = tid; i < n_meta; i += kThreads) idx_s[i] = __ldg(meta_indices + i);
+  __syncthreads();
+
+  uint32_t p_ld = p_begin + pg_in, p = p_ld;
+  H8 mx[kDepth], mn[kDepth];
+  auto issue = [&](int s) {
+    const uint32_t pc = min(p_ld, len - 1);  // past the end: re-read the last page (never stored)
+    const uint32_t mp = p_magic ? __umulhi(pc, p_magic) : pc;
+    const uint32_t e = pc - mp * P;
+    const uint8_t* a = base + (uint64_t)(uint32_t)idx_s[mp] * (2u * slab_bytes) + e * row_bytes;
+    mx[s] = ld_stream(a);
+    mn[s] = ld_stream(a + slab_bytes);
+    p_ld += PPP;
+  };
+#pragma unroll
+  for (int s = 0; s < kDepth; ++s) issue(s);
+
+  if (meta_stable) pdl_wait();
+  float qv[8];
+  uint32_t mk[4];
+  if (kG == 1) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(q + (size_t)kvh * D + lir * 8);
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+      qv[2 * i] = f.x;
+      qv[2 * i + 1] = f.y;
+      // sign-bit test: for q = -0 either choice gives a +-0 product, which cannot change the sum
+      mk[i] = ((w[i] & 0x8000u) ? 0u : 0xffffu) | ((w[i] & 0x80000000u) ? 0u : 0xffff0000u);
+    }
+  } else {
+    for (uint32_t i = tid; i < Hq * D / 2; i += kThreads) {
+      const __half2 h2 = reinterpret_cast<const __half2*>(q)[i];
+      const float2 f = __half22float2(h2);
+      q_s[2 * i] = f.x;
+      q_s[2 * i + 1] = f.y;
+      const uint32_t bits = *reinterpret_cast<const uint32_t*>(&h2);
+      m_s[i] = ((bits & 0x8000u) ? 0u : 0xffffu) | ((bits & 0x80000000u) ? 0u : 0xffff0000u);
+    }
+    __syncthreads();
+  }
+  pdl_trigger();
+
+  while (p - pg_in < p_end) {  // uniform over the CTA: the pass's first page is still in range
+    uint32_t sel[kDepth][4];
+#pragma unroll
+    for (int s = 0; s < kDepth; ++s) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint32_t hi, lo;
+        if (kOrdered) {
+          hi = *reinterpret_cast<const uint32_t*>(&mx[s].h[i]);
+          lo = *reinterpret_cast<const uint32_t*>(&mn[s].h[i]);
+        } else {
+          const __half2 a = __hmax2(mx[s].h[i], mn[s].h[i]);
+          const __half2 b = __hmin2(mx[s].h[i], mn[s].h[i]);
+          hi = *reinterpret_cast<const uint32_t*>(&a);
+          lo = *reinterpret_cast<const uint32_t*>(&b);
+        }
+        if (kG == 1) {
+          sel[s][i] = (hi & mk[i]) | (lo & ~mk[i]);
+        } else {  // keep both; the select depends on the q head
+          sel[s][i] = hi;
+          mx[s].h[i] = *reinterpret_cast<const __half2*>(&lo);  // parked until the refill below
+        }
+      }
+      if (kG == 1) issue(s);  // refill this stage with the page kDepth passes ahead
+    }
+    const uint32_t pp = p + (lir / (LPR / 4)) * PPP;  // page whose score this lane holds after the reduce
+    const bool st = (lir % (LPR / 4)) == 0 && pp < p_end;
+    if (kG == 1) {
+      float sa[kDepth];
+#pragma unroll
+      for (int s = 0; s < kDepth; ++s) {
+        float sacc = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&sel[s][i]));
+          // reference order (decode_attn.cuh:152-160): 8 sequential fp32 adds of exact products
+          sacc = __fmaf_rn(qv[2 * i], f.x, sacc);
+          sacc = __fmaf_rn(qv[2 * i + 1], f.y, sacc);
+        }
+        sa[s] = sacc;
+      }
+      const float v = reduce4_transposed<LPR>(sa, lir);
+      if (st) o[(size_t)kvh * len + pp] = __float2half_rn(v);
+    } else {
+      for (uint32_t g = 0; g < G; ++g) {
+        const uint32_t h = kvh * G + g;
+        const float4* qp = reinterpret_cast<const float4*>(q_s + h * D + lir * 8);
+        const float4 q0 = qp[0], q1 = qp[1];
+        const uint4 msk = *reinterpret_cast<const uint4*>(m_s + h * (D / 2) + lir * 4);
+        const float qg[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        const uint32_t mg[4] = {msk.x, msk.y, msk.z, msk.w};
+        float sa[kDepth];
+#pragma unroll
+        for (int s = 0; s < kDepth; ++s) {
+          float sacc = 0.f;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t lo = *reinterpret_cast<const uint32_t*>(&mx[s].h[i]);
+            const uint32_t x = (sel[s][i] & mg[i]) | (lo & ~mg[i]);
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&x));
+            sacc = __fmaf_rn(qg[2 * i], f.x, sacc);
+            sacc = __fmaf_rn(qg[2 * i + 1], f.y, sacc);
+          }
+          sa[s] = sacc;
+        }
+        const float v = reduce4_transposed<LPR>(sa, lir);
+        if (st) o[(size_t)h * len + pp] = __float2half_rn(v);
+      }
+#pragma unroll
+      for (int s = 0; s < kDepth; ++s) issue(s);
+    }
+    p += kDepth * PPP;
+  }
+}
+
+template <int D>
+static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void* meta, const int32_t* meta_indices,
+                                uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t flags, cudaStream_t stream) {
+  constexpr uint32_t T_r = kTileWarps * (32 / (D / 8));
+  static int num_sms = 0;
+  if (!num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (num_sms <= 0) num_sms = 148;
+  }
+  const uint32_t G = Hq / Hkv, PPP = T_r / Hkv;
+  uint32_t grid = 2 * num_sms;
+  const uint32_t need = (len + PPP - 1) / PPP;  // at least one pass of pages per CTA
+  if (grid > need) grid = need;
+  const uint32_t n_meta = (len + P - 1) / P;
+  size_t smem = ((size_t)n_meta * 4 + 15) & ~(size_t)15;
+  if (G != 1) smem += (size_t)Hq * D * 6;
+  if (smem > 100 * 1024) return QUEST_ERR_UNSUPPORTED;
+  const bool ord = flags & QUEST_EST_META_ORDERED;
+  auto kern = G == 1 ? (ord ? estimate_tile_kernel<D, 1, 1> : estimate_tile_kernel<D, 0, 1>)
+                     : (ord ? estimate_tile_kernel<D, 1, 0> : estimate_tile_kernel<D, 0, 0>);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kTileWarps * 32);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const uint32_t p_magic = P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta, meta_indices,
+                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE);
+  if (e != cudaSuccess) return (int)e;
+  QUEST_RETURN_LAUNCH();
+}
+
 template <int D, int kEstThreads, int kEstDepth>
 static int launch_estimate(const void* q, void* o, uint32_t len, const void* meta,
                            const int32_t* meta_indices, uint32_t Hq, uint32_t Hkv, uint32_t P,
@@ -149,8 +363,8 @@ static int launch_estimate(const void* q, void* o, uint32_t len, const void* met
   const size_t smem = (size_t)Hq * D * sizeof(float) + (size_t)Hq * D / 2 * sizeof(uint32_t) + (size_t)n_meta * 4;
   if (smem > 100 * 1024 || (uint64_t)len * Hkv >= (1u << 24)) return QUEST_ERR_UNSUPPORTED;
   const uint32_t G = Hq / Hkv;
-  auto kern = G == 1 ? estimate_kernel<D, kEstThreads, kEstDepth, 1> : G == 4 ? estimate_kernel<D, kEstThreads, kEstDepth, 4>
-                                                                       : estimate_kernel<D, kEstThreads, kEstDepth, 0>;
+  auto kern = G == 1 ? estimate_rows_kernel<D, kEstThreads, kEstDepth, 1> : G == 4 ? estimate_rows_kernel<D, kEstThreads, kEstDepth, 4>
+                                                                       : estimate_rows_kernel<D, kEstThreads, kEstDepth, 0>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -183,6 +397,21 @@ extern "C" int quest_estimate(const void* q, void* o, uint32_t len, const void* 
   if (len == 0) return QUEST_OK;
   if ((size_t)num_qo_heads * head_dim * 6 > 160 * 1024) return QUEST_ERR_UNSUPPORTED;
   cudaStream_t s = (cudaStream_t)stream;
+  {  // product path: the tile kernel, whenever the kv heads divide its row tile
+    const uint32_t T_r = quest::kTileWarps * (32 / (head_dim / 8));
+    static int force_rows = -1;
+    if (force_rows < 0) {
+      const char* e = getenv("QUEST_EST_ROWS");
+      force_rows = e && e[0] == '1';
+    }
+    if (!force_rows && T_r % num_kv_heads == 0 && (head_dim == 64 || head_dim == 128 || head_dim == 256)) {
+      switch (head_dim) {
+        case 64: return quest::launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
+        case 128: return quest::launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
+        default: return quest::launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
+      }
+    }
+  }
   static int cfg = -1;  // tuning hook: QUEST_EST_CFG selects the (threads, depth) variant for head_dim 128
   if (cfg < 0) {
     const char* e = getenv("QUEST_EST_CFG");

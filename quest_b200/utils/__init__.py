@@ -96,6 +96,8 @@ def decode_estimate(q: torch.Tensor, iController: InferenceController, layer_idx
         iController.metadata_cache.last_page_len,
         iController.metadata_last_page_idx,
         iController.layout,
+        # the controller's metadata pool is only ever written by append_kv, which keeps max >= min
+        _kernels.EST_META_ORDERED,
     )
     return o
 

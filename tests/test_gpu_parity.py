@@ -115,14 +115,35 @@ def test_estimate_bitexact_reference_sweep(kv_len):
 
 @pytest.mark.parametrize("Hq,Hkv,D,P,kv_len", [(8, 8, 64, 16, 300), (4, 4, 256, 16, 200), (32, 8, 128, 16, 1000),
                                                 (8, 2, 128, 7, 150), (6, 3, 64, 1, 40), (32, 32, 128, 32, 2100)])
-def test_estimate_bitexact_shapes_and_gqa(Hq, Hkv, D, P, kv_len):
+@pytest.mark.parametrize("flags", [0, K.EST_META_ORDERED, K.EST_META_ORDERED | K.EST_META_STABLE])
+def test_estimate_bitexact_shapes_and_gqa(Hq, Hkv, D, P, kv_len, flags):
+    """(6,3,64,...) has kv heads that do not divide the row tile -> estimate_rows_kernel; the others take the tile kernel."""
     oc, gc, k, v, rng = make_pair(kv_len, P, Hkv, D, seed=kv_len + D)
     q = rng.standard_normal((1, Hq, D), dtype=np.float32).astype(np.float16)
     n = len(oc.kv_indices) - 1
     o = torch.empty((Hq, n), dtype=torch.float16, device=DEV)
     kvi, kvp, mi, mp = gc.tables()
-    K.estimate_attn_score(t(q), o, gc.meta, mi, mp, oc.meta_last_page_len, oc.meta_indices[-1], 0)
+    torch.cuda.synchronize()  # EST_META_STABLE: nothing that writes metadata may immediately precede the call
+    K.estimate_attn_score(t(q), o, gc.meta, mi, mp, oc.meta_last_page_len, oc.meta_indices[-1], 0, flags)
     np.testing.assert_array_equal(bits(o), orc.estimate_scores(q[0], oc.meta_pool, oc.meta_indices, n, Hq).view(np.int16))
+
+
+@pytest.mark.parametrize("Hq,Hkv,D,P,n_pages", [(32, 32, 128, 16, 519), (8, 2, 64, 3, 77), (4, 4, 256, 7, 100), (6, 3, 128, 16, 65)])
+def test_estimate_unordered_random_metadata(Hq, Hkv, D, P, n_pages):
+    """Reference kernels/src/test/test_max_possible.cu:29-154: max and min slabs are independent N(0,1) draws (so
+    max >= min does NOT hold) behind a shuffled page table; sum_d max(q*max, q*min) must still be bit-exact."""
+    rng = np.random.default_rng(n_pages + D)
+    n_meta = (n_pages + P - 1) // P
+    pool = rng.standard_normal((n_meta + 3, 2, P, Hkv, D), dtype=np.float32).astype(np.float16)
+    meta_indices = [int(x) for x in rng.permutation(n_meta + 3)[:n_meta]]
+    q = rng.standard_normal((1, Hq, D), dtype=np.float32).astype(np.float16)
+    n = n_pages - 1
+    o = torch.empty((Hq, n), dtype=torch.float16, device=DEV)
+    mi = torch.tensor(meta_indices, dtype=torch.int32, device=DEV)
+    mp = torch.tensor([0, n_meta], dtype=torch.int32, device=DEV)
+    last_len = n_pages - (n_meta - 1) * P
+    K.estimate_attn_score(t(q), o, t(pool), mi, mp, last_len, meta_indices[-1], 0)
+    np.testing.assert_array_equal(bits(o), orc.estimate_scores(q[0], pool, meta_indices, n, Hq).view(np.int16))
 
 
 # ------------------------------------------------------------------ top-k (exact set, deterministic order)
