@@ -6,6 +6,18 @@
 
 #include "../../include/quest_b200.h"
 
+// Where each kernel releases its programmatic dependents (0 = only at exit).  Measured on B200 (profiles/r01_pdl_trigger_ab.txt):
+// early triggers made estimate->top-k and top-k->decode 6-11 us SLOWER per pair, so the default is exit-only.
+#ifndef QUEST_TRIG_EST
+#define QUEST_TRIG_EST 0
+#endif
+#ifndef QUEST_TRIG_TOPK
+#define QUEST_TRIG_TOPK 0
+#endif
+#ifndef QUEST_TRIG_DEC
+#define QUEST_TRIG_DEC 0
+#endif
+
 namespace quest {
 
 extern unsigned long long g_launch_count;  // defined in capi.cu

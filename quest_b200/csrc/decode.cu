@@ -68,7 +68,9 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     for (int i = 0; i < 8; ++i) qv[i] *= sm_scale_log2;
   }
   __syncthreads();
+#if QUEST_TRIG_DEC
   pdl_trigger();
+#endif
 
   float acc[8];
 #pragma unroll

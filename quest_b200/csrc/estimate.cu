@@ -88,7 +88,9 @@ estimate_rows_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
     m_s[i] = ((bits & 0x8000u) ? 0u : 0xffffu) | ((bits & 0x80000000u) ? 0u : 0xffff0000u);
   }
   __syncthreads();
+#if QUEST_TRIG_EST
   pdl_trigger();
+#endif
 
 
   while (r - rsub < total_rows) {
@@ -222,7 +224,9 @@ estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
     }
     __syncthreads();
   }
+#if QUEST_TRIG_EST
   pdl_trigger();
+#endif
 
   while (p - pg_in < p_end) {  // uniform over the CTA: the pass's first page is still in range
     uint32_t sel[kDepth][4];

@@ -21,7 +21,9 @@ topk_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_
   const uint16_t* s = scores + (size_t)head * len;
   const uint32_t len8 = (len + 7) & ~7u;
 
+#if QUEST_TRIG_TOPK
   pdl_trigger();
+#endif
   pdl_wait();  // scores come from the estimate kernel
   // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent
   for (uint32_t i = tid; i < len8; i += T) keys[i] = i < len ? key_of(s[i]) : (uint16_t)0;
