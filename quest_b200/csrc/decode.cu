@@ -7,6 +7,8 @@
 // rows; every warp keeps two items (8 independent 128-bit loads per lane) in flight while it consumes the
 // previous one.  Partials go to a caller-owned workspace; the last CTA to arrive for a head (atomic
 // ticket) merges them -- no separate merge launch.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace quest {
@@ -36,7 +38,8 @@ __global__ void __launch_bounds__(kDecThreads, 7)
 decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __restrict__ lse,
               const __half* __restrict__ kv, const int32_t* __restrict__ indices, uint32_t idx_stride,
               uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len, uint32_t Hkv, uint32_t G,
-              uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws) {
+              uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws,
+              uint32_t dbg) {
   constexpr int LPR = D / 8;
   constexpr int TPL = 32 / LPR;           // token rows per warp-wide load
   constexpr int IT = 2 * TPL;             // tokens per item
@@ -77,59 +80,66 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
   for (int i = 0; i < 8; ++i) acc[i] = 0.f;
   float m = kNegBig, d = 0.f;
 
-  // Branch-free inner loop.  This lane group's token in sub-load j of the item being issued is kept as
-  // (local page, entry) and advanced by the item stride without divisions; validity of the 2x2 loads in
-  // flight is remembered in okm (bit 2*stage + j).  Invalid rows are not loaded (predicated) and enter the
+  // Each warp owns whole pages of the chunk (local pages warp, warp+4, ...) and walks their token rows with a
+  // 4-deep register ring of (K row, V row) pairs: a stage is one warp-wide load of TPL token rows, so addresses
+  // advance by a constant inside a page and are recomputed (one shared-memory lookup) only at page boundaries.
+  // Invalid rows (past the last page's length, past the chunk) are not loaded (predicated) and enter the
   // softmax with weight 0; their stale registers always hold finite halves.
-  H8 kk[2][2], vv[2][2];
+  constexpr int kRing = 4;
+  H8 kk[kRing], vv[kRing];
 #pragma unroll
-  for (int st = 0; st < 2; ++st)
+  for (int st = 0; st < kRing; ++st)
 #pragma unroll
-    for (int j = 0; j < 2; ++j)
-#pragma unroll
-      for (int i = 0; i < 4; ++i) kk[st][j].h[i] = vv[st][j].h[i] = __half2half2(__ushort_as_half(0));
-  const uint32_t S = kDecWarps * IT;  // tokens between consecutive items of one warp
-  const uint32_t dpg = div_p(S, p_magic), de = S - dpg * P;
-  uint32_t pgl[2], en[2], okm = 0;
-#pragma unroll
-  for (int j = 0; j < 2; ++j) {
-    const uint32_t t = warp * IT + j * TPL + sub;
-    pgl[j] = div_p(t, p_magic);
-    en[j] = t - pgl[j] * P;
-  }
-  const uint32_t row_bytes = Hkv * D * 2, page_bytes = 2 * P * row_bytes, slab_bytes = P * row_bytes;
-  const uint8_t* kvb = reinterpret_cast<const uint8_t*>(kv) + (size_t)kvh * D * 2 + lir * 16;
+    for (int i = 0; i < 4; ++i) kk[st].h[i] = vv[st].h[i] = __half2half2(__ushort_as_half(0));
+  const uint32_t row_bytes = Hkv * D * 2, slab_bytes = P * row_bytes;
+  const uint64_t page_bytes = 2ull * slab_bytes;
+  const uint8_t* kvb = reinterpret_cast<const uint8_t*>(kv) + (size_t)kvh * D * 2 + lir * 16 + (size_t)sub * row_bytes;
+  const uint32_t n_tl = (P + TPL - 1) / TPL;                   // token-loads per page
   const uint32_t n_sel_local = n_sel > pg0 ? n_sel - pg0 : 0;  // local pages below this are selected (full) pages
-  auto issue = [&](int st) {
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const bool ok = pgl[j] < npg && (pgl[j] < n_sel_local || en[j] < last_page_len);
-      const uint32_t page = (uint32_t)s_pages[min(pgl[j], npg - 1)];
-      const uint8_t* kp = kvb + (uint64_t)page * page_bytes + en[j] * row_bytes;
-      ld_stream_if(kk[st][j], kp, ok);
-      ld_stream_if(vv[st][j], kp + slab_bytes, ok);
-      okm = (okm & ~(1u << (2 * st + j))) | ((uint32_t)ok << (2 * st + j));
-      pgl[j] += dpg;
-      en[j] += de;
-      if (en[j] >= P) {
-        en[j] -= P;
-        ++pgl[j];
-      }
+  // issue-side cursor
+  uint32_t pg_ld = warp, i_ld = 0, okm = 0;
+  const uint8_t* ptr = kvb;
+  uint32_t nv_ld = 0;  // valid tokens of the page under the cursor
+  auto open_page = [&]() {
+    if (pg_ld < npg) {
+      ptr = kvb + (uint64_t)(uint32_t)s_pages[pg_ld] * page_bytes;
+      nv_ld = pg_ld < n_sel_local ? P : last_page_len;
+    } else {
+      nv_ld = 0;
     }
   };
-  auto consume = [&](int st) {
+  open_page();
+  auto issue = [&](int st) {
+    const bool ok = i_ld * TPL + sub < nv_ld;
+    ld_stream_if(kk[st], ptr, ok);
+    ld_stream_if(vv[st], ptr + slab_bytes, ok);
+    okm = (okm & ~(1u << st)) | ((uint32_t)ok << st);
+    ptr += TPL * row_bytes;
+    if (++i_ld == n_tl) {  // warp-uniform
+      i_ld = 0;
+      pg_ld += kDecWarps;
+      open_page();
+    }
+  };
+  auto consume2 = [&](int st) {  // stages st, st+1: two token rows per lane group, one softmax rescale
+    if (dbg & 2) {  // experiment: loads only
+      float kf[8];
+      h8_to_float(kk[st], kf); acc[0] += kf[0]; h8_to_float(vv[st], kf); acc[1] += kf[0];
+      h8_to_float(kk[st + 1], kf); acc[2] += kf[0]; h8_to_float(vv[st + 1], kf); acc[3] += kf[0];
+      return;
+    }
     float sc[2];
     float mt = m;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
       float kf[8];
-      h8_to_float(kk[st][j], kf);
+      h8_to_float(kk[st + j], kf);
       float a = 0.f;
 #pragma unroll
       for (int i = 0; i < 8; ++i) a = fmaf(qv[i], kf[i], a);
 #pragma unroll
       for (int off = LPR / 2; off > 0; off >>= 1) a += __shfl_xor_sync(0xffffffffu, a, off);
-      sc[j] = (okm >> (2 * st + j)) & 1u ? a : kNegBig;
+      sc[j] = (okm >> (st + j)) & 1u ? a : kNegBig;
       mt = fmaxf(mt, sc[j]);
     }
     const float scale = ex2(m - mt);
@@ -139,22 +149,26 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     for (int i = 0; i < 8; ++i) acc[i] *= scale;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      const float p = (okm >> (2 * st + j)) & 1u ? ex2(sc[j] - m) : 0.f;
+      const float p = (okm >> (st + j)) & 1u ? ex2(sc[j] - m) : 0.f;
       d += p;
       float vf[8];
-      h8_to_float(vv[st][j], vf);
+      h8_to_float(vv[st + j], vf);
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[i] = fmaf(p, vf[i], acc[i]);
     }
   };
-  // warp-uniform trip count (the shuffles use the full mask)
-  issue(0);
-  issue(1);
-  for (uint32_t it = warp; it < n_items; it += 2 * kDecWarps) {
-    consume(0);
+  // token-loads this warp must consume: its pages x n_tl (warp-uniform; the shuffles use the full mask)
+  const uint32_t my_pages = npg > warp ? (npg - warp + kDecWarps - 1) / kDecWarps : 0;
+  const uint32_t my_tl = my_pages * n_tl;
+#pragma unroll
+  for (int st = 0; st < kRing; ++st) issue(st);
+  for (uint32_t t = 0; t < my_tl; t += kRing) {
+    consume2(0);
     issue(0);
-    consume(1);
     issue(1);
+    consume2(2);
+    issue(2);
+    issue(3);
   }
 
   // CTA merge of the NG group states.
@@ -202,33 +216,84 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     ws_md[((size_t)h * nchunks + chunk) * 2] = M;
     ws_md[((size_t)h * nchunks + chunk) * 2 + 1] = dsum;
   }
-  __threadfence();
+  if (dbg & 1) return;  // experiment: no merge
+  // Release/acquire through the ticket: the CTA's partial is ordered before tid 0's acq_rel atomic by the
+  // barrier, and the last arriver's acquire orders every other CTA's partial before its loads below.
   __syncthreads();
-  if (tid == 0) s_last = (atomicAdd(ticket + h, 1u) == nchunks - 1);
+  if (tid == 0) {
+    uint32_t old;
+    asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(old) : "l"(ticket + h) : "memory");
+    s_last = old == nchunks - 1;
+  }
   __syncthreads();
   if (!s_last) return;
-  __threadfence();
-  float MM = kNegBig;
-  for (uint32_t c = 0; c < nchunks; ++c) MM = fmaxf(MM, __ldcg(ws_md + ((size_t)h * nchunks + c) * 2));
-  float dd = 0.f, oo[CPT];
+  // Last arriver: one round trip.  All partial rows are requested as independent 128-bit loads
+  // (kDecThreads / (D/4) rows per sweep, 8 sweeps in flight) before any weight is needed.
+  constexpr int NV = D / 4;               // float4 per partial row
+  constexpr int RPS = kDecThreads / NV;   // rows per sweep
+  static_assert(RPS >= 1 && RPS <= NG, "partial-row sweep must fit the group-state buffer");
+  const uint32_t cr = tid / NV, c4 = tid % NV;
+  const float4* po = reinterpret_cast<const float4*>(ws_o + (size_t)h * nchunks * D);
+  const float2* pmd = reinterpret_cast<const float2*>(ws_md + (size_t)h * nchunks * 2);
+  float4 a4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  float MM = kNegBig, dd = 0.f;
+  for (uint32_t cb = 0; cb < nchunks; cb += RPS * 8) {
+    float4 v[8];
+    float2 md[8];
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) oo[c] = 0.f;
-  for (uint32_t cc = 0; cc < nchunks; ++cc) {
-    const float w = ex2(__ldcg(ws_md + ((size_t)h * nchunks + cc) * 2) - MM);
-    dd += __ldcg(ws_md + ((size_t)h * nchunks + cc) * 2 + 1) * w;
+    for (int i = 0; i < 8; ++i) {
+      const uint32_t c = cb + i * RPS + cr;
+      v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      md[i] = make_float2(kNegBig, 0.f);
+      if (c < nchunks) {
+        v[i] = __ldcg(po + (size_t)c * NV + c4);
+        md[i] = __ldcg(pmd + c);
+      }
+    }
+    float mb = MM;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) mb = fmaxf(mb, md[i].x);
+    const float sc0 = ex2(MM - mb);
+    MM = mb;
+    dd *= sc0;
+    a4.x *= sc0, a4.y *= sc0, a4.z *= sc0, a4.w *= sc0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float w = ex2(md[i].x - MM);
+      dd += md[i].y * w;
+      a4.x += v[i].x * w, a4.y += v[i].y * w, a4.z += v[i].z * w, a4.w += v[i].w * w;
+    }
+  }
+  // combine the RPS row groups (each saw a disjoint subset of the chunks) through shared memory
+  *reinterpret_cast<float4*>(&s_o[cr][c4 * 4]) = a4;
+  if (c4 == 0) {
+    s_md[cr][0] = MM;
+    s_md[cr][1] = dd;
+  }
+  __syncthreads();
+  float Mf = kNegBig;
+#pragma unroll
+  for (int g = 0; g < RPS; ++g) Mf = fmaxf(Mf, s_md[g][0]);
+  float df = 0.f, of[CPT];
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) of[c] = 0.f;
+#pragma unroll
+  for (int g = 0; g < RPS; ++g) {
+    const float w = ex2(s_md[g][0] - Mf);
+    df += s_md[g][1] * w;
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
       const uint32_t col = tid + c * kDecThreads;
-      if (col < D) oo[c] += __ldcg(ws_o + ((size_t)h * nchunks + cc) * D + col) * w;
+      if (col < D) of[c] += s_o[g][col] * w;
     }
   }
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
     const uint32_t col = tid + c * kDecThreads;
-    if (col < D) o[(size_t)h * D + col] = __float2half_rn(__fdividef(oo[c], dd));
+    if (col < D) o[(size_t)h * D + col] = __float2half_rn(__fdividef(of[c], df));
   }
   if (tid == 0) {
-    if (lse) lse[h] = MM + lg2(dd);
+    if (lse) lse[h] = Mf + lg2(df);
     ticket[h] = 0;  // ready for the next launch
   }
 }
@@ -254,7 +319,8 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
   const float sm_scale_log2 = kLog2e / sqrtf((float)D);
   cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<D>, (const __half*)q, (__half*)o, lse, (const __half*)kv,
                                      indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv, Hq / Hkv, P,
-                                     div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws);
+                                     div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws,
+                                     (uint32_t)(getenv("QUEST_DEC_DBG") ? atoi(getenv("QUEST_DEC_DBG")) : 0));
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -275,6 +341,10 @@ extern "C" int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, 
   if (min_ppc == 0) min_ppc = 1;
   uint32_t ppc = min_ppc;
   while (ppc < total && (uint64_t)num_qo_heads * ((total + ppc - 1) / ppc) > slots) ++ppc;
+  if (const char* e = getenv("QUEST_DEC_PPC")) {  // tuning hook
+    const uint32_t v = (uint32_t)atoi(e);
+    if (v) ppc = v;
+  }
   if (ppc > total) ppc = total;
   *pages_per_chunk = ppc;
   *num_chunks = (total + ppc - 1) / ppc;

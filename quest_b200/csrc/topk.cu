@@ -4,16 +4,18 @@
 // (reference kernels/include/topk/decode_select_k.cuh:25-62; raft select_radix.cuh:82-104 key twiddle,
 // :380-399 choose_bucket, :404-440 last_filter).  Unlike raft's atomicAdd race among ties, the tie rule
 // here is deterministic: lowest position first.
+#include <stdlib.h>
+
 #include "topk.cuh"
 
 namespace quest {
 
 constexpr uint32_t kTopkMaxLen = 96 * 1024;  // 192 KB of u16 keys
 
-template <int W>
+template <int W, int KPC>
 __global__ void __launch_bounds__(32 * W)
 topk_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_idx, uint32_t in_stride,
-            uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx, uint32_t len, uint32_t k) {
+            uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx, uint32_t len, uint32_t k, uint32_t dbg) {
   extern __shared__ __align__(16) uint16_t keys[];  // [len rounded up to 8]
   __shared__ TopkScratch<W> sc;
   constexpr uint32_t T = 32 * W;
@@ -26,17 +28,60 @@ topk_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_
 #endif
   pdl_wait();  // scores come from the estimate kernel
   // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent
+  if (dbg == 1) return;
   for (uint32_t i = tid; i < len8; i += T) keys[i] = i < len ? key_of(s[i]) : (uint16_t)0;
   __syncthreads();
-  topk_select<W>(keys, len, k, tid, 1, &sc, in_idx ? in_idx + (size_t)head * in_stride : nullptr,
-                 out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr);
+  if (dbg == 2) { if (keys[tid] == 0x1234 && tid == 77) out_idx[0] = 1; return; }
+  topk_select<W, KPC>(keys, len, k, tid, 1, &sc, in_idx ? in_idx + (size_t)head * in_stride : nullptr,
+                 out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr, dbg);
 }
 
 template <int W>
+__global__ void __launch_bounds__(32 * W)
+topk_fast_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_idx, uint32_t in_stride,
+                 uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx, uint32_t len, uint32_t k) {
+  __shared__ __align__(16) uint16_t keys[4 * 32 * W];
+  __shared__ TopkFastScratch<W> sc;
+  constexpr uint32_t T = 32 * W;
+  const uint32_t head = blockIdx.x, tid = threadIdx.x;
+  const uint16_t* s = scores + (size_t)head * len;
+  const uint32_t len8 = (len + 7) & ~7u;
+  pdl_wait();  // scores come from the estimate kernel
+  // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent (4 per thread)
+  uint16_t v[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) v[j] = tid + j * T < len ? s[tid + j * T] : (uint16_t)0xffffu;  // 0xffff -> key 0
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (tid + j * T < len8) keys[tid + j * T] = key_of(v[j]);
+  __syncthreads();
+  topk_select_fast<W>(keys, len, k, tid, 1, &sc, in_idx ? in_idx + (size_t)head * in_stride : nullptr,
+                      out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr);
+}
+
+template <int W>
+static int launch_topk_fast(const void* scores, const int32_t* in_idx, uint32_t in_stride, void* out_val, int32_t* out_idx,
+                            uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_heads);
+  cfg.blockDim = dim3(32 * W);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_fast_kernel<W>, (const uint16_t*)scores, in_idx, in_stride,
+                                     (uint16_t*)out_val, out_idx, len, k);
+  if (e != cudaSuccess) return (int)e;
+  QUEST_RETURN_LAUNCH();
+}
+
+template <int W, int KPC>
 static int launch_topk(const void* scores, const int32_t* in_idx, uint32_t in_stride, void* out_val, int32_t* out_idx,
                        uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream) {
   const size_t smem = (((size_t)len + 7) & ~(size_t)7) * sizeof(uint16_t);
-  auto kern = topk_kernel<W>;
+  auto kern = topk_kernel<W, KPC>;
   if (smem > 40 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -52,7 +97,7 @@ static int launch_topk(const void* scores, const int32_t* in_idx, uint32_t in_st
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const uint16_t*)scores, in_idx, in_stride, (uint16_t*)out_val,
-                                     out_idx, len, k);
+                                     out_idx, len, k, (uint32_t)(getenv("QUEST_TOPK_DBG") ? atoi(getenv("QUEST_TOPK_DBG")) : 0));
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -68,6 +113,11 @@ extern "C" int quest_topk(const void* scores, const int32_t* in_idx, uint32_t in
   if (k > len) return QUEST_ERR_BAD_ARG;
   if (len > quest::kTopkMaxLen) return QUEST_ERR_UNSUPPORTED;
   cudaStream_t s = (cudaStream_t)stream;
-  if (len <= 8192) return quest::launch_topk<8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
-  return quest::launch_topk<32>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  static const bool no_fast = getenv("QUEST_TOPK_GENERIC") != nullptr;  // test hook: force the generic kernels
+  if (!no_fast && len <= 1024) return quest::launch_topk_fast<8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (!no_fast && len <= 2048) return quest::launch_topk_fast<16>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (!no_fast && len <= 4096) return quest::launch_topk_fast<32>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (len <= 2048) return quest::launch_topk<16, 4>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (len <= 8192) return quest::launch_topk<32, 8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  return quest::launch_topk<32, 8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
 }

@@ -13,6 +13,13 @@
 
 namespace quest {
 
+#ifdef QUEST_TOPK_CLOCKS
+__device__ long long g_topk_clk[64];
+#define TOPK_STAMP(i) do { if (t == 0 && blockIdx.x == 0) g_topk_clk[i] = clock64(); } while (0)
+#else
+#define TOPK_STAMP(i) do { } while (0)
+#endif
+
 __device__ __forceinline__ uint16_t key_of(uint16_t h) { return (h & 0x8000u) ? (uint16_t)~h : (uint16_t)(h | 0x8000u); }
 __device__ __forceinline__ uint16_t half_of(uint16_t k) { return (k & 0x8000u) ? (uint16_t)(k & 0x7fffu) : (uint16_t)~k; }
 
@@ -26,64 +33,217 @@ struct TopkScratch {
   uint32_t wgt[W], weq[W];
 };
 
+__device__ __forceinline__ uint64_t shl64_clamped(uint32_t s) {  // 1 << s, 0 for s >= 64 (PTX shl clamps)
+  uint64_t r;
+  asm("shl.b64 %0, %1, %2;" : "=l"(r) : "l"(1ull), "r"(s));
+  return r;
+}
+
+template <int W>
+struct TopkFastScratch {
+  uint8_t histT[2][16][W];  // [pass parity][bin][warp]: per-warp bin totals (<= 128 each)
+  uint32_t wgt[W], weq[W];
+};
+
+// Fast path for n <= 4 * 32 * W: every thread owns 4 consecutive keys (two packed words) held in registers for
+// the whole selection.  The counting loop is bound by the integer pipe (half rate on this part), so it is
+// written for instruction count: per key a 128-bit one-hot (8-bit field per bin) is built with two clamped
+// 64-bit shifts and added into 4 words (fields cannot carry: a thread adds at most 4, a warp at most 128, so
+// REDUX runs on the 8-bit fields directly); bin totals are published transposed so that lane b sums its bin
+// over all warps with one 128-bit load and dp4a.
+template <int W>
+__device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t n, uint32_t k, uint32_t t,
+                                                 uint32_t bar_id, TopkFastScratch<W>* sc,
+                                                 const int32_t* __restrict__ in_idx, int32_t* __restrict__ out_idx,
+                                                 uint16_t* __restrict__ out_val) {
+  static_assert(W == 4 || W == 8 || W == 16 || W == 32, "W bytes per bin row are read as 32-bit words");
+  constexpr uint32_t T = 32 * W;
+  const uint32_t lane = t & 31, warp = t >> 5;
+  const uint32_t i0 = t * 4;  // first key of this thread (keys are zero-padded to a multiple of 8 past n)
+  uint32_t wd[2] = {0, 0};
+  if (i0 < ((n + 7) & ~7u)) {
+    const uint2 v = reinterpret_cast<const uint2*>(keys)[t];
+    wd[0] = v.x, wd[1] = v.y;
+  }
+  int32_t pay[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) pay[j] = i0 + j < n ? (in_idx ? __ldg(in_idx + i0 + j) : (int32_t)(i0 + j)) : 0;
+
+  uint32_t prefix = 0, kk = k;
+#pragma unroll
+  for (int pass = 0; pass < 4; ++pass) {
+    constexpr uint32_t kOnes = 0x00010001u;
+    const uint32_t shift = 12 - 4 * pass;
+    const uint32_t hi_mask = (0xffffu >> (shift + 4)) * kOnes, pp = prefix * kOnes;
+    uint32_t c[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int x = 0; x < 2; ++x) {
+      const uint32_t y = ((wd[x] >> (shift + 4)) & hi_mask) ^ pp;      // 0 in a half <=> that key matches the prefix
+      const uint32_t d8lo = ((wd[x] << 3) >> shift) & 0x78u;           // 8 * digit of the low key
+      const uint32_t d8hi = ((wd[x] >> 13) >> shift) & 0x78u;          // 8 * digit of the high key
+      const uint32_t slo = (y & 0xffffu) == 0 ? d8lo : 255u, shi = (y >> 16) == 0 ? d8hi : 255u;
+      const uint64_t a0 = shl64_clamped(slo), a1 = shl64_clamped(slo - 64u);
+      const uint64_t b0 = shl64_clamped(shi), b1 = shl64_clamped(shi - 64u);
+      c[0] += (uint32_t)a0 + (uint32_t)b0;
+      c[1] += (uint32_t)(a0 >> 32) + (uint32_t)(b0 >> 32);
+      c[2] += (uint32_t)a1 + (uint32_t)b1;
+      c[3] += (uint32_t)(a1 >> 32) + (uint32_t)(b1 >> 32);
+    }
+    // zero-padded / out-of-range keys: key 0 never matches a non-zero prefix and sits in the lowest bin otherwise,
+    // below every real key, so it cannot change which bin holds the k-th largest.
+    uint32_t tot[4];
+#pragma unroll
+    for (int x = 0; x < 4; ++x) tot[x] = __reduce_add_sync(0xffffffffu, c[x]);  // warp-uniform
+    if (lane < 16) {
+      const uint32_t wsel = (lane >> 2) == 0 ? tot[0] : (lane >> 2) == 1 ? tot[1] : (lane >> 2) == 2 ? tot[2] : tot[3];
+      sc->histT[pass & 1][lane][warp] = (uint8_t)(wsel >> ((lane & 3) * 8));
+    }
+    group_bar(bar_id, T);
+    uint32_t s = 0;
+    if (lane < 16) {
+      const uint32_t* row = reinterpret_cast<const uint32_t*>(sc->histT[pass & 1][lane]);
+#pragma unroll
+      for (int x = 0; x < W / 4; ++x) s = __dp4a(row[x], 0x01010101u, s);
+    }
+    uint32_t suf = s;  // suffix sums over the 16 bin lanes (lanes 16..31 carry zeros)
+#pragma unroll
+    for (int off = 1; off < 16; off <<= 1) {
+      const uint32_t x = __shfl_down_sync(0xffffffffu, suf, off);
+      if (lane + off < 16) suf += x;
+    }
+    const uint32_t above = suf - s;
+    const bool hit = lane < 16 && above < kk && above + s >= kk;
+    const uint32_t b = __ffs(__ballot_sync(0xffffffffu, hit)) - 1;
+    kk -= __shfl_sync(0xffffffffu, above, b);
+    prefix = (prefix << 4) | b;
+  }
+  const uint32_t tau = prefix, need = kk;
+
+  uint32_t key[4];
+  key[0] = wd[0] & 0xffffu, key[1] = wd[0] >> 16, key[2] = wd[1] & 0xffffu, key[3] = wd[1] >> 16;
+  uint32_t ngt = 0, neq = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const bool in = i0 + j < n;
+    ngt += in && key[j] > tau;
+    neq += in && key[j] == tau;
+  }
+  uint32_t pk = (ngt << 16) | neq, spk = pk;  // both counts < 65536: scan them as one word
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const uint32_t a = __shfl_up_sync(0xffffffffu, spk, off);
+    if (lane >= (uint32_t)off) spk += a;
+  }
+  if (lane == 31) sc->wgt[warp] = spk;
+  group_bar(bar_id, T);
+  uint32_t before = spk - pk;
+#pragma unroll
+  for (int w2 = 0; w2 < W; ++w2)
+    if ((uint32_t)w2 < warp) before += sc->wgt[w2];
+  uint32_t gt_before = before >> 16, eq_before = before & 0xffffu;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const bool in = i0 + j < n;
+    const bool gt = in && key[j] > tau, eq = in && key[j] == tau;
+    if (gt || (eq && eq_before < need)) {
+      const uint32_t pos = gt_before + min(eq_before, need);
+      out_idx[pos] = pay[j];
+      if (out_val) out_val[pos] = half_of((uint16_t)key[j]);
+    }
+    gt_before += gt;
+    eq_before += eq;
+  }
+}
+
 // keys: shared, 16-byte aligned, readable (and zero-padded) up to a multiple of 8 elements past n.
 // t: thread index inside the group [0, 32*W); bar_id: a named barrier reserved for this group.
 // in_idx: payload ids (global; nullptr = position); out_idx/out_val: global rows of k entries.
-template <int W>
+// KPC: keys per ownership chunk (4 or 8).  The whole selection is a chain of dependent short instructions, so
+// its time is (instructions per warp) x (issue latency): small chunks on more warps shorten the chain.
+template <int W, int KPC>
 __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, uint32_t k, uint32_t t, uint32_t bar_id,
                                             TopkScratch<W>* sc, const int32_t* __restrict__ in_idx,
-                                            int32_t* __restrict__ out_idx, uint16_t* __restrict__ out_val) {
+                                            int32_t* __restrict__ out_idx, uint16_t* __restrict__ out_val, uint32_t dbg = 0) {
+  static_assert(KPC == 4 || KPC == 8, "chunk of 4 or 8 keys");
   constexpr uint32_t T = 32 * W;
+  constexpr int WPC = KPC / 2;  // 32-bit words per chunk
   const uint32_t lane = t & 31, warp = t >> 5;
-  const uint32_t n8 = (n + 7) >> 3;                 // 8-key chunks
-  const uint32_t cpt = (n8 + T - 1) / T;            // chunks per thread (blocked ownership)
-  const uint32_t c0 = min(t * cpt, n8), c1 = min(c0 + cpt, n8);
-  const uint4* kv = reinterpret_cast<const uint4*>(keys);
+  const uint32_t nc = (n + KPC - 1) / KPC;          // chunks
+  const uint32_t cpt = (nc + T - 1) / T;            // chunks per thread (blocked ownership)
+  const uint32_t c0 = min(t * cpt, nc), c1 = min(c0 + cpt, nc);
+  const uint32_t* kw = reinterpret_cast<const uint32_t*>(keys);
+  auto load_chunk = [&](uint32_t c, uint32_t (&w)[WPC]) {
+    if (KPC == 8) {
+      const uint4 v = reinterpret_cast<const uint4*>(kw)[c];
+      w[0] = v.x, w[1] = v.y, w[WPC - 2] = v.z, w[WPC - 1] = v.w;
+    } else {
+      const uint2 v = reinterpret_cast<const uint2*>(kw)[c];
+      w[0] = v.x, w[1] = v.y;
+    }
+  };
 
   // payload ids of this thread's slice, fetched now so the compaction does not wait on them
   const bool pre = in_idx != nullptr && cpt == 1;
-  int32_t pay[8];
+  int32_t pay[KPC];
   if (pre) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) pay[j] = c0 * 8 + j < n ? __ldg(in_idx + c0 * 8 + j) : 0;
+    for (int j = 0; j < KPC; ++j) pay[j] = c0 * KPC + j < n ? __ldg(in_idx + c0 * KPC + j) : 0;
   }
 
   uint32_t prefix = 0, kk = k;
 #pragma unroll 1
   for (int pass = 0; pass < 4; ++pass) {
     const uint32_t shift = 12 - 4 * pass;
-    uint64_t cw0 = 0, cw1 = 0, cw2 = 0, cw3 = 0;
-    for (uint32_t c = c0; c < c1; ++c) {
-      const uint4 v = kv[c];
-      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    TOPK_STAMP(pass * 8 + 0);
+    // 16 bins as 8-bit fields of 4 words, flushed to 16-bit fields (8 words) every 31 chunks
+    uint32_t acc16[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const uint32_t key = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-        const bool match = pass == 0 || (key >> (shift + 4)) == prefix;
-        const uint32_t d = (key >> shift) & 15u;
-        const uint64_t inc = match ? (1ull << ((d & 3u) * 16)) : 0ull;
-        const uint32_t q = d >> 2;
-        cw0 += q == 0 ? inc : 0ull;
-        cw1 += q == 1 ? inc : 0ull;
-        cw2 += q == 2 ? inc : 0ull;
-        cw3 += q == 3 ? inc : 0ull;
+    for (int x = 0; x < 8; ++x) acc16[x] = 0;
+    for (uint32_t cb = c0; cb < c1; cb += 31) {
+      uint32_t c8[4] = {0, 0, 0, 0};
+      const uint32_t ce = min(cb + 31, c1);
+      for (uint32_t c = cb; c < ce; ++c) {
+        uint32_t w[WPC];
+        load_chunk(c, w);
+#pragma unroll
+        for (int j = 0; j < KPC; ++j) {
+          const uint32_t key = (j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xffffu);
+          const bool match = pass == 0 || (key >> (shift + 4)) == prefix;
+          const uint32_t d = (key >> shift) & 15u;
+          const uint32_t inc = match ? (1u << ((d & 3u) * 8)) : 0u;
+          const uint32_t q = d >> 2;
+          c8[0] += q == 0 ? inc : 0u;
+          c8[1] += q == 1 ? inc : 0u;
+          c8[2] += q == 2 ? inc : 0u;
+          c8[3] += q == 3 ? inc : 0u;
+        }
+      }
+#pragma unroll
+      for (int x = 0; x < 4; ++x) {  // word x holds bins 4x..4x+3
+        acc16[2 * x] += c8[x] & 0x00ff00ffu;             // bins 4x (low half), 4x+2 (high half)
+        acc16[2 * x + 1] += (c8[x] >> 8) & 0x00ff00ffu;  // bins 4x+1, 4x+3
       }
     }
+    TOPK_STAMP(pass * 8 + 1);
     // warp totals: the packed 16-bit fields add without carries (a warp sees < 65536 keys), so 8 REDUX do 16 bins
     uint32_t mine = 0;
 #pragma unroll
     for (int x = 0; x < 8; ++x) {
-      const uint64_t cw = (x >> 1) == 0 ? cw0 : (x >> 1) == 1 ? cw1 : (x >> 1) == 2 ? cw2 : cw3;
-      const uint32_t tot = __reduce_add_sync(0xffffffffu, (uint32_t)(cw >> ((x & 1) * 32)));
+      const uint32_t tot = __reduce_add_sync(0xffffffffu, acc16[x]);
       if (lane == (uint32_t)x) mine = tot;
     }
-    if (lane < 8) sc->hist[pass & 1][warp][lane] = mine;  // word x = bins 2x (low half), 2x+1 (high half)
+    TOPK_STAMP(pass * 8 + 2);
+    if (lane < 8) sc->hist[pass & 1][warp][lane] = mine;
     group_bar(bar_id, T);
+    TOPK_STAMP(pass * 8 + 3);
+    // lane b < 16 gathers bin b: word 2*(b/4) + (b&1), half (b>>1)&1
     uint32_t s = 0;
     if (lane < 16) {
+      const uint32_t word = 2 * (lane >> 2) + (lane & 1), sh = ((lane >> 1) & 1) * 16;
 #pragma unroll
-      for (int w2 = 0; w2 < W; ++w2) s += (sc->hist[pass & 1][w2][lane >> 1] >> ((lane & 1) * 16)) & 0xffffu;
+      for (int w2 = 0; w2 < W; ++w2) s += (sc->hist[pass & 1][w2][word] >> sh) & 0xffffu;
     }
+    TOPK_STAMP(pass * 8 + 4);
     // above = sum of bins higher than mine (lanes 16..31 carry zeros)
     uint32_t suf = s;
 #pragma unroll
@@ -96,18 +256,20 @@ __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, ui
     const uint32_t b = __ffs(__ballot_sync(0xffffffffu, hit)) - 1;  // exactly one lane hits while 1 <= kk <= candidates
     kk -= __shfl_sync(0xffffffffu, above, b);
     prefix = (prefix << 4) | b;
+    TOPK_STAMP(pass * 8 + 5);
+    if (dbg == 3 + (uint32_t)pass) { if (prefix == 0xfffff) out_idx[0] = 1; return; }
   }
   const uint32_t tau = prefix, need = kk;
 
   // stable compaction over the blocked ownership
   uint32_t ngt = 0, neq = 0;
   for (uint32_t c = c0; c < c1; ++c) {
-    const uint4 v = kv[c];
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t w[WPC];
+    load_chunk(c, w);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const uint32_t key = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-      const bool in = c * 8 + j < n;
+    for (int j = 0; j < KPC; ++j) {
+      const uint32_t key = (j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xffffu);
+      const bool in = c * KPC + j < n;
       ngt += in && key > tau;
       neq += in && key == tau;
     }
@@ -127,6 +289,7 @@ __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, ui
     sc->weq[warp] = seq;
   }
   group_bar(bar_id, T);
+  if (dbg == 7) { if (sgt == 0xfffff) out_idx[0] = 1; return; }
   uint32_t gt_before = sgt - ngt, eq_before = seq - neq;
 #pragma unroll
   for (int w2 = 0; w2 < W; ++w2) {
@@ -136,12 +299,12 @@ __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, ui
     }
   }
   for (uint32_t c = c0; c < c1; ++c) {
-    const uint4 v = kv[c];
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t w[WPC];
+    load_chunk(c, w);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const uint32_t key = (w[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-      const uint32_t i = c * 8 + j;
+    for (int j = 0; j < KPC; ++j) {
+      const uint32_t key = (j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xffffu);
+      const uint32_t i = c * KPC + j;
       const bool in = i < n;
       const bool gt = in && key > tau, eq = in && key == tau;
       if (gt || (eq && eq_before < need)) {

@@ -155,7 +155,7 @@ def run_topk(scores, payload, k):
     return dout.cpu().numpy(), iout.cpu().numpy()
 
 
-@pytest.mark.parametrize("n,k", [(13, 2), (24, 24), (77, 19), (311, 69), (1110, 251), (2047, 127), (2047, 1),
+@pytest.mark.parametrize("n,k", [(13, 2), (24, 24), (77, 19), (311, 69), (1024, 1024), (1025, 7), (1110, 251), (2047, 127), (2047, 1), (2048, 2048), (3001, 640), (4096, 1), (4097, 333),
                                  (8191, 255), (8192, 4095), (65535, 511)])
 @pytest.mark.parametrize("dist", ["normal", "ties", "const"])
 def test_topk_exact(n, k, dist):
