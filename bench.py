@@ -154,7 +154,7 @@ class Workload:
         torch.cuda.synchronize()
 
     # -- device-resident path: straight C-ABI calls, pointers precomputed, capturable in a CUDA graph
-    def make_raw_step(self, parts=("append", "estimate", "topk", "decode")):
+    def make_raw_step(self, parts=("append", "step")):
         import quest_b200._kernels as K
         lib = K.load_library()
         ic = self.ic
@@ -162,7 +162,10 @@ class Workload:
         assert lib.quest_decode_plan(K_SEL, H, H, D, P, torch.cuda.get_device_properties(self.dev).multi_processor_count,
                                      ctypes.byref(ppc), ctypes.byref(nch)) == 0
         self.plan = (ppc.value, nch.value)
-        self.ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, nch.value), dtype=torch.uint8, device=self.dev)
+        sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
+        # sized for both the stand-alone decode plan and the fused layer-step kernel (2 CTAs/SM shared by the heads)
+        self.ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, max(nch.value, 2 * sms // H)), dtype=torch.uint8,
+                              device=self.dev)
         kvi, mi = ic.kv_indices_with_last, ic.metadata_indices
         n_meta = mi.numel()
         kv_last_len, meta_last_len = ic.kv_cache.last_page_len, ic.metadata_cache.last_page_len
@@ -179,6 +182,10 @@ class Workload:
                 calls.append((lib.quest_estimate, (q, s, N_SCORED, mp, mi.data_ptr(), H, H, D, P, 3)))  # QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED
             if "topk" in parts:
                 calls.append((lib.quest_topk, (s, kvi.data_ptr(), 0, None, ti, H, N_SCORED, K_SEL)))
+            if "step" in parts:  # estimate + top-k + decode in one call (one persistent kernel, csrc/fused.cu)
+                calls.append((lib.quest_sparse_decode_step, (q, o, kvp, kvi.data_ptr(), N_SCORED, last_idx, kv_last_len, mp,
+                                                             mi.data_ptr(), s, ti, K_SEL, H, H, D, P, ppc.value,
+                                                             self.ws.data_ptr(), self.ws.numel())))
             if "decode" in parts:
                 calls.append((lib.quest_decode_run, (q, o, None, kvp, ti, K_SEL, K_SEL, last_idx, kv_last_len, H, H, D, P,
                                                      ppc.value, self.ws.data_ptr(), self.ws.numel())))
@@ -268,26 +275,32 @@ def main():
     wl = Workload(dev, 1234 + rank)
 
     step, launches_per_step = wl.make_raw_step()
-    step()  # eager once: validates return codes
+    lib.quest_launch_count_reset()
+    step()  # eager once: validates return codes and counts the kernels one step launches
     torch.cuda.synchronize()
+    kernels_per_step = int(lib.quest_launch_count())
     g = graph_of(step)
     sampler = ClockSampler(local) if rank == 0 else None
     lib.quest_launch_count_reset()
     sec = timed(g.replay, args.steps, args.warmup, dist_on)
     clocks = sampler.stop() if sampler else None
     sec_eager = timed(step, args.steps, args.warmup, dist_on)
-    gpu_launches = launches_per_step * args.steps  # graph replays of the captured launches
+    gpu_launches = kernels_per_step * args.steps  # graph replays of the captured kernel launches
 
     # per-kernel device time (graph of that kernel alone over the 32 layer pools), for the roofline
     kern = {}
-    for name, nbytes in (("estimate", BYTES_ESTIMATE), ("topk", BYTES_TOPK), ("decode", BYTES_DECODE), ("append", BYTES_APPEND)):
+    for name, nbytes in (("step", BYTES_STEP), ("estimate", BYTES_ESTIMATE), ("topk", BYTES_TOPK), ("decode", BYTES_DECODE),
+                         ("append", BYTES_APPEND)):
         st, n = wl.make_raw_step(parts=(name,))
         gk = graph_of(st)
         t = timed(gk.replay, args.steps, 3, dist_on) / (args.steps * n)
         kern[name] = {"us": t * 1e6, "GBps": nbytes / t / 1e9}
     peak, peak_kind = peaks()
-    dom = max(("estimate", "decode"), key=lambda k_: kern[k_]["us"])
-    dom_bytes = {"estimate": BYTES_ESTIMATE, "decode": BYTES_DECODE}[dom]
+    fused = os.environ.get("QUEST_FUSED", "1") != "0"
+    dom = "step" if fused else max(("estimate", "decode"), key=lambda k_: kern[k_]["us"])
+    dom_bytes = {"step": BYTES_STEP, "estimate": BYTES_ESTIMATE, "decode": BYTES_DECODE}[dom]
+    dom_name = {"step": "fused_step_kernel (estimate + top-k + decode + merge)", "estimate": "estimate_tile_kernel",
+                "decode": "decode_kernel"}[dom]
 
     sec_e2e = timed(wl.e2e_step, max(3, args.steps // 5), 3, dist_on) / max(3, args.steps // 5)
 
@@ -304,12 +317,12 @@ def main():
         "vs_baseline": None, "dtype": "f16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "step": "one token: 32 layers x (append_kv + estimate + top-k + sparse decode), "
                    "decode position 32768 repeated", "l2": "inputs larger than L2: 32 layer pools (17.4 GB) rotated every launch",
-                   "launch": "CUDA graph of 128 C-ABI launches, PDL-chained", "parallelism": f"batch-sharded x{world}, no collective",
+                   "launch": f"CUDA graph of {launches_per_step} C-ABI calls (append_kv + fused layer step per layer), {kernels_per_step} kernels", "parallelism": f"batch-sharded x{world}, no collective",
                    "algorithmic_bytes_per_layer": BYTES_STEP, "decode_plan_pages_per_chunk": wl.plan[0]},
         "frac_of_hbm_peak": BYTES_STEP / (us_layer * 1e-6) / 1e9 / peak,
         "eager_us_per_layer": sec_eager / args.steps * 1e6 / L,
         "kernels": kern,
-        "roofline": {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "peak_kind": peak_kind,
+        "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": kern[dom]["GBps"], "peak": peak, "peak_kind": peak_kind,
                      "unit": "GB/s", "frac": kern[dom]["GBps"] / peak, "traffic": None,
                      "algorithmic_bytes_per_launch": dom_bytes},
         "e2e": {"value": world * BYTES_STEP * L / sec_e2e / 1e9, "unit": UNIT, "ms_per_step": sec_e2e * 1e3,

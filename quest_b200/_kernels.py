@@ -12,7 +12,8 @@ from typing import Optional
 
 import torch
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libquest_b200.so")
+# QUEST_B200_LIB selects another build of the same library (e.g. the instrumented libquest_b200_dbg.so of tools/)
+_LIB_PATH = os.environ.get("QUEST_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libquest_b200.so")
 
 _c = ctypes
 _vp, _u32, _i32p, _f32, _sz = _c.c_void_p, _c.c_uint32, _c.c_void_p, _c.c_float, _c.c_size_t

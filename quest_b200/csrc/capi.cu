@@ -7,6 +7,11 @@
 
 namespace quest {
 unsigned long long g_launch_count = 0;
+int launch_fused_step(const void* q, void* o, const void* kv_data, const int32_t* kv_indices, uint32_t len,
+                      uint32_t last_page_idx, uint32_t last_page_len, const void* meta_data,
+                      const int32_t* meta_indices, void* scores, int32_t* topk_idx, uint32_t k, uint32_t Hq,
+                      uint32_t Hkv, uint32_t D, uint32_t P, void* workspace, size_t workspace_bytes, uint32_t flags,
+                      cudaStream_t stream);  // fused.cu
 int pdl_enabled() {
   static int v = -1;
   if (v < 0) {
@@ -30,7 +35,12 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
                                         void* stream) {
   if (!kv_indices || !scores || !topk_idx) return QUEST_ERR_BAD_ARG;
   if (k > len) return QUEST_ERR_BAD_ARG;
-  int rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+  // one persistent kernel when the shape allows it (fused.cu), else the three stand-alone kernels
+  int rc = quest::launch_fused_step(q, o, kv_data, kv_indices, len, last_page_idx, last_page_len, meta_data, meta_indices,
+                                    scores, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, workspace,
+                                    workspace_bytes, QUEST_EST_META_ORDERED, (cudaStream_t)stream);
+  if (rc != QUEST_ERR_UNSUPPORTED) return rc;
+  rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                           QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, stream);
   if (rc) return rc;
   // payload ids = the sequence's page table, shared by all heads (row stride 0)

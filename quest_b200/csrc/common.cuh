@@ -80,6 +80,22 @@ __device__ __forceinline__ size_t nhd_off(size_t page, uint32_t slab, uint32_t e
 
 constexpr float kLog2e = 1.44269504088896340736f;
 
+// Decode workspace layout (caller-owned bytes, zero-filled once when allocated):
+//   [0, 4096)              sync words of the fused layer-step kernel (self-resetting)
+//   [4096, 4096 + 4*Hq)    one merge ticket per q head (self-resetting)
+//   ws_md_off(Hq)          fp32 (m, d) pairs [Hq][nchunks]
+//   ws_o_off(Hq, nchunks)  fp32 partial outputs [Hq][nchunks][D]
+// The zero-state words sit at fixed offsets so that launches with different chunk counts can share a workspace.
+constexpr size_t kWsSyncBytes = 4096;
+__host__ __device__ inline size_t ws_ticket_off() { return kWsSyncBytes; }
+__host__ __device__ inline size_t ws_md_off(uint32_t Hq) { return (kWsSyncBytes + (size_t)Hq * 4 + 255) & ~(size_t)255; }
+__host__ __device__ inline size_t ws_o_off(uint32_t Hq, uint32_t nchunks) {
+  return (ws_md_off(Hq) + (size_t)Hq * nchunks * 2 * sizeof(float) + 255) & ~(size_t)255;
+}
+__host__ __device__ inline size_t ws_bytes(uint32_t Hq, uint32_t D, uint32_t nchunks) {
+  return ws_o_off(Hq, nchunks) + (size_t)Hq * nchunks * D * sizeof(float);
+}
+
 }  // namespace quest
 
 #define QUEST_RETURN_LAUNCH()                         \

@@ -17,13 +17,7 @@ constexpr int kDecThreads = 128;
 constexpr int kDecWarps = kDecThreads / 32;
 constexpr float kNegBig = -1e30f;
 
-// workspace layout: [Hq*nchunks*D] fp32 o | [Hq*nchunks*2] fp32 (m,d) | [Hq] u32 tickets
-__host__ __device__ inline size_t ws_md_off(uint32_t Hq, uint32_t D, uint32_t nchunks) {
-  return (size_t)Hq * nchunks * D * sizeof(float);
-}
-__host__ __device__ inline size_t ws_ticket_off(uint32_t Hq, uint32_t D, uint32_t nchunks) {
-  return ws_md_off(Hq, D, nchunks) + (size_t)Hq * nchunks * 2 * sizeof(float);
-}
+// workspace layout: common.cuh (ws_ticket_off / ws_md_off / ws_o_off)
 
 // t / P for any page size: p_magic = ceil(2^32 / P) (0 for P == 1); exact while t < 2^32 / P.
 __host__ __device__ inline uint32_t div_magic(uint32_t P) { return P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P); }
@@ -204,9 +198,9 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     if (lse && tid == 0) lse[h] = M + lg2(dsum);
     return;
   }
-  float* ws_o = reinterpret_cast<float*>(ws);
-  float* ws_md = reinterpret_cast<float*>(ws + ws_md_off(Hq, D, nchunks));
-  uint32_t* ticket = reinterpret_cast<uint32_t*>(ws + ws_ticket_off(Hq, D, nchunks));
+  float* ws_o = reinterpret_cast<float*>(ws + ws_o_off(Hq, nchunks));
+  float* ws_md = reinterpret_cast<float*>(ws + ws_md_off(Hq));
+  uint32_t* ticket = reinterpret_cast<uint32_t*>(ws + ws_ticket_off());
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
     const uint32_t col = tid + c * kDecThreads;
@@ -352,7 +346,7 @@ extern "C" int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, 
 }
 
 extern "C" size_t quest_decode_workspace_bytes(uint32_t num_qo_heads, uint32_t head_dim, uint32_t num_chunks) {
-  return quest::ws_ticket_off(num_qo_heads, head_dim, num_chunks) + (size_t)num_qo_heads * sizeof(uint32_t);
+  return quest::ws_bytes(num_qo_heads, head_dim, num_chunks);
 }
 
 extern "C" int quest_decode_run(const void* q, void* o, float* lse, const void* kv_data, const int32_t* indices,

@@ -39,6 +39,10 @@ __device__ __forceinline__ uint64_t shl64_clamped(uint32_t s) {  // 1 << s, 0 fo
   return r;
 }
 
+#ifndef TOPK_FAST_STAMP
+#define TOPK_FAST_STAMP(i) do { } while (0)  // fused.cu's timeline build stamps the passes
+#endif
+
 template <int W>
 struct TopkFastScratch {
   uint8_t histT[2][16][W];  // [pass parity][bin][warp]: per-warp bin totals (<= 128 each)
@@ -55,7 +59,8 @@ template <int W>
 __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t n, uint32_t k, uint32_t t,
                                                  uint32_t bar_id, TopkFastScratch<W>* sc,
                                                  const int32_t* __restrict__ in_idx, int32_t* __restrict__ out_idx,
-                                                 uint16_t* __restrict__ out_val) {
+                                                 uint16_t* __restrict__ out_val,
+                                                 unsigned long long* publish = nullptr) {
   static_assert(W == 4 || W == 8 || W == 16 || W == 32, "W bytes per bin row are read as 32-bit words");
   constexpr uint32_t T = 32 * W;
   const uint32_t lane = t & 31, warp = t >> 5;
@@ -116,6 +121,7 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
     const uint32_t b = __ffs(__ballot_sync(0xffffffffu, hit)) - 1;
     kk -= __shfl_sync(0xffffffffu, above, b);
     prefix = (prefix << 4) | b;
+    TOPK_FAST_STAMP(pass);
   }
   const uint32_t tau = prefix, need = kk;
 
@@ -141,6 +147,18 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
   for (int w2 = 0; w2 < W; ++w2)
     if ((uint32_t)w2 < warp) before += sc->wgt[w2];
   uint32_t gt_before = before >> 16, eq_before = before & 0xffffu;
+  if (publish) {
+    // The selection as one word, for consumers that hold the keys themselves (fused.cu): position i is selected
+    // iff key > tau or (key == tau and i < tie_cut).  Written by the thread that owns the need-th tie (need >= 1).
+    uint32_t e = eq_before;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (i0 + j < n && key[j] == tau && ++e == need) {
+        const unsigned long long w = (1ull << 63) | ((unsigned long long)(i0 + j + 1) << 16) | tau;
+        asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(publish), "l"(w) : "memory");
+      }
+    }
+  }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     const bool in = i0 + j < n;
