@@ -55,12 +55,19 @@ struct TopkFastScratch {
 // 64-bit shifts and added into 4 words (fields cannot carry: a thread adds at most 4, a warp at most 128, so
 // REDUX runs on the 8-bit fields directly); bin totals are published transposed so that lane b sums its bin
 // over all warps with one 128-bit load and dp4a.
-template <int W>
+// Hook: called by every thread of the group once the selection is decided and before the ids are written, with
+// the selection as one word for consumers that hold the keys themselves (fused.cu): position i is selected iff
+// key > tau or (key == tau and i < tie_cut); word = 1<<63 | tie_cut<<16 | tau.  `holder` is true for the one thread
+// that owns the need-th tie (need >= 1 always), which is the thread that knows tie_cut.
+struct TopkNoHook {
+  __device__ __forceinline__ void operator()(bool, unsigned long long) const {}
+};
+
+template <int W, class Hook = TopkNoHook>
 __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t n, uint32_t k, uint32_t t,
                                                  uint32_t bar_id, TopkFastScratch<W>* sc,
                                                  const int32_t* __restrict__ in_idx, int32_t* __restrict__ out_idx,
-                                                 uint16_t* __restrict__ out_val,
-                                                 unsigned long long* publish = nullptr) {
+                                                 uint16_t* __restrict__ out_val, Hook hook = Hook()) {
   static_assert(W == 4 || W == 8 || W == 16 || W == 32, "W bytes per bin row are read as 32-bit words");
   constexpr uint32_t T = 32 * W;
   const uint32_t lane = t & 31, warp = t >> 5;
@@ -147,17 +154,12 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
   for (int w2 = 0; w2 < W; ++w2)
     if ((uint32_t)w2 < warp) before += sc->wgt[w2];
   uint32_t gt_before = before >> 16, eq_before = before & 0xffffu;
-  if (publish) {
-    // The selection as one word, for consumers that hold the keys themselves (fused.cu): position i is selected
-    // iff key > tau or (key == tau and i < tie_cut).  Written by the thread that owns the need-th tie (need >= 1).
-    uint32_t e = eq_before;
+  {
+    uint32_t e = eq_before, cut = 0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (i0 + j < n && key[j] == tau && ++e == need) {
-        const unsigned long long w = (1ull << 63) | ((unsigned long long)(i0 + j + 1) << 16) | tau;
-        asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(publish), "l"(w) : "memory");
-      }
-    }
+    for (int j = 0; j < 4; ++j)
+      if (i0 + j < n && key[j] == tau && ++e == need) cut = i0 + j + 1;
+    hook(cut != 0, (1ull << 63) | ((unsigned long long)cut << 16) | tau);
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {

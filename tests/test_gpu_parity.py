@@ -276,8 +276,8 @@ def test_layer_step_matches_oracle(kv_len, budget):
                                                (16, 9000, 100, 16), (8, 4000, 17, 16), (32, 5000, 8, 8), (32, 40, 2, 16),
                                                (32, 32768 + 16 * 300, 128, 16), (4, 3000, 16, 16), (32, 3000, 16, 32)])
 def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
-    """quest_sparse_decode_step (one persistent kernel where the shape allows, fused.cu) against the three operator calls:
-    scores and selected pages bit-exact, attention within tolerance (the merge is chunked differently)."""
+    """quest_sparse_decode_step against the three operator calls: scores and selected pages bit-exact, attention within
+    tolerance (the experimental cluster kernel of fused.cu, QUEST_FUSED=1|2, chunks the merge differently)."""
     D = 128
     oc, gc, k, v, rng = make_pair(kv_len, P, H, D, seed=11 + H + budget)
     q = rng.standard_normal((1, H, D), dtype=np.float32).astype(np.float16)
