@@ -151,10 +151,11 @@ class Workload:
         self.d_out = torch.empty(L, 1, H, D, dtype=torch.float16, device=dev)
         self.scores = torch.empty(L, H, N_SCORED, dtype=torch.float16, device=dev)
         self.topk = torch.zeros(L, H, K_SEL, dtype=torch.int32, device=dev)
+        self.e2e_views = [(self.d_qkv[0, l], self.d_qkv[1, l], self.d_qkv[2, l], self.d_out[l]) for l in range(L)]
         torch.cuda.synchronize()
 
     # -- device-resident path: straight C-ABI calls, pointers precomputed, capturable in a CUDA graph
-    def make_raw_step(self, parts=("append", "step")):
+    def make_raw_step(self, parts=("layer",)):
         import quest_b200._kernels as K
         lib = K.load_library()
         ic = self.ic
@@ -175,6 +176,10 @@ class Workload:
             kvp, mp = ic.kv_cache.buf_layer(l).data_ptr(), ic.metadata_cache.buf_layer(l).data_ptr()
             q, k, v = (self.d_qkv[i, l].data_ptr() for i in range(3))
             o, s, ti = self.d_out[l].data_ptr(), self.scores[l].data_ptr(), self.topk[l].data_ptr()
+            if "layer" in parts:  # the whole layer step in one C call: append carried by the estimate kernel, top-k, decode
+                calls.append((lib.quest_decode_layer_step, (q, k, v, o, kvp, kvi.data_ptr(), N_PAGES, last_idx, kv_last_len, mp,
+                                                            mi.data_ptr(), n_meta, meta_last_len, s, ti, K_SEL, H, H, D, P,
+                                                            ppc.value, self.ws.data_ptr(), self.ws.numel())))
             if "append" in parts:
                 calls.append((lib.quest_append_decode, (k, v, kvp, kvi.data_ptr(), N_PAGES, kv_last_len, mp, mi.data_ptr(),
                                                         n_meta, meta_last_len, H, D, P)))
@@ -204,13 +209,19 @@ class Workload:
         self.d_qkv.copy_(self.h_qkv, non_blocking=True)
         ic.begin_forward(1)
         for l in range(L):
-            q, k, v = self.d_qkv[0, l], self.d_qkv[1, l], self.d_qkv[2, l]
-            qu.append_kv(k, v, ic, l)
-            s = qu.decode_estimate(q, ic, l)
-            qu.decode_topk(s, ic)
-            self.d_out[l] = qu.decode_sparse_attn(q, ic, l, ic.topk_dindices_buffer)
+            q, k, v, out = self.e2e_views[l]
+            if E2E_FOUR_OPS:  # the reference's call sequence (QuestAttention.py:100-150), op by op
+                qu.append_kv(k, v, ic, l)
+                s = qu.decode_estimate(q, ic, l)
+                qu.decode_topk(s, ic)
+                self.d_out[l] = qu.decode_sparse_attn(q, ic, l, ic.topk_dindices_buffer)
+            else:             # the same four ops as one native call
+                qu.decode_layer_step(q, k, v, ic, l, out=out)
         ic.end_forward()
         self.h_out.copy_(self.d_out, non_blocking=True)
+
+
+E2E_FOUR_OPS = os.environ.get("QUEST_E2E_FOUR_OPS", "0") == "1"
 
 
 def timed(fn, steps, warmup, dist_on):
@@ -289,18 +300,15 @@ def main():
 
     # per-kernel device time (graph of that kernel alone over the 32 layer pools), for the roofline
     kern = {}
-    for name, nbytes in (("step", BYTES_STEP), ("estimate", BYTES_ESTIMATE), ("topk", BYTES_TOPK), ("decode", BYTES_DECODE),
-                         ("append", BYTES_APPEND)):
+    for name, nbytes in (("estimate", BYTES_ESTIMATE), ("topk", BYTES_TOPK), ("decode", BYTES_DECODE), ("append", BYTES_APPEND)):
         st, n = wl.make_raw_step(parts=(name,))
         gk = graph_of(st)
         t = timed(gk.replay, args.steps, 3, dist_on) / (args.steps * n)
         kern[name] = {"us": t * 1e6, "GBps": nbytes / t / 1e9}
     peak, peak_kind = peaks()
-    fused = os.environ.get("QUEST_FUSED", "1") != "0"
-    dom = "step" if fused else max(("estimate", "decode"), key=lambda k_: kern[k_]["us"])
-    dom_bytes = {"step": BYTES_STEP, "estimate": BYTES_ESTIMATE, "decode": BYTES_DECODE}[dom]
-    dom_name = {"step": "fused_step_kernel (estimate + top-k + decode + merge)", "estimate": "estimate_tile_kernel",
-                "decode": "decode_kernel"}[dom]
+    dom = max(("estimate", "decode"), key=lambda k_: kern[k_]["us"])
+    dom_bytes = {"estimate": BYTES_ESTIMATE, "decode": BYTES_DECODE}[dom]
+    dom_name = {"estimate": "estimate_tile_kernel", "decode": "decode_kernel"}[dom]
 
     sec_e2e = timed(wl.e2e_step, max(3, args.steps // 5), 3, dist_on) / max(3, args.steps // 5)
 
@@ -317,7 +325,8 @@ def main():
         "vs_baseline": None, "dtype": "f16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "step": "one token: 32 layers x (append_kv + estimate + top-k + sparse decode), "
                    "decode position 32768 repeated", "l2": "inputs larger than L2: 32 layer pools (17.4 GB) rotated every launch",
-                   "launch": f"CUDA graph of {launches_per_step} C-ABI calls (append_kv + fused layer step per layer), {kernels_per_step} kernels", "parallelism": f"batch-sharded x{world}, no collective",
+                   "launch": f"CUDA graph of {launches_per_step} quest_decode_layer_step calls = {kernels_per_step} kernels (estimate carrying the "
+                             "append, top-k, decode per layer), chained with programmatic dependent launch", "parallelism": f"batch-sharded x{world}, no collective",
                    "algorithmic_bytes_per_layer": BYTES_STEP, "decode_plan_pages_per_chunk": wl.plan[0]},
         "frac_of_hbm_peak": BYTES_STEP / (us_layer * 1e-6) / 1e9 / peak,
         "eager_us_per_layer": sec_eager / args.steps * 1e6 / L,
@@ -327,7 +336,8 @@ def main():
                      "algorithmic_bytes_per_launch": dom_bytes},
         "e2e": {"value": world * BYTES_STEP * L / sec_e2e / 1e9, "unit": UNIT, "ms_per_step": sec_e2e * 1e3,
                 "h2d_bytes_per_step": wl.h_qkv.numel() * 2, "d2h_bytes_per_step": wl.h_out.numel() * 2,
-                "path": "quest_b200.utils operator surface (controller + 4 ops/layer), pinned host q/k/v in, o out"},
+                "path": "quest_b200.utils operator surface (controller + " + ("4 ops/layer" if E2E_FOUR_OPS else "decode_layer_step/layer")
+                        + "), pinned host q/k/v in, o out"},
         "gpu_launches": gpu_launches,
         "clocks": clocks,
     }

@@ -143,6 +143,24 @@ int quest_sparse_decode_step(const void* q, void* o,
                              uint32_t page_size, uint32_t pages_per_chunk,
                              void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- one decode step of one layer ---------------------------------------------------------------
+ * append_kv + estimate + top-k + sparse decode in one call: the four operator calls of
+ * quest/models/QuestAttention.py:100-150 (append_kv, decode_estimate, decode_topk, decode_sparse_attn;
+ * quest/utils/__init__.py:137-276).  k_new, v_new: [num_kv_heads, head_dim] of the new token; the page tables
+ * and lengths already count it (as for quest_append_decode); kv_last_page_idx = kv_indices[num_kv_pages-1]
+ * as a host value (the reference passes it the same way, controller.py:86-87).  k pages are selected among
+ * the num_kv_pages-1 full pages (k = 0: attend to the last page only); scores [num_qo_heads, num_kv_pages-1]
+ * fp16 and topk_idx [num_qo_heads, k] are outputs.  The append rides on the estimate kernel (3 launches). */
+int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new, void* o,
+                            void* kv_data, const int32_t* kv_indices, uint32_t num_kv_pages,
+                            uint32_t kv_last_page_idx, uint32_t kv_last_page_len,
+                            void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                            uint32_t meta_last_page_len,
+                            void* scores, int32_t* topk_idx, uint32_t k,
+                            uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                            uint32_t page_size, uint32_t pages_per_chunk,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- paged causal prefill ----------------------------------------------------------------------
  * Replaces prefill_with_paged_kv_cache (bsk_ops.h:78-86, batch_prefill.cu:27-117, prefill.cuh:674-1115).
  * q, o: [qo_len, num_qo_heads, head_dim]; the KV sequence is the num_kv_pages pages of kv_indices

@@ -32,6 +32,8 @@ SIGNATURES = {
     "quest_decode_workspace_bytes": (_sz, [_u32, _u32, _u32]),
     "quest_decode_run": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_sparse_decode_step": (_c.c_int, [_vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
+    "quest_decode_layer_step": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32,
+                                           _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _c.c_int, _u32, _u32, _u32, _u32, _vp]),
     "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _vp, _vp, _u32, _u32, _vp]),
     "quest_launch_count": (_c.c_uint64, []),
@@ -303,3 +305,35 @@ class BatchDecodeWithPagedKVCachePyTorchWrapper:
                                             paged_kv_indices.data_ptr(), stride, n_sel, int(paged_kv_last_page_idx),
                                             int(paged_kv_last_page_len), Hq, Hkv, D, P, ppc, self._ws.data_ptr(),
                                             self._ws.numel(), _stream()), "BatchDecodeWithPagedKVCache")
+
+    def layer_step_args(self, q, k, v, o, kv_data, kv_indices, kv_last_page_len, kv_last_page_idx, metadata_data,
+                        metadata_indices, metadata_last_page_len, scores, topk_indices):
+        """Validates a layer step and returns the argument tuple of quest_decode_layer_step (without the stream)."""
+        if self._plan is None:
+            raise RuntimeError("BatchDecodeWithPagedKVCache: layer_step() called before begin_forward()")
+        for t_, n_ in ((q, "q"), (k, "k"), (v, "v"), (o, "o"), (kv_data, "kv_data"), (kv_indices, "kv_indices"),
+                       (metadata_data, "metadata_data"), (metadata_indices, "metadata_indices"), (scores, "scores"),
+                       (topk_indices, "topk_indices")):
+            _check_input(t_, n_)
+        P, Hkv, D = _pool_dims(kv_data, "kv_data")
+        _check(_pool_dims(metadata_data, "metadata_data") == (P, Hkv, D), "metadata_data must share page_size/heads/dim with kv_data")
+        Hq = q.size(1)
+        n_pages, n_sel = kv_indices.size(0), self._plan[0]
+        _check(q.dim() == 3 and q.size(0) == 1 and q.size(2) == D, "q must be [1, num_qo_heads, head_dim]")
+        _check(k.shape == (1, Hkv, D) and v.shape == k.shape, "k, v must be [1, num_kv_heads, head_dim]")
+        _check(kv_indices.dtype == torch.int32 and metadata_indices.dtype == torch.int32 and topk_indices.dtype == torch.int32,
+               "page tables and topk_indices must be int32")
+        _check(tuple(scores.shape) == (Hq, n_pages - 1), "scores must be [num_qo_heads, num_kv_pages - 1]")
+        _check(tuple(topk_indices.shape) == (Hq, n_sel), "topk_indices must be [num_qo_heads, planned num_pages]")
+        _check_half(q, "decode_layer_step")
+        ppc, _ = self._planned(n_sel, Hq, Hkv, D, P, q.device)
+        return (q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), kv_data.data_ptr(), kv_indices.data_ptr(), n_pages,
+                int(kv_last_page_idx), int(kv_last_page_len), metadata_data.data_ptr(), metadata_indices.data_ptr(),
+                metadata_indices.size(0), int(metadata_last_page_len), scores.data_ptr(), topk_indices.data_ptr(), n_sel,
+                Hq, Hkv, D, P, ppc, self._ws.data_ptr(), self._ws.numel())
+
+    def layer_step(self, *tensors_and_ints):
+        """append_kv_cache_decode + estimate_attn_score + topk_filtering + forward in one C call
+        (quest_decode_layer_step: the append rides on the estimate kernel).  Same tensors as those four ops take
+        (see layer_step_args); begin_forward must have planned num_pages = topk_indices.size(1)."""
+        _rc(load_library().quest_decode_layer_step(*self.layer_step_args(*tensors_and_ints), _stream()), "decode_layer_step")

@@ -12,6 +12,9 @@ int launch_fused_step(const void* q, void* o, const void* kv_data, const int32_t
                       const int32_t* meta_indices, void* scores, int32_t* topk_idx, uint32_t k, uint32_t Hq,
                       uint32_t Hkv, uint32_t D, uint32_t P, void* workspace, size_t workspace_bytes, uint32_t flags,
                       cudaStream_t stream);  // fused.cu
+int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
+                      uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                      uint32_t flags, const AppendArgs& ap, cudaStream_t s);  // estimate.cu
 int pdl_enabled() {
   static int v = -1;
   if (v < 0) {
@@ -48,4 +51,42 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
   if (rc) return rc;
   return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, last_page_idx, last_page_len, num_qo_heads,
                           num_kv_heads, head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
+}
+
+// One decode step of one layer: append_kv + estimate + top-k + sparse decode (the four calls of
+// quest/models/QuestAttention.py:100-150 in the reference).  The append rides on the estimate kernel's first CTA, so
+// the step is three launches.
+extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new, void* o, void* kv_data,
+                                       const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_idx,
+                                       uint32_t kv_last_page_len, void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                                       uint32_t meta_last_page_len, void* scores, int32_t* topk_idx, uint32_t k,
+                                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                                       uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+  if (!q || !k_new || !v_new || !o || !kv_data || !kv_indices || !meta_data || !meta_indices) return QUEST_ERR_BAD_ARG;
+  if (!num_kv_pages || !num_meta_pages || !num_qo_heads || !num_kv_heads || !page_size) return QUEST_ERR_BAD_ARG;
+  if (num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
+  if (kv_last_page_len < 1 || kv_last_page_len > page_size || meta_last_page_len < 1 || meta_last_page_len > page_size)
+    return QUEST_ERR_BAD_ARG;
+  if (num_meta_pages != (num_kv_pages + page_size - 1) / page_size ||
+      meta_last_page_len != (num_kv_pages - 1) % page_size + 1)
+    return QUEST_ERR_BAD_ARG;  // one metadata entry per KV page
+  const uint32_t len = num_kv_pages - 1;  // scored pages: all but the last
+  if (k > len || (k && (!scores || !topk_idx))) return QUEST_ERR_BAD_ARG;
+  quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, (__half*)kv_data, kv_indices, (__half*)meta_data,
+                          num_kv_pages, kv_last_page_len, num_meta_pages, meta_last_page_len};
+  int rc;
+  if (k == 0) {  // nothing to select: attend to the last page only
+    rc = quest_append_decode(k_new, v_new, kv_data, kv_indices, num_kv_pages, kv_last_page_len, meta_data, meta_indices,
+                             num_meta_pages, meta_last_page_len, num_kv_heads, head_dim, page_size, stream);
+  } else {
+    rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+                                  QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream);
+    if (rc) return rc;
+    // payload ids = the sequence's page table, shared by all heads (row stride 0)
+    rc = quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
+  }
+  if (rc) return rc;
+  return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, kv_last_page_idx, kv_last_page_len, num_qo_heads, num_kv_heads,
+                          head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
 }

@@ -78,6 +78,69 @@ __device__ __forceinline__ size_t nhd_off(size_t page, uint32_t slab, uint32_t e
   return (((page * 2 + slab) * P + entry) * H + head) * (size_t)D;
 }
 
+__device__ __forceinline__ void h8_max(H8& a, const H8& b) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) a.h[i] = __hmax2(a.h[i], b.h[i]);
+}
+__device__ __forceinline__ void h8_min(H8& a, const H8& b) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) a.h[i] = __hmin2(a.h[i], b.h[i]);
+}
+__device__ __forceinline__ H8 h8_fill(float x) {
+  H8 r;
+  const __half2 v = __float2half2_rn(x);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) r.h[i] = v;
+  return r;
+}
+
+constexpr float kMaxHalf = 65504.f;  // CUDART_MAX_NORMAL_FP16 (decode_page.cuh:430-431)
+
+// append_kv of one token for one 16-byte column c of the [H*D] row: K/V rows into the last KV page, running
+// max/min into the last metadata entry (reference decode_page.cuh:398-449; -+65504 start for a page's first token).
+__device__ __forceinline__ void append_decode_column(const __half* __restrict__ k, const __half* __restrict__ v,
+                                                     __half* __restrict__ kv, const int32_t* __restrict__ kv_indices,
+                                                     uint32_t num_kv_pages, uint32_t kv_last_len, __half* __restrict__ meta,
+                                                     const int32_t* __restrict__ meta_indices, uint32_t num_meta_pages,
+                                                     uint32_t meta_last_len, uint32_t row_vecs /* H*D/8 */, uint32_t P,
+                                                     uint32_t c) {
+  const size_t row = (size_t)row_vecs * 8;  // H*D elements
+  const size_t page = (size_t)__ldg(kv_indices + num_kv_pages - 1);
+  const uint32_t entry = kv_last_len - 1;
+  const size_t mpage = (size_t)__ldg(meta_indices + num_meta_pages - 1);
+  const uint32_t mentry = meta_last_len - 1;
+  __half* kdst = kv + ((page * 2) * P + entry) * row + c * 8;
+  __half* vdst = kdst + (size_t)P * row;
+  __half* mxp = meta + ((mpage * 2) * P + mentry) * row + c * 8;
+  __half* mnp = mxp + (size_t)P * row;
+  const H8 kk = ld_plain(k + c * 8);
+  const H8 vv = ld_plain(v + c * 8);
+  H8 mx, mn;
+  if (entry > 0) {
+    mx = ld_plain(mxp);
+    mn = ld_plain(mnp);
+  } else {
+    mx = h8_fill(-kMaxHalf);
+    mn = h8_fill(kMaxHalf);
+  }
+  h8_max(mx, kk);
+  h8_min(mn, kk);
+  st_plain(kdst, kk);
+  st_plain(vdst, vv);
+  st_plain(mxp, mx);
+  st_plain(mnp, mn);
+}
+
+// Optional append_kv work carried by another kernel's first CTA (estimate.cu); k == nullptr: none.
+struct AppendArgs {
+  const __half* k;
+  const __half* v;
+  __half* kv;
+  const int32_t* kv_indices;
+  __half* meta;
+  uint32_t num_kv_pages, kv_last_len, num_meta_pages, meta_last_len;
+};
+
 constexpr float kLog2e = 1.44269504088896340736f;
 
 // Decode workspace layout (caller-owned bytes, zero-filled once when allocated):

@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(kTileWarps * 32, 2)
 estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t len,
                      const __half* __restrict__ meta, const int32_t* __restrict__ meta_indices,
                      uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_magic /* ceil(2^32/P), 0 for P=1 */,
-                     uint32_t meta_stable) {
+                     uint32_t meta_stable, const AppendArgs ap) {
   constexpr int LPR = D / 8, RPL = 32 / LPR, kThreads = kTileWarps * 32, kDepth = 4;
   constexpr uint32_t T_r = kTileWarps * RPL;  // metadata rows per CTA pass; Hkv divides T_r
   extern __shared__ __align__(16) uint8_t est_smem[];
@@ -176,12 +176,25 @@ estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
   const uint32_t rt = warp * RPL + rsub;                // this lane's row in the pass
   const uint32_t pg_in = rt / Hkv, kvh = rt - pg_in * Hkv;
   // contiguous page range of this CTA, balanced to one page
-  const uint32_t p_begin = (uint32_t)(((uint64_t)blockIdx.x * len) / gridDim.x);
-  const uint32_t p_end = (uint32_t)(((uint64_t)(blockIdx.x + 1) * len) / gridDim.x);
+  // with an append to carry, the last CTA does only that and the scan is shared by the others
+  const uint32_t n_scan = ap.k != nullptr ? gridDim.x - 1 : gridDim.x;
+  const bool scans = blockIdx.x < n_scan;
+  const uint32_t p_begin = scans ? (uint32_t)(((uint64_t)blockIdx.x * len) / n_scan) : 0u;
+  const uint32_t p_end = scans ? (uint32_t)(((uint64_t)(blockIdx.x + 1) * len) / n_scan) : 0u;
   const uint32_t row_bytes = Hkv * D * 2, slab_bytes = P * row_bytes;
   const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + (size_t)kvh * (D * 2) + lir * 16;
 
-  if (!meta_stable) pdl_wait();  // see QUEST_EST_META_STABLE
+  // append_kv of the step's new token rides on one extra CTA of this launch.  The entry it updates (the last
+  // page's) is not one of the scored ones; the decode kernel two launches later reads the new K/V row.
+  const bool carries_append = !scans;
+  if (!meta_stable || carries_append) pdl_wait();  // see QUEST_EST_META_STABLE
+  if (carries_append) {
+    const uint32_t row_vecs = Hkv * D / 8;
+    for (uint32_t c = tid; c < row_vecs; c += kThreads)
+      append_decode_column(ap.k, ap.v, ap.kv, ap.kv_indices, ap.num_kv_pages, ap.kv_last_len, ap.meta, meta_indices,
+                           ap.num_meta_pages, ap.meta_last_len, row_vecs, P, c);
+    return;
+  }
   for (uint32_t i = tid; i < n_meta; i += kThreads) idx_s[i] = __ldg(meta_indices + i);
   __syncthreads();
 
@@ -199,7 +212,7 @@ estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
 #pragma unroll
   for (int s = 0; s < kDepth; ++s) issue(s);
 
-  if (meta_stable) pdl_wait();
+  if (meta_stable && !carries_append) pdl_wait();
   float qv[8];
   uint32_t mk[4];
   if (kG == 1) {
@@ -305,7 +318,8 @@ estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
 
 template <int D>
 static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void* meta, const int32_t* meta_indices,
-                                uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t flags, cudaStream_t stream) {
+                                uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t flags, const AppendArgs& ap,
+                                cudaStream_t stream) {
   constexpr uint32_t T_r = kTileWarps * (32 / (D / 8));
   static int num_sms = 0;
   if (!num_sms) {
@@ -315,9 +329,10 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
     if (num_sms <= 0) num_sms = 148;
   }
   const uint32_t G = Hq / Hkv, PPP = T_r / Hkv;
-  uint32_t grid = 2 * num_sms;
+  uint32_t grid = 2 * num_sms - (ap.k != nullptr ? 1u : 0u);  // scanning CTAs
   const uint32_t need = (len + PPP - 1) / PPP;  // at least one pass of pages per CTA
   if (grid > need) grid = need;
+  if (ap.k != nullptr) ++grid;  // + the CTA that carries the append
   const uint32_t n_meta = (len + P - 1) / P;
   size_t smem = ((size_t)n_meta * 4 + 15) & ~(size_t)15;
   if (G != 1) smem += (size_t)Hq * D * 6;
@@ -341,7 +356,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   cfg.numAttrs = 1;
   const uint32_t p_magic = P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P);
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta, meta_indices,
-                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE);
+                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, ap);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -392,6 +407,44 @@ static int launch_estimate(const void* q, void* o, uint32_t len, const void* met
 
 }  // namespace quest
 
+namespace quest {
+// estimate, optionally carrying the step's append_kv (ap.k != nullptr) on the tile kernel's first CTA
+int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
+                      uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                      uint32_t flags, const AppendArgs& ap, cudaStream_t s) {
+  if ((size_t)num_qo_heads * head_dim * 6 > 160 * 1024) return QUEST_ERR_UNSUPPORTED;
+  {  // product path: the tile kernel, whenever the kv heads divide its row tile
+    const uint32_t T_r = kTileWarps * (32 / (head_dim / 8));
+    static int force_rows = -1;
+    if (force_rows < 0) {
+      const char* e = getenv("QUEST_EST_ROWS");  // test hook: exercise the generic kernel on shapes the tile kernel takes
+      force_rows = e && e[0] == '1';
+    }
+    if (!force_rows && len && T_r % num_kv_heads == 0 && (head_dim == 64 || head_dim == 128 || head_dim == 256)) {
+      switch (head_dim) {
+        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s);
+        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s);
+        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s);
+      }
+    }
+  }
+  if (ap.k != nullptr) {  // generic path: append as its own launch
+    const int rc = quest_append_decode(ap.k, ap.v, ap.kv, ap.kv_indices, ap.num_kv_pages, ap.kv_last_len, ap.meta,
+                                       meta_indices, ap.num_meta_pages, ap.meta_last_len, num_kv_heads, head_dim,
+                                       page_size, s);
+    if (rc) return rc;
+    flags &= ~QUEST_EST_META_STABLE;  // the kernel before the estimate now writes the metadata pool
+  }
+  if (len == 0) return QUEST_OK;
+  switch (head_dim) {
+    case 64: return launch_estimate<64, 448, 4>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
+    case 128: return launch_estimate<128, 448, 4>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
+    case 256: return launch_estimate<256, 448, 4>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
+    default: return QUEST_ERR_UNSUPPORTED;
+  }
+}
+}  // namespace quest
+
 extern "C" int quest_estimate(const void* q, void* o, uint32_t len, const void* meta_data,
                               const int32_t* meta_indices, uint32_t num_qo_heads, uint32_t num_kv_heads,
                               uint32_t head_dim, uint32_t page_size, uint32_t flags, void* stream) {
@@ -399,35 +452,7 @@ extern "C" int quest_estimate(const void* q, void* o, uint32_t len, const void* 
     return QUEST_ERR_BAD_ARG;
   if (num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
   if (len == 0) return QUEST_OK;
-  if ((size_t)num_qo_heads * head_dim * 6 > 160 * 1024) return QUEST_ERR_UNSUPPORTED;
-  cudaStream_t s = (cudaStream_t)stream;
-  {  // product path: the tile kernel, whenever the kv heads divide its row tile
-    const uint32_t T_r = quest::kTileWarps * (32 / (head_dim / 8));
-    static int force_rows = -1;
-    if (force_rows < 0) {
-      const char* e = getenv("QUEST_EST_ROWS");
-      force_rows = e && e[0] == '1';
-    }
-    if (!force_rows && T_r % num_kv_heads == 0 && (head_dim == 64 || head_dim == 128 || head_dim == 256)) {
-      switch (head_dim) {
-        case 64: return quest::launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-        case 128: return quest::launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-        default: return quest::launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-      }
-    }
-  }
-  static int cfg = -1;  // tuning hook: QUEST_EST_CFG selects the (threads, depth) variant for head_dim 128
-  if (cfg < 0) {
-    const char* e = getenv("QUEST_EST_CFG");
-    cfg = e ? atoi(e) : 0;
-  }
-  if (head_dim == 128 && cfg == 1) return quest::launch_estimate<128, 512, 3>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-  if (head_dim == 128 && cfg == 2) return quest::launch_estimate<128, 384, 4>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-  if (head_dim == 128 && cfg == 3) return quest::launch_estimate<128, 512, 4>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-  switch (head_dim) {
-    case 64: return quest::launch_estimate<64, 448, 4>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-    case 128: return quest::launch_estimate<128, 448, 4>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-    case 256: return quest::launch_estimate<256, 448, 4>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, s);
-    default: return QUEST_ERR_UNSUPPORTED;
-  }
+  quest::AppendArgs none = {};
+  return quest::estimate_dispatch(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+                                  flags, none, (cudaStream_t)stream);
 }

@@ -7,24 +7,6 @@
 
 namespace quest {
 
-__device__ __forceinline__ void h8_max(H8& a, const H8& b) {
-#pragma unroll
-  for (int i = 0; i < 4; ++i) a.h[i] = __hmax2(a.h[i], b.h[i]);
-}
-__device__ __forceinline__ void h8_min(H8& a, const H8& b) {
-#pragma unroll
-  for (int i = 0; i < 4; ++i) a.h[i] = __hmin2(a.h[i], b.h[i]);
-}
-__device__ __forceinline__ H8 h8_fill(float x) {
-  H8 r;
-  const __half2 v = __float2half2_rn(x);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) r.h[i] = v;
-  return r;
-}
-
-constexpr float kMaxHalf = 65504.f;  // CUDART_MAX_NORMAL_FP16 (decode_page.cuh:430-431)
-
 // One thread per 16-byte column vector of the [H*D] row.
 __global__ void __launch_bounds__(256)
 append_decode_kernel(const __half* __restrict__ k, const __half* __restrict__ v, __half* __restrict__ kv,
@@ -35,31 +17,8 @@ append_decode_kernel(const __half* __restrict__ k, const __half* __restrict__ v,
   const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
   pdl_wait();
   if (c >= row_vecs) return;
-  const size_t row = (size_t)row_vecs * 8;  // H*D elements
-  const size_t page = (size_t)__ldg(kv_indices + num_kv_pages - 1);
-  const uint32_t entry = kv_last_len - 1;
-  const size_t mpage = (size_t)__ldg(meta_indices + num_meta_pages - 1);
-  const uint32_t mentry = meta_last_len - 1;
-  __half* kdst = kv + ((page * 2) * P + entry) * row + c * 8;
-  __half* vdst = kdst + (size_t)P * row;
-  __half* mxp = meta + ((mpage * 2) * P + mentry) * row + c * 8;
-  __half* mnp = mxp + (size_t)P * row;
-  const H8 kk = ld_plain(k + c * 8);
-  const H8 vv = ld_plain(v + c * 8);
-  H8 mx, mn;
-  if (entry > 0) {
-    mx = ld_plain(mxp);
-    mn = ld_plain(mnp);
-  } else {
-    mx = h8_fill(-kMaxHalf);
-    mn = h8_fill(kMaxHalf);
-  }
-  h8_max(mx, kk);
-  h8_min(mn, kk);
-  st_plain(kdst, kk);
-  st_plain(vdst, vv);
-  st_plain(mxp, mx);
-  st_plain(mnp, mn);
+  append_decode_column(k, v, kv, kv_indices, num_kv_pages, kv_last_len, meta, meta_indices, num_meta_pages, meta_last_len,
+                       row_vecs, P, c);
 }
 
 // grid = (pages touched, column slices); each thread owns one 16-byte column of the page.

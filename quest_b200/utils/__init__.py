@@ -20,6 +20,7 @@ __all__ = [
     "decode_estimate",
     "decode_topk",
     "decode_sparse_attn",
+    "decode_layer_step",
     "rms_norm_forward",
     "apply_rope_in_place",
 ]
@@ -131,4 +132,54 @@ def decode_sparse_attn(q: torch.Tensor, iController: InferenceController, layer_
         rope_scale,
         rope_theta,
     )
+    return o
+
+
+class _BoundStep:
+    """Everything of a decode_layer_step call that does not change between the layers of one token: validated once
+    per begin_forward, so that the per-layer cost is a handful of data_ptr() calls and one ctypes call."""
+    __slots__ = ("fn", "mid", "tail", "kv_ptrs", "meta_ptrs", "qshape", "kshape", "dtype", "device")
+
+    def __init__(self, ic: InferenceController, q, k, v):
+        w = ic._decode_handler._wrapper
+        L = ic.kv_cache.buf_layer(0)
+        scores = ic._scores_buffer(ic.kv_indices_with_last.size(0) - 1)
+        # one fully validated call's worth of checks (shapes, dtypes, devices, plan) without launching anything
+        args = w.layer_step_args(q, k, v, torch.empty_like(q), L, ic.kv_indices_with_last, ic.kv_cache.last_page_len,
+                                 ic.kv_last_page_idx, ic.metadata_cache.buf_layer(0), ic.metadata_indices,
+                                 ic.metadata_cache.last_page_len, scores, ic.topk_dindices_buffer)
+        self.fn = _kernels.load_library().quest_decode_layer_step
+        self.mid = args[5:9]     # kv_indices, num_kv_pages, last idx, last len
+        self.tail = args[10:]    # meta_indices ... workspace_bytes (stream appended per call)
+        layers = range(ic.kv_cache.pool.num_layers)
+        self.kv_ptrs = [ic.kv_cache.buf_layer(i).data_ptr() for i in layers]
+        self.meta_ptrs = [ic.metadata_cache.buf_layer(i).data_ptr() for i in layers]
+        self.qshape, self.kshape, self.dtype, self.device = q.shape, k.shape, q.dtype, q.device
+
+
+def decode_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iController: InferenceController,
+                      layer_idx: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """append_kv + decode_estimate + decode_topk + decode_sparse_attn of one layer in ONE native call (the sequence at
+    reference quest/models/QuestAttention.py:100-150 when iController.need_estimate()): three kernel launches, one
+    Python->C transition.  Selected ids land in iController.topk_dindices_buffer as with decode_topk.  Without a
+    budget to enforce (need_estimate() false) it is append_kv + attention over all pages, as the reference does.
+    ``out`` (optional, like q): written instead of a fresh tensor."""
+    if not iController.need_estimate():
+        append_kv(k, v, iController, layer_idx)
+        o = decode_sparse_attn(q, iController, layer_idx, iController.kv_indices_without_last)
+        return o if out is None else out.copy_(o)
+    st = iController._step
+    if st is None:
+        st = iController._step = _BoundStep(iController, q, k, v)
+    for t_, shape in ((q, st.qshape), (k, st.kshape), (v, st.kshape)):
+        if t_.shape != shape or t_.dtype != st.dtype or t_.device != st.device or not t_.is_contiguous():
+            raise RuntimeError("decode_layer_step: q must be [1, num_heads, head_dim], k and v [1, num_kv_heads, head_dim]; "
+                               "contiguous fp16 tensors on the controller's device")
+    o = torch.empty_like(q) if out is None else out
+    if out is not None and (out.shape != st.qshape or out.dtype != st.dtype or out.device != st.device or not out.is_contiguous()):
+        raise RuntimeError("decode_layer_step: out must look like q")
+    rc = st.fn(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), st.kv_ptrs[layer_idx], *st.mid,
+               st.meta_ptrs[layer_idx], *st.tail, torch.cuda.current_stream().cuda_stream)
+    if rc:
+        _kernels._rc(rc, "decode_layer_step")
     return o

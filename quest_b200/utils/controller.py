@@ -42,6 +42,7 @@ class InferenceController:
         self._meta_synced = 0
         self._indptr_cache = {}
         self._topk_cache = {}
+        self._step = None  # bound arguments of decode_layer_step, valid until the next begin_forward
 
         self.kv_indices_with_last = None
         self.kv_indices_without_last = None
@@ -85,6 +86,7 @@ class InferenceController:
 
     # Prepare metadata used for inference under certain PAGE_BUDGET (called per budget change).
     def begin_forward(self, seq_len: int, updateTensor: bool = True):
+        self._step = None
         kv_ids, meta_ids = self.kv_cache.indicies, self.metadata_cache.indicies
         if updateTensor:
             self._kv_synced = self._sync_table(self._kv_table, kv_ids, self._kv_synced)
@@ -123,6 +125,16 @@ class InferenceController:
 
         self._decode_handler.begin_forward(self.kv_indptr_for_approx_decode, self.num_heads, self.num_kv_heads,
                                            self.head_dim, self.page_size, self.dtype, num_pages=k)
+
+    def _scores_buffer(self, n):
+        """[num_heads, n] fp16 scratch for decode_layer_step (decode_estimate allocates a fresh tensor per call, as the
+        reference does): a view of one flat buffer that grows geometrically."""
+        flat = getattr(self, "_scores_flat", None)
+        need = self.num_heads * n
+        if flat is None or flat.numel() < need:
+            self._scores_flat = flat = torch.empty(max(need, 2 * (flat.numel() if flat is not None else 0)),
+                                                   dtype=self.dtype, device=self.device)
+        return flat[:need].view(self.num_heads, n)
 
     # Release the split-KV plan (reference frees handler buffers here).
     def end_forward(self):

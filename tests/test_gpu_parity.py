@@ -272,6 +272,41 @@ def test_layer_step_matches_oracle(kv_len, budget):
     assert np.abs(o[0].float().cpu().numpy() - want_o).max() <= ATTN_ATOL
 
 
+@pytest.mark.parametrize("kv_len,budget", [(61, 3), (482, 7), (1011, 31), (3330, 71)])
+def test_decode_layer_step_operator_equals_four_ops(kv_len, budget):
+    """quest_b200.utils.decode_layer_step (one native call per layer) against append_kv + decode_estimate + decode_topk +
+    decode_sparse_attn on a second controller: output, selected ids and both pools identical, over several tokens."""
+    H, D, P = 32, 128, 16
+    _, k, v = golden_inputs(kv_len * 5 + budget, kv_len + 3, H, D)
+    q = np.random.default_rng(kv_len).standard_normal((4, H, D), dtype=np.float32).astype(np.float16)
+    ics = [qu.InferenceController(1, H, D, P, budget, 4096, torch.float16, torch.device(DEV)) for _ in range(2)]
+    for ic in ics:
+        ic.prepare_metadata(kv_len - 1), ic.begin_forward(kv_len - 1)
+        qu.append_kv(t(k[:kv_len - 1]), t(v[:kv_len - 1]), ic, 0)
+        ic.end_forward()
+    for step in range(4):
+        i = kv_len - 1 + step
+        tq, tk, tv = t(q[step:step + 1]), t(k[i:i + 1]), t(v[i:i + 1])
+        a, b = ics
+        a.prepare_metadata(1), a.begin_forward(1)
+        qu.append_kv(tk, tv, a, 0)
+        assert a.need_estimate()
+        sc = qu.decode_estimate(tq, a, 0)
+        qu.decode_topk(sc, a)
+        o1 = qu.decode_sparse_attn(tq, a, 0, a.topk_dindices_buffer)
+        a.end_forward()
+        b.prepare_metadata(1), b.begin_forward(1)
+        o2 = qu.decode_layer_step(tq, tk, tv, b, 0)
+        b.end_forward()
+        assert torch.equal(o1, o2), f"step {step}"
+        assert torch.equal(a.topk_dindices_buffer, b.topk_dindices_buffer)
+        assert a.kv_cache.indicies == b.kv_cache.indicies
+        for ca, cb in ((a.kv_cache, b.kv_cache), (a.metadata_cache, b.metadata_cache)):  # written slots only
+            idx = torch.tensor(ca.indicies, device=DEV)
+            pa, pb = ca.buf_layer(0)[idx].view(torch.int16), cb.buf_layer(0)[idx].view(torch.int16)
+            assert torch.equal(pa[:-1], pb[:-1]) and torch.equal(pa[-1, :, :ca.last_page_len], pb[-1, :, :ca.last_page_len])
+
+
 @pytest.mark.parametrize("H,kv_len,budget,P", [(32, 2500, 32, 16), (32, 32768, 128, 16), (32, 20000, 64, 16), (32, 700, 44, 16),
                                                (16, 9000, 100, 16), (8, 4000, 17, 16), (32, 5000, 8, 8), (32, 40, 2, 16),
                                                (32, 32768 + 16 * 300, 128, 16), (4, 3000, 16, 16), (32, 3000, 16, 32)])
@@ -315,6 +350,55 @@ def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
     # the stand-alone decode can share the workspace afterwards
     o3 = run_decode(q, gc, i1.cpu().numpy(), oc)
     assert torch.equal(o1, o3)
+
+
+@pytest.mark.parametrize("Hq,Hkv,kv_len,budget,P,D", [(32, 32, 2500, 32, 16, 128), (32, 32, 32768, 128, 16, 128), (32, 32, 2049, 16, 16, 128),
+                                                      (32, 32, 2065, 16, 16, 128), (32, 8, 3000, 24, 16, 128), (8, 8, 700, 9, 8, 64),
+                                                      (32, 32, 17, 2, 16, 128), (32, 32, 9, 1, 16, 128), (6, 3, 1000, 12, 16, 128)])
+def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P, D):
+    """quest_decode_layer_step (append carried by the estimate kernel) against append_kv + estimate + top-k + decode on a
+    second copy of the cache: pools, scores, selected pages and output all bit-identical; repeated over 3 tokens so that
+    page and metadata-page boundaries are crossed (kv_len 2049 starts a page, 2065 continues one)."""
+    rng = np.random.default_rng(kv_len + budget)
+    oc = OracleCache((kv_len + 3 + P - 1) // P + 2, P, Hkv, D, seed=kv_len)
+    ga, gb = GpuCache(oc), GpuCache(oc)
+    k0, v0 = rand_kv(rng, kv_len - 1, Hkv, D)
+    oc.append(k0, v0), ga.append(k0, v0), gb.append(k0, v0)
+    lib = K.load_library()
+    import ctypes
+    for step in range(3):
+        k1, v1 = rand_kv(rng, 1, Hkv, D)
+        q = rng.standard_normal((1, Hq, D), dtype=np.float32).astype(np.float16)
+        oc.append(k1, v1)
+        n_pages = len(oc.kv_indices)
+        n, kk = n_pages - 1, min(budget, n_pages) - 1
+        kvi, kvp, mi, mp = ga.tables()
+        # A: the four operator calls
+        ga.append(k1, v1)
+        s1 = torch.zeros((Hq, n), dtype=torch.float16, device=DEV)
+        i1 = torch.zeros((Hq, kk), dtype=torch.int32, device=DEV)
+        if kk:
+            K.estimate_attn_score(t(q), s1, ga.meta, mi, mp, oc.meta_last_page_len, oc.meta_indices[-1], 0, K.EST_META_ORDERED)
+            K.topk_filtering(s1, kvi[:-1].unsqueeze(0).expand(Hq, -1), torch.zeros((Hq, kk), dtype=torch.float16, device=DEV), i1, None, kk)
+        o1 = run_decode(q, ga, i1.cpu().numpy(), oc)
+        # B: one call
+        ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
+        assert lib.quest_decode_plan(kk, Hq, Hkv, D, P, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0
+        ws = torch.zeros(lib.quest_decode_workspace_bytes(Hq, D, nch.value), dtype=torch.uint8, device=DEV)
+        s2, i2 = torch.zeros_like(s1), torch.zeros_like(i1)
+        o2 = torch.zeros((1, Hq, D), dtype=torch.float16, device=DEV)
+        tq, tk, tv = t(q), t(k1), t(v1)
+        rc = lib.quest_decode_layer_step(tq.data_ptr(), tk.data_ptr(), tv.data_ptr(), o2.data_ptr(), gb.kv.data_ptr(), kvi.data_ptr(),
+                                         n_pages, oc.kv_indices[-1], oc.last_page_len, gb.meta.data_ptr(), mi.data_ptr(),
+                                         len(oc.meta_indices), oc.meta_last_page_len, s2.data_ptr(), i2.data_ptr(), kk, Hq, Hkv,
+                                         D, P, ppc.value, ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream)
+        assert rc == 0
+        torch.cuda.synchronize()
+        assert torch.equal(ga.kv.view(torch.int16), gb.kv.view(torch.int16)), f"kv pool, step {step}"
+        assert torch.equal(ga.meta.view(torch.int16), gb.meta.view(torch.int16)), f"metadata pool, step {step}"
+        assert torch.equal(s1, s2) and torch.equal(i1, i2) and torch.equal(o1, o2), f"step {step}"
+    ga.assert_equal_oracle()
+    gb.assert_equal_oracle()
 
 
 # ------------------------------------------------------------------ golden vectors from the reference's own code
