@@ -6,8 +6,11 @@
 
 #include "../../include/quest_b200.h"
 
-// Where each kernel releases its programmatic dependents (0 = only at exit).  Measured on B200 (profiles/r01_pdl_trigger_ab.txt):
-// early triggers made estimate->top-k and top-k->decode 6-11 us SLOWER per pair, so the default is exit-only.
+// Where each kernel releases its programmatic dependents (0 = only at exit, 1 = after its prologue).  Measured on
+// B200 (profiles/r01_pdl_trigger_ab.txt, r01_pdl_trigger_ab2.txt; us per layer step): releasing from the estimate
+// kernel parks the top-k CTAs on SM slots the scan needs (21.7 -> 26.9); from the top-k kernel it changes nothing;
+// from the decode kernel it lets the next launch on the stream -- the next layer's estimate, whose first ring of
+// metadata loads does not depend on anything earlier -- start under the decode's merge tail (21.7 -> 20.0).
 #ifndef QUEST_TRIG_EST
 #define QUEST_TRIG_EST 0
 #endif
@@ -15,7 +18,7 @@
 #define QUEST_TRIG_TOPK 0
 #endif
 #ifndef QUEST_TRIG_DEC
-#define QUEST_TRIG_DEC 0
+#define QUEST_TRIG_DEC 1
 #endif
 
 namespace quest {

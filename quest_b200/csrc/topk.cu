@@ -46,6 +46,9 @@ topk_fast_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict_
   const uint32_t head = blockIdx.x, tid = threadIdx.x;
   const uint16_t* s = scores + (size_t)head * len;
   const uint32_t len8 = (len + 7) & ~7u;
+#if QUEST_TRIG_TOPK
+  pdl_trigger();
+#endif
   pdl_wait();  // scores come from the estimate kernel
   // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent (4 per thread)
   uint16_t v[4];
