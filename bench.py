@@ -162,6 +162,9 @@ class Workload:
         ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
         assert lib.quest_decode_plan(K_SEL, H, H, D, P, torch.cuda.get_device_properties(self.dev).multi_processor_count,
                                      ctypes.byref(ppc), ctypes.byref(nch)) == 0
+        if os.environ.get("BENCH_PPC"):  # tuning experiment: override the planner's pages per chunk
+            ppc.value = int(os.environ["BENCH_PPC"])
+            nch.value = (K_SEL + 1 + ppc.value - 1) // ppc.value
         self.plan = (ppc.value, nch.value)
         sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
         # sized for both the stand-alone decode plan and the fused layer-step kernel (2 CTAs/SM shared by the heads)

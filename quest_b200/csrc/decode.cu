@@ -13,6 +13,21 @@
 
 namespace quest {
 
+// -DQUEST_DEC_CLOCKS: every CTA stamps %globaltimer at its phase boundaries (tools/decode_timeline.py)
+#ifdef QUEST_DEC_CLOCKS
+__device__ unsigned long long g_dec_clk[4096 * 8];
+#define D_STAMP(i)                                                                             \
+  do {                                                                                         \
+    if (threadIdx.x == 0) {                                                                    \
+      unsigned long long t_;                                                                   \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                   \
+      g_dec_clk[((blockIdx.y * gridDim.x + blockIdx.x) & 4095) * 8 + (i)] = t_;                \
+    }                                                                                          \
+  } while (0)
+#else
+#define D_STAMP(i) do { } while (0)
+#endif
+
 constexpr int kDecThreads = 128;
 constexpr int kDecWarps = kDecThreads / 32;
 constexpr float kNegBig = -1e30f;
@@ -27,17 +42,17 @@ __device__ __forceinline__ uint32_t div_p(uint32_t t, uint32_t p_magic) { return
 // 2 warp-wide K loads + 2 V loads (a lane group of D/8 lanes owns one 16-byte-per-lane token row), with
 // the next item's loads issued before the current item is consumed: 8 independent 128-bit loads per lane
 // stay in flight, ~128 KB per SM at 8 CTAs/SM, and the softmax arithmetic hides under them.
-template <int D>
-__global__ void __launch_bounds__(kDecThreads, 7)
+template <int D, int kThreads, int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks)
 decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __restrict__ lse,
               const __half* __restrict__ kv, const int32_t* __restrict__ indices, uint32_t idx_stride,
               uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len, uint32_t Hkv, uint32_t G,
-              uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws,
-              uint32_t dbg) {
+              uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws) {
+  constexpr int kWarps = kThreads / 32;
   constexpr int LPR = D / 8;
   constexpr int TPL = 32 / LPR;           // token rows per warp-wide load
   constexpr int IT = 2 * TPL;             // tokens per item
-  constexpr int NG = kDecWarps * TPL;     // lane groups per CTA
+  constexpr int NG = kWarps * TPL;     // lane groups per CTA
   extern __shared__ int32_t s_pages[];    // [pages of this chunk]
   __shared__ float s_o[NG][D];
   __shared__ float s_md[NG][2];
@@ -53,9 +68,11 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
   const size_t slab = (size_t)P * Hkv * D;  // K -> V offset inside a page
   const size_t row = (size_t)Hkv * D;
 
+  D_STAMP(0);
   pdl_wait();  // q, the page ids (top-k kernel) and the last page's new row (append) come from earlier kernels
+  D_STAMP(1);
   const int32_t* idx_row = indices + (size_t)h * idx_stride;
-  for (uint32_t i = tid; i < npg; i += kDecThreads)
+  for (uint32_t i = tid; i < npg; i += kThreads)
     s_pages[i] = pg0 + i < n_sel ? __ldg(idx_row + pg0 + i) : (int32_t)last_page_idx;
   float qv[8];
   {
@@ -65,6 +82,7 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     for (int i = 0; i < 8; ++i) qv[i] *= sm_scale_log2;
   }
   __syncthreads();
+  D_STAMP(2);  // page ids and q are in
 #if QUEST_TRIG_DEC
   pdl_trigger();
 #endif
@@ -111,17 +129,11 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     ptr += TPL * row_bytes;
     if (++i_ld == n_tl) {  // warp-uniform
       i_ld = 0;
-      pg_ld += kDecWarps;
+      pg_ld += kWarps;
       open_page();
     }
   };
   auto consume2 = [&](int st) {  // stages st, st+1: two token rows per lane group, one softmax rescale
-    if (dbg & 2) {  // experiment: loads only
-      float kf[8];
-      h8_to_float(kk[st], kf); acc[0] += kf[0]; h8_to_float(vv[st], kf); acc[1] += kf[0];
-      h8_to_float(kk[st + 1], kf); acc[2] += kf[0]; h8_to_float(vv[st + 1], kf); acc[3] += kf[0];
-      return;
-    }
     float sc[2];
     float mt = m;
 #pragma unroll
@@ -152,7 +164,7 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     }
   };
   // token-loads this warp must consume: its pages x n_tl (warp-uniform; the shuffles use the full mask)
-  const uint32_t my_pages = npg > warp ? (npg - warp + kDecWarps - 1) / kDecWarps : 0;
+  const uint32_t my_pages = npg > warp ? (npg - warp + kWarps - 1) / kWarps : 0;
   const uint32_t my_tl = my_pages * n_tl;
 #pragma unroll
   for (int st = 0; st < kRing; ++st) issue(st);
@@ -165,6 +177,7 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     issue(3);
   }
 
+  D_STAMP(3);  // warp 0's rows are consumed
   // CTA merge of the NG group states.
 #pragma unroll
   for (int i = 0; i < 8; ++i) s_o[gid][lir * 8 + i] = acc[i];
@@ -173,7 +186,7 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     s_md[gid][1] = d;
   }
   __syncthreads();
-  constexpr int CPT = (D + kDecThreads - 1) / kDecThreads;  // output columns per thread
+  constexpr int CPT = (D + kThreads - 1) / kThreads;  // output columns per thread
   float M = kNegBig, dsum = 0.f, osum[CPT];
 #pragma unroll
   for (int g = 0; g < NG; ++g) M = fmaxf(M, s_md[g][0]);
@@ -185,14 +198,14 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     dsum += s_md[g][1] * w;
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
-      const uint32_t col = tid + c * kDecThreads;
+      const uint32_t col = tid + c * kThreads;
       if (col < D) osum[c] += s_o[g][col] * w;
     }
   }
   if (nchunks == 1) {
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
-      const uint32_t col = tid + c * kDecThreads;
+      const uint32_t col = tid + c * kThreads;
       if (col < D) o[(size_t)h * D + col] = __float2half_rn(__fdividef(osum[c], dsum));
     }
     if (lse && tid == 0) lse[h] = M + lg2(dsum);
@@ -203,14 +216,13 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
   uint32_t* ticket = reinterpret_cast<uint32_t*>(ws + ws_ticket_off());
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
-    const uint32_t col = tid + c * kDecThreads;
+    const uint32_t col = tid + c * kThreads;
     if (col < D) ws_o[((size_t)h * nchunks + chunk) * D + col] = osum[c];
   }
   if (tid == 0) {
     ws_md[((size_t)h * nchunks + chunk) * 2] = M;
     ws_md[((size_t)h * nchunks + chunk) * 2 + 1] = dsum;
   }
-  if (dbg & 1) return;  // experiment: no merge
   // Release/acquire through the ticket: the CTA's partial is ordered before tid 0's acq_rel atomic by the
   // barrier, and the last arriver's acquire orders every other CTA's partial before its loads below.
   __syncthreads();
@@ -220,11 +232,12 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     s_last = old == nchunks - 1;
   }
   __syncthreads();
+  D_STAMP(4);  // partial published, ticket taken
   if (!s_last) return;
   // Last arriver: one round trip.  All partial rows are requested as independent 128-bit loads
-  // (kDecThreads / (D/4) rows per sweep, 8 sweeps in flight) before any weight is needed.
+  // (kThreads / (D/4) rows per sweep, 8 sweeps in flight) before any weight is needed.
   constexpr int NV = D / 4;               // float4 per partial row
-  constexpr int RPS = kDecThreads / NV;   // rows per sweep
+  constexpr int RPS = kThreads / NV;   // rows per sweep
   static_assert(RPS >= 1 && RPS <= NG, "partial-row sweep must fit the group-state buffer");
   const uint32_t cr = tid / NV, c4 = tid % NV;
   const float4* po = reinterpret_cast<const float4*>(ws_o + (size_t)h * nchunks * D);
@@ -277,19 +290,20 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
     df += s_md[g][1] * w;
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
-      const uint32_t col = tid + c * kDecThreads;
+      const uint32_t col = tid + c * kThreads;
       if (col < D) of[c] += s_o[g][col] * w;
     }
   }
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
-    const uint32_t col = tid + c * kDecThreads;
+    const uint32_t col = tid + c * kThreads;
     if (col < D) o[(size_t)h * D + col] = __float2half_rn(__fdividef(of[c], df));
   }
   if (tid == 0) {
     if (lse) lse[h] = Mf + lg2(df);
     ticket[h] = 0;  // ready for the next launch
   }
+  D_STAMP(5);  // head merged
 }
 
 template <int D>
@@ -311,10 +325,9 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const float sm_scale_log2 = kLog2e / sqrtf((float)D);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<D>, (const __half*)q, (__half*)o, lse, (const __half*)kv,
-                                     indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv, Hq / Hkv, P,
-                                     div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws,
-                                     (uint32_t)(getenv("QUEST_DEC_DBG") ? atoi(getenv("QUEST_DEC_DBG")) : 0));
+  cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<D, kDecThreads, 7>, (const __half*)q, (__half*)o, lse,
+                                     (const __half*)kv, indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv,
+                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -335,10 +348,6 @@ extern "C" int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, 
   if (min_ppc == 0) min_ppc = 1;
   uint32_t ppc = min_ppc;
   while (ppc < total && (uint64_t)num_qo_heads * ((total + ppc - 1) / ppc) > slots) ++ppc;
-  if (const char* e = getenv("QUEST_DEC_PPC")) {  // tuning hook
-    const uint32_t v = (uint32_t)atoi(e);
-    if (v) ppc = v;
-  }
   if (ppc > total) ppc = total;
   *pages_per_chunk = ppc;
   *num_chunks = (total + ppc - 1) / ppc;
@@ -377,3 +386,9 @@ extern "C" int quest_decode_run(const void* q, void* o, float* lse, const void* 
   }
 #undef QUEST_DEC
 }
+
+#ifdef QUEST_DEC_CLOCKS
+extern "C" int quest_debug_decode_clocks(unsigned long long* host_out, uint32_t n_ctas) {
+  return (int)cudaMemcpyFromSymbol(host_out, quest::g_dec_clk, (size_t)n_ctas * 8 * 8);
+}
+#endif

@@ -15,7 +15,7 @@ constexpr uint32_t kTopkMaxLen = 96 * 1024;  // 192 KB of u16 keys
 template <int W, int KPC>
 __global__ void __launch_bounds__(32 * W)
 topk_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_idx, uint32_t in_stride,
-            uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx, uint32_t len, uint32_t k, uint32_t dbg) {
+            uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx, uint32_t len, uint32_t k) {
   extern __shared__ __align__(16) uint16_t keys[];  // [len rounded up to 8]
   __shared__ TopkScratch<W> sc;
   constexpr uint32_t T = 32 * W;
@@ -28,12 +28,10 @@ topk_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_
 #endif
   pdl_wait();  // scores come from the estimate kernel
   // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent
-  if (dbg == 1) return;
   for (uint32_t i = tid; i < len8; i += T) keys[i] = i < len ? key_of(s[i]) : (uint16_t)0;
   __syncthreads();
-  if (dbg == 2) { if (keys[tid] == 0x1234 && tid == 77) out_idx[0] = 1; return; }
   topk_select<W, KPC>(keys, len, k, tid, 1, &sc, in_idx ? in_idx + (size_t)head * in_stride : nullptr,
-                 out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr, dbg);
+                 out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr);
 }
 
 template <int W>
@@ -100,7 +98,7 @@ static int launch_topk(const void* scores, const int32_t* in_idx, uint32_t in_st
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const uint16_t*)scores, in_idx, in_stride, (uint16_t*)out_val,
-                                     out_idx, len, k, (uint32_t)(getenv("QUEST_TOPK_DBG") ? atoi(getenv("QUEST_TOPK_DBG")) : 0));
+                                     out_idx, len, k);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }

@@ -183,7 +183,7 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
 template <int W, int KPC>
 __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, uint32_t k, uint32_t t, uint32_t bar_id,
                                             TopkScratch<W>* sc, const int32_t* __restrict__ in_idx,
-                                            int32_t* __restrict__ out_idx, uint16_t* __restrict__ out_val, uint32_t dbg = 0) {
+                                            int32_t* __restrict__ out_idx, uint16_t* __restrict__ out_val) {
   static_assert(KPC == 4 || KPC == 8, "chunk of 4 or 8 keys");
   constexpr uint32_t T = 32 * W;
   constexpr int WPC = KPC / 2;  // 32-bit words per chunk
@@ -277,7 +277,6 @@ __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, ui
     kk -= __shfl_sync(0xffffffffu, above, b);
     prefix = (prefix << 4) | b;
     TOPK_STAMP(pass * 8 + 5);
-    if (dbg == 3 + (uint32_t)pass) { if (prefix == 0xfffff) out_idx[0] = 1; return; }
   }
   const uint32_t tau = prefix, need = kk;
 
@@ -309,7 +308,6 @@ __device__ __forceinline__ void topk_select(const uint16_t* keys, uint32_t n, ui
     sc->weq[warp] = seq;
   }
   group_bar(bar_id, T);
-  if (dbg == 7) { if (sgt == 0xfffff) out_idx[0] = 1; return; }
   uint32_t gt_before = sgt - ngt, eq_before = seq - neq;
 #pragma unroll
   for (int w2 = 0; w2 < W; ++w2) {
