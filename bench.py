@@ -92,6 +92,8 @@ def cpu_layer_step_inputs():
 
 def run_cpu_port(steps, warmup):
     from oracle import torch_path
+    # all the host threads this process may use (torchrun exports OMP_NUM_THREADS=1)
+    torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
     q, k, v = cpu_layer_step_inputs()
     for _ in range(warmup):
         torch_path.quest_torch_decode(q, k, v, TOKEN_BUDGET, P, 1)
