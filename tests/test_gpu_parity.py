@@ -441,16 +441,67 @@ def test_rms_norm():
     np.testing.assert_allclose(o.float().cpu().numpy(), orc.rms_norm(x, w, 1e-5), rtol=5e-3, atol=5e-3)
 
 
-@pytest.mark.parametrize("qo_len,kv_len,Hq,Hkv,D,P", [(13, 33, 32, 32, 128, 16), (502, 1110, 8, 8, 128, 16), (64, 64, 8, 2, 64, 8),
-                                                     (47, 111, 4, 1, 128, 1), (200, 333, 4, 4, 64, 16)])
-def test_prefill_matches_dense_causal(qo_len, kv_len, Hq, Hkv, D, P):
-    """quest/tests/test_prefill_attention.py:46-87 + GQA cases of kernels/src/test/test_prefill.cu:407-467."""
-    rng = np.random.default_rng(qo_len + kv_len)
+PREFILL_CASES = [(13, 33, 32, 32, 128, 16), (502, 1110, 8, 8, 128, 16), (64, 64, 8, 2, 64, 8), (47, 111, 4, 1, 128, 1),
+                 (200, 333, 4, 4, 64, 16), (128, 128, 4, 4, 128, 16), (129, 129, 2, 2, 128, 16), (1, 700, 4, 4, 128, 16),
+                 (640, 2049, 8, 2, 128, 16), (17, 4100, 4, 4, 128, 16), (257, 321, 6, 2, 64, 32)]
+
+
+def _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, causal, impl):
     rounds = [kv_len - qo_len, qo_len] if kv_len > qo_len else [qo_len]
     oc, gc, k, v, rng = make_pair(0, P, Hkv, D, seed=qo_len, rounds=[r for r in rounds if r])
     q = rng.standard_normal((qo_len, Hq, D), dtype=np.float32).astype(np.float16)
     kvi, *_ = gc.tables()
-    o = K.prefill_with_paged_kv_cache(t(q), gc.kv, kvi, oc.last_page_len, True, 0, False, 1.0, 1e4)
+    old = os.environ.get("QUEST_PF_IMPL")
+    if impl:
+        os.environ["QUEST_PF_IMPL"] = impl
+    try:
+        o = K.prefill_with_paged_kv_cache(t(q), gc.kv, kvi, oc.last_page_len, causal, 0, False, 1.0, 1e4)
+        torch.cuda.synchronize()
+    finally:
+        if old is None:
+            os.environ.pop("QUEST_PF_IMPL", None)
+        else:
+            os.environ["QUEST_PF_IMPL"] = old
+    assert K.load_library().quest_debug_prefill_timeouts() == 0
+    want = orc.dense_attention(q, k, v, causal=causal)
+    assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL
+
+
+@pytest.mark.parametrize("impl", ["", "umma", "simt"])  # "": the library's own choice by qo_len
+@pytest.mark.parametrize("qo_len,kv_len,Hq,Hkv,D,P", PREFILL_CASES)
+def test_prefill_matches_dense_causal(qo_len, kv_len, Hq, Hkv, D, P, impl):
+    """quest/tests/test_prefill_attention.py:46-87 + GQA cases of kernels/src/test/test_prefill.cu:407-467; both the
+    tcgen05 kernel and the SIMT kernel on every shape (ragged query tiles, kv tails, page sizes 1..32, GQA)."""
+    _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, True, impl)
+
+
+@pytest.mark.parametrize("impl", ["umma", "simt"])
+@pytest.mark.parametrize("qo_len,kv_len,Hq,Hkv,D,P", [(130, 333, 4, 4, 128, 16), (64, 1000, 4, 2, 64, 8)])
+def test_prefill_matches_dense_noncausal(qo_len, kv_len, Hq, Hkv, D, P, impl):
+    _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, False, impl)
+
+
+def test_prefill_large_logits_lazy_rescale():
+    """Rows whose running maximum keeps growing by large steps (keys scaled up along the sequence): exercises the
+    in-TMEM rescale of the tcgen05 kernel's accumulator."""
+    qo_len = kv_len = 512
+    H, D, P = 2, 128, 16
+    rng = np.random.default_rng(5)
+    q = rng.standard_normal((qo_len, H, D), dtype=np.float32).astype(np.float16)
+    k = (rng.standard_normal((kv_len, H, D), dtype=np.float32) * np.linspace(0.2, 6.0, kv_len)[:, None, None]).astype(np.float16)
+    v = rng.standard_normal((kv_len, H, D), dtype=np.float32).astype(np.float16)
+    oc = OracleCache(kv_len // P + 2, P, H, D, seed=3)
+    gc = GpuCache(oc)
+    oc.append(k, v)
+    gc.append(k, v)
+    kvi, *_ = gc.tables()
+    os.environ["QUEST_PF_IMPL"] = "umma"
+    try:
+        o = K.prefill_with_paged_kv_cache(t(q), gc.kv, kvi, oc.last_page_len, True, 0, False, 1.0, 1e4)
+        torch.cuda.synchronize()
+    finally:
+        os.environ.pop("QUEST_PF_IMPL", None)
+    assert K.load_library().quest_debug_prefill_timeouts() == 0
     want = orc.dense_attention(q, k, v, causal=True)
     assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL
 
