@@ -47,6 +47,9 @@ def main():
     ref = C.CDLL(ref_path) if os.path.exists(ref_path) else None
     if ref is not None and not hasattr(ref, "ref_prefill"):
         ref = None
+    only = os.environ.get("PF_ONLY") == "umma"  # profiling runs: just our tensor-core kernel
+    if only:
+        ref = None
     lib = K.load_library()
     st = torch.cuda.current_stream().cuda_stream
     torch.manual_seed(0)
@@ -71,7 +74,7 @@ def main():
         t_u = timed(lambda: ours("umma"), reps)
         assert lib.quest_debug_prefill_timeouts() == 0
         line = f"{n:6d} {flops / 1e9:9.1f} | {t_u:10.3f} {flops / t_u / 1e9:8.1f} {flops / t_u / 1e9 / peak:5.2f} | "
-        if n <= 8192:
+        if n <= 8192 and not only:
             t_s = timed(lambda: ours("simt"), 2)
             line += f"{t_s:8.2f} {flops / t_s / 1e9:8.1f} | "
         else:
