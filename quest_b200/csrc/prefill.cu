@@ -323,11 +323,18 @@ prefill_umma_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32
   if (warp == 0) tmem_free<kUmTmemCols>(tbase);
 }
 
-// 0 = by qo_len (default), 1 = SIMT always, 2 = tcgen05 always (QUEST_PF_IMPL=simt|umma; test / A-B hook, read per call)
+// prefill_tma.cu: the warp-specialised TMA + tcgen05 kernel (page sizes 2^n >= 8)
+int launch_prefill_tma(const __half* q, __half* o, uint32_t qo_len, const __half* kv, const int32_t* kv_indices,
+                       uint32_t num_pages, uint32_t kv_len, int causal, uint32_t Hq, uint32_t Hkv, uint32_t D, uint32_t P,
+                       float sc, cudaStream_t s);
+unsigned int prefill_tma_timeouts();
+
+// QUEST_PF_IMPL (test / A-B hook, read per call): unset = by shape (TMA kernel where it applies, else the cp.async
+// tcgen05 kernel; SIMT for qo_len <= 16), "simt" = 1, "umma" = 2 (cp.async tcgen05 kernel), "tma" = 3 (no fallback)
 static int prefill_impl_override() {
   const char* e = std::getenv("QUEST_PF_IMPL");
   if (!e) return 0;
-  return !std::strcmp(e, "simt") ? 1 : !std::strcmp(e, "umma") ? 2 : 0;
+  return !std::strcmp(e, "simt") ? 1 : !std::strcmp(e, "umma") ? 2 : !std::strcmp(e, "tma") ? 3 : 0;
 }
 
 template <int D>
@@ -349,7 +356,7 @@ static cudaError_t launch_prefill_umma(const __half* q, __half* o, uint32_t qo_l
 extern "C" int quest_debug_prefill_timeouts(void) {
   unsigned int v = 0;
   if (cudaMemcpyFromSymbol(&v, quest::g_pf_timeouts, sizeof(v)) != cudaSuccess) return -1;
-  return (int)v;
+  return (int)(v | (quest::prefill_tma_timeouts() << 1));
 }
 
 extern "C" int quest_prefill(const void* q, void* o, uint32_t qo_len, const void* kv_data, const int32_t* kv_indices,
@@ -366,6 +373,12 @@ extern "C" int quest_prefill(const void* q, void* o, uint32_t qo_len, const void
   const float sc = quest::kLog2e / sqrtf((float)head_dim);
   cudaStream_t s = (cudaStream_t)stream;
   const int force = quest::prefill_impl_override();
+  if (force == 3 || (force == 0 && qo_len > (uint32_t)quest::kPfBQ)) {
+    const int rc = quest::launch_prefill_tma((const __half*)q, (__half*)o, qo_len, (const __half*)kv_data, kv_indices, num_kv_pages,
+                                             kv_len, causal, num_qo_heads, num_kv_heads, head_dim, page_size, sc, s);
+    if (rc == QUEST_OK) QUEST_RETURN_LAUNCH();
+    if (rc != QUEST_ERR_UNSUPPORTED || force == 3) return rc;
+  }
   const bool use_umma = force == 2 || (force == 0 && qo_len > (uint32_t)quest::kPfBQ);
   if (use_umma) {
     cudaError_t e;

@@ -120,5 +120,73 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
+
+// ---- mbarrier arrivals and an abort-aware wait for warp-specialised pipelines: the first wait that runs out sets
+// *abort_flag (shared memory) and every later wait in the CTA returns at once, so a lost signal ends the kernel
+// quickly with a wrong result (reported through a global counter) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_arrive(uint32_t bar_saddr) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar_saddr) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar_saddr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar_saddr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_abortable(uint32_t bar_saddr, uint32_t parity, volatile uint32_t* abort_flag) {
+  for (uint32_t spin = 0; spin < (1u << 20); ++spin) {
+    uint32_t done;
+    asm volatile(
+        "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(done)
+        : "r"(bar_saddr), "r"(parity)
+        : "memory");
+    if (done) return;
+    if ((spin & 63u) == 63u && *abort_flag) return;
+  }
+  *abort_flag = 1u;
+}
+
+// ---- TMA: one box of a tiled tensor map -> shared memory, completion counted in bytes on an mbarrier.
+// Coordinates are innermost first.  Issued by ONE thread.
+__device__ __forceinline__ void tma_load_3d(uint32_t dst_saddr, const void* tmap, uint32_t bar_saddr, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2,%3,%4}], [%5];"
+      :: "r"(dst_saddr), "l"((uint64_t)tmap), "r"(c0), "r"(c1), "r"(c2), "r"(bar_saddr)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_5d(uint32_t dst_saddr, const void* tmap, uint32_t bar_saddr, int c0, int c1, int c2,
+                                            int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2,%3,%4,%5,%6}], [%7];"
+      :: "r"(dst_saddr), "l"((uint64_t)tmap), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4), "r"(bar_saddr)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" :: "l"((uint64_t)tmap) : "memory");
+}
+
+// ---- packed fp32x2 arithmetic (FFMA2 / FADD2) and the 3-input maximum (FMNMX3) of sm_100
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t add_f32x2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+
 }  // namespace umma
 }  // namespace quest

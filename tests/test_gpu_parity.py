@@ -443,10 +443,13 @@ def test_rms_norm():
 
 PREFILL_CASES = [(13, 33, 32, 32, 128, 16), (502, 1110, 8, 8, 128, 16), (64, 64, 8, 2, 64, 8), (47, 111, 4, 1, 128, 1),
                  (200, 333, 4, 4, 64, 16), (128, 128, 4, 4, 128, 16), (129, 129, 2, 2, 128, 16), (1, 700, 4, 4, 128, 16),
-                 (640, 2049, 8, 2, 128, 16), (17, 4100, 4, 4, 128, 16), (257, 321, 6, 2, 64, 32)]
+                 (640, 2049, 8, 2, 128, 16), (17, 4100, 4, 4, 128, 16), (257, 321, 6, 2, 64, 32), (300, 500, 4, 2, 128, 64),
+                 (70, 135, 2, 1, 64, 128)]
 
 
 def _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, causal, impl):
+    if impl == "tma" and (P < 8 or P & (P - 1)):
+        pytest.skip("the TMA kernel covers page sizes 2^n >= 8")
     rounds = [kv_len - qo_len, qo_len] if kv_len > qo_len else [qo_len]
     oc, gc, k, v, rng = make_pair(0, P, Hkv, D, seed=qo_len, rounds=[r for r in rounds if r])
     q = rng.standard_normal((qo_len, Hq, D), dtype=np.float32).astype(np.float16)
@@ -467,23 +470,25 @@ def _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, causal, impl):
     assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL
 
 
-@pytest.mark.parametrize("impl", ["", "umma", "simt"])  # "": the library's own choice by qo_len
+@pytest.mark.parametrize("impl", ["", "tma", "umma", "simt"])  # "": the library's own choice by shape
 @pytest.mark.parametrize("qo_len,kv_len,Hq,Hkv,D,P", PREFILL_CASES)
 def test_prefill_matches_dense_causal(qo_len, kv_len, Hq, Hkv, D, P, impl):
     """quest/tests/test_prefill_attention.py:46-87 + GQA cases of kernels/src/test/test_prefill.cu:407-467; both the
-    tcgen05 kernel and the SIMT kernel on every shape (ragged query tiles, kv tails, page sizes 1..32, GQA)."""
+    tcgen05 kernels (TMA-fed and cp.async-fed) and the SIMT kernel on every shape (ragged query tiles, kv tails, page
+    sizes 1..128, GQA)."""
     _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, True, impl)
 
 
-@pytest.mark.parametrize("impl", ["umma", "simt"])
+@pytest.mark.parametrize("impl", ["tma", "umma", "simt"])
 @pytest.mark.parametrize("qo_len,kv_len,Hq,Hkv,D,P", [(130, 333, 4, 4, 128, 16), (64, 1000, 4, 2, 64, 8)])
 def test_prefill_matches_dense_noncausal(qo_len, kv_len, Hq, Hkv, D, P, impl):
     _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, False, impl)
 
 
-def test_prefill_large_logits_lazy_rescale():
+@pytest.mark.parametrize("impl", ["tma", "umma"])
+def test_prefill_large_logits_lazy_rescale(impl):
     """Rows whose running maximum keeps growing by large steps (keys scaled up along the sequence): exercises the
-    in-TMEM rescale of the tcgen05 kernel's accumulator."""
+    in-TMEM rescale of the tcgen05 kernels' accumulator."""
     qo_len = kv_len = 512
     H, D, P = 2, 128, 16
     rng = np.random.default_rng(5)
@@ -495,7 +500,7 @@ def test_prefill_large_logits_lazy_rescale():
     oc.append(k, v)
     gc.append(k, v)
     kvi, *_ = gc.tables()
-    os.environ["QUEST_PF_IMPL"] = "umma"
+    os.environ["QUEST_PF_IMPL"] = impl
     try:
         o = K.prefill_with_paged_kv_cache(t(q), gc.kv, kvi, oc.last_page_len, True, 0, False, 1.0, 1e4)
         torch.cuda.synchronize()

@@ -1,5 +1,5 @@
 """causal prefill over the paged KV cache, LongChat-7B shape (32 heads x 128, page 16, fp16),
-one layer: our tcgen05 kernel, our SIMT kernel (short lengths only) and the reference's own kernel
+one layer: our tcgen05 kernels (TMA-fed warp-specialised, and the cp.async-fed v1), our SIMT kernel (short lengths only) and the reference's own kernel
 (oracle/_ref/libquest_ref.so: kernels/include/prefill/prefill.cuh built for sm_100a, mma.sync) on the same pool and page
 table.  FLOPs counted as the causal attention does them: 4 * D * H * sum_i (kv_len - qo_len + i + 1).  CUDA events around
 REPS back-to-back launches after warm-up; the tensor roofline denominator is MEASURED_PEAKS.json's bf16_tflops.
@@ -47,7 +47,7 @@ def main():
     ref = C.CDLL(ref_path) if os.path.exists(ref_path) else None
     if ref is not None and not hasattr(ref, "ref_prefill"):
         ref = None
-    only = os.environ.get("PF_ONLY") == "umma"  # profiling runs: just our tensor-core kernel
+    only = os.environ.get("PF_ONLY") == "tma"  # profiling runs: just our TMA tensor-core kernel
     if only:
         ref = None
     lib = K.load_library()
@@ -55,14 +55,14 @@ def main():
     torch.manual_seed(0)
     print(f"causal prefill, one layer, H={H} D={D} P={P} fp16, qo_len = kv_len = n; ms per launch; "
           f"tensor peak = {peak:.0f} TFLOP/s (MEASURED_PEAKS.json bf16)")
-    print(f"{'n':>6s} {'GFLOP':>9s} | {'tcgen05 ms':>10s} {'TFLOP/s':>8s} {'frac':>5s} | {'simt ms':>8s} {'TFLOP/s':>8s} | "
+    print(f"{'n':>6s} {'GFLOP':>9s} | {'tma ms':>10s} {'TFLOP/s':>8s} {'frac':>5s} | {'cp.async':>8s} {'TFLOP/s':>8s} | {'simt ms':>8s} {'TFLOP/s':>8s} | "
           f"{'ref ms':>8s} {'TFLOP/s':>8s} | {'speed-up':>8s} {'max|diff|':>9s}")
     for n in lens:
         n_pages = n // P
         pool = torch.randn(n_pages, 2, P, H, D, device=DEV, dtype=torch.float16)
         q = torch.randn(n, H, D, device=DEV, dtype=torch.float16)
         table = torch.randperm(n_pages, device=DEV).to(torch.int32)
-        o = {k: torch.zeros(n, H, D, device=DEV, dtype=torch.float16) for k in ("umma", "simt", "ref")}
+        o = {k: torch.zeros(n, H, D, device=DEV, dtype=torch.float16) for k in ("tma", "umma", "simt", "ref")}
         flops = 4.0 * D * H * (n * (n + 1) / 2)
         reps = max(2, min(50, int(2e13 / flops)))
 
@@ -71,9 +71,14 @@ def main():
             rc = lib.quest_prefill(q.data_ptr(), o[impl].data_ptr(), n, pool.data_ptr(), table.data_ptr(), n_pages, P, 1, H, H, D, P, st)
             assert rc == 0, rc
 
-        t_u = timed(lambda: ours("umma"), reps)
+        t_u = timed(lambda: ours("tma"), reps)
         assert lib.quest_debug_prefill_timeouts() == 0
         line = f"{n:6d} {flops / 1e9:9.1f} | {t_u:10.3f} {flops / t_u / 1e9:8.1f} {flops / t_u / 1e9 / peak:5.2f} | "
+        if not only:
+            t_c = timed(lambda: ours("umma"), reps)
+            line += f"{t_c:8.3f} {flops / t_c / 1e9:8.1f} | "
+        else:
+            line += f"{'-':>8s} {'-':>8s} | "
         if n <= 8192 and not only:
             t_s = timed(lambda: ours("simt"), 2)
             line += f"{t_s:8.2f} {flops / t_s / 1e9:8.1f} | "
@@ -90,7 +95,7 @@ def main():
                 assert rc == 0, rc
             t_r = timed(reff, max(2, reps // 4))
             torch.cuda.synchronize()
-            err = (o["ref"].float() - o["umma"].float()).abs().max().item()
+            err = (o["ref"].float() - o["tma"].float()).abs().max().item()
             line += f"{t_r:8.3f} {flops / t_r / 1e9:8.1f} | {t_r / t_u:8.2f} {err:9.1e}"
         else:
             line += f"{'n/a':>8s} {'n/a':>8s} | {'n/a':>8s} {'n/a':>9s}"
