@@ -3,9 +3,9 @@
 // that are a power of two >= 8 (the reference accepts 1, 8, 16, 32: prefill.cuh:1031-1035); other shapes stay on the
 // cp.async kernel in prefill.cu.
 //
-// One CTA = 128 queries of one head, seven warps in four roles.  Warps 0-3 (one query row per thread = one TMEM
-// lane) run the online softmax; lane 0 of warp 4 issues every tcgen05.mma; warp 5 loads Q and the K tiles, warp 6 the
-// V tiles (TMA: lane l sends the boxes of the tile's l-th page).  Each role runs its own in-order loop and they meet
+// One CTA = 128 queries of one head, eight warps in five roles.  Warps 0-3 (one query row per thread = one TMEM
+// lane) run the online softmax; lane 0 of warp 7 issues the S = Q K^T MMAs, lane 0 of warp 4 the O += P V MMAs; warp 5
+// loads Q and the K tiles, warp 6 the V tiles (TMA: lane l sends the boxes of the tile's l-th page).  Each role runs its own in-order loop and they meet
 // only on mbarriers, so TMA issue latency, MMA issue latency and the softmax arithmetic overlap.
 //   * K/V pages come straight from the paged pool through ONE 5-d tensor map [page][k|v][slot][head][dim] with
 //     128-byte swizzle: a box is (64 dims, 1 head, min(P,64) slots) of one page, so a 64-token tile of K (or V) is
@@ -18,6 +18,8 @@
 //     packed FFMA2 / FADD2 for the scale-subtract and the row sum.
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "umma.cuh"
 
@@ -25,11 +27,12 @@ namespace quest {
 
 constexpr int kTmBQ = 128;
 constexpr int kTmBK = 64;
-constexpr int kTmThreads = 224;        // 4 softmax warps + MMA warp + K-loader warp + V-loader warp
+constexpr int kTmThreads = 256;        // 4 softmax warps + PV-MMA warp + K-loader + V-loader + S-MMA warp
 constexpr uint32_t kTmTmemCols = 256;  // S0 [0,64), S1 [64,128), O [128, 128+D)
 constexpr float kTmLazyLog2 = 8.f;
 
 __device__ unsigned int g_pf_tma_timeouts;
+__device__ unsigned int g_pf_tma_first[4];  // first wait that ran out: barrier slot, parity, thread, block (x | y << 16)
 
 #ifdef QUEST_PF_CLOCKS  // per-iteration timeline of one CTA (tools/prefill_timeline.py); not in the product build
 __device__ unsigned long long g_pf_clk[64][16];
@@ -50,7 +53,7 @@ struct TmSmem {
   static constexpr uint32_t off_bar = off_p + kP, total = off_bar + 128;
 };
 // barrier slots (8 bytes each) from off_bar
-enum : uint32_t { kBarQ = 0, kBarK = 1, kBarV = 3, kBarS = 5, kBarPV = 7, kBarP = 8, kBarVFree = 9, kNumBars = 11 };
+enum : uint32_t { kBarQ = 0, kBarK = 1, kBarV = 3, kBarS = 5, kBarPV = 7, kBarVFree = 9, kBarSFree = 11, kBarP = 13, kNumBars = 15 };
 
 // Page id of this lane's box of the 64-token tile at t0 (lane l < boxes per tile = 64 / min(P,64)), or -1 when the
 // tile has no such page.  Loaded one or more iterations before it is used, so the latency is off the issue path.
@@ -79,7 +82,7 @@ __device__ __forceinline__ void tm_issue_tile(const CUtensorMap* kvmap, uint32_t
   }
 }
 
-template <int D>
+template <int D, bool kPTmem>
 __global__ void __launch_bounds__(kTmThreads, 2)
 prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_constant__ CUtensorMap kvmap,
                    __half* __restrict__ o, uint32_t qo_len, const int32_t* __restrict__ kv_indices, uint32_t num_pages,
@@ -93,6 +96,13 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tm_smem + L::off_bar + kNumBars * 8);
   volatile uint32_t* abort_flag = reinterpret_cast<volatile uint32_t*>(tm_smem + L::off_bar + kNumBars * 8 + 4);
   auto bar = [&](uint32_t i) { return bars + i * 8; };
+  auto wait = [&](uint32_t slot, uint32_t parity) {
+    if (!mbar_wait_abortable(bars + slot * 8, parity, abort_flag) && atomicCAS(&g_pf_tma_first[3], 0u, 0x80000000u | blockIdx.x | (blockIdx.y << 16)) == 0u) {
+      g_pf_tma_first[0] = slot;
+      g_pf_tma_first[1] = parity;
+      g_pf_tma_first[2] = threadIdx.x;
+    }
+  };
 
   const uint32_t tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
   const uint32_t qtile = gridDim.x - 1 - blockIdx.x;  // longest (latest) query tiles first
@@ -104,7 +114,7 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
 
   if (warp == 4) tmem_alloc<kTmTmemCols>(smem_u32(tmem_slot));
   if (tid == 0) {
-    for (uint32_t i = 0; i < kNumBars; ++i) mbar_init(bar(i), i == kBarP ? 128u : 1u);
+    for (uint32_t i = 0; i < kNumBars; ++i) mbar_init(bar(i), i >= kBarSFree ? 128u : 1u);
     *abort_flag = (sbase & 1023u) ? 1u : 0u;
     mbar_init_fence();
   }
@@ -116,51 +126,49 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
   pdl_wait();
 
   if (warp == 4) {
-    // ------------------------------------------------------------------ MMA warp: lane 0 issues every tcgen05.mma
+    // ------------------------------------------------------------------ PV warp: lane 0 issues O += P(j) V(j)
     if (lane == 0) {
-      auto issue_s = [&](uint32_t jj) {
-        const uint32_t b = jj & 1;
+      for (uint32_t j = 0; j < ntiles; ++j) {
+        const uint32_t b = j & 1, ph = (j >> 1) & 1;
+        PF_STAMP(j, 2);
+        wait(kBarP + b, ph);    // P(j) has been handed over
+        PF_STAMP(j, 3);
+        wait(kBarV + b, ph);    // V(j) has landed
+        PF_STAMP(j, 4);
+        fence_after_sync();
+#pragma unroll
+        for (uint32_t kk = 0; kk < kTmBK / 16; ++kk) {
+          const uint64_t bd = desc_mn_major(v_s + b * L::kTile + kk * 2048, kTmBK * 128);
+          if constexpr (kPTmem)
+            mma_f16_ts(tbase + 128, tbase + b * 64 + kk * 8, bd, kIdescO, (j | kk) > 0);
+          else
+            mma_f16_ss(tbase + 128, desc_k_major(p_s + kk * 32), bd, kIdescO, (j | kk) > 0);
+        }
+        mma_commit(bar(kBarPV));         // softmax warps: the P tile is free, O is up to date
+        mma_commit(bar(kBarVFree + b));  // V loader: the stage is free
+        PF_STAMP(j, 5);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 7) {
+    // ------------------------------------------------------------------ S warp: lane 0 issues S(j) = Q K(j)^T, two tiles ahead
+    if (lane == 0) {
+      wait(kBarQ, 0);
+      for (uint32_t j = 0; j < ntiles; ++j) {
+        const uint32_t b = j & 1, ph = (j >> 1) & 1;
+        // the buffer is free once S(j-2) has been read out of it, or, with P(j-2) stored over it, once PV(j-2) is done
+        if (j >= 2) wait((kPTmem ? kBarVFree : kBarSFree) + b, ph ^ 1);
+        wait(kBarK + b, ph);                      // K(j) has landed
+        PF_STAMP(j, 6);
+        fence_after_sync();
 #pragma unroll
         for (uint32_t kk = 0; kk < D / 16; ++kk) {
           const uint64_t a = desc_k_major(q_s + (kk / 4) * (kTmBQ * 128) + (kk % 4) * 32);
           const uint64_t bd = desc_k_major(k_s + b * L::kTile + (kk / 4) * (kTmBK * 128) + (kk % 4) * 32);
           mma_f16_ss(tbase + b * 64, a, bd, kIdescS, kk > 0);
         }
-        mma_commit(bar(kBarS + b));  // S(jj) is ready for the softmax warps, and its K stage is free for the loader
-      };
-      mbar_wait_abortable(bar(kBarQ), 0, abort_flag);
-      mbar_wait_abortable(bar(kBarK), 0, abort_flag);
-      fence_after_sync();
-      issue_s(0);
-      if (ntiles > 1) {
-        mbar_wait_abortable(bar(kBarK + 1), 0, abort_flag);
-        fence_after_sync();
-        issue_s(1);
-      }
-      for (uint32_t j = 0; j < ntiles; ++j) {
-        const uint32_t b = j & 1, ph = (j >> 1) & 1;
-        PF_STAMP(j, 2);
-        mbar_wait_abortable(bar(kBarP), j & 1, abort_flag);     // P(j) is in shared memory, S(j) has been read
-        PF_STAMP(j, 3);
-        mbar_wait_abortable(bar(kBarV + b), ph, abort_flag);    // V(j) has landed
-        PF_STAMP(j, 4);
-        fence_after_sync();
-#pragma unroll
-        for (uint32_t kk = 0; kk < kTmBK / 16; ++kk) {
-          const uint64_t a = desc_k_major(p_s + kk * 32);
-          const uint64_t bd = desc_mn_major(v_s + b * L::kTile + kk * 2048, kTmBK * 128);
-          mma_f16_ss(tbase + 128, a, bd, kIdescO, (j | kk) > 0);
-        }
-        mma_commit(bar(kBarPV));         // softmax warps: the P tile is free, O is up to date
-        mma_commit(bar(kBarVFree + b));  // V loader: the stage is free
-        PF_STAMP(j, 5);
-        if (j + 2 < ntiles) {
-          mbar_wait_abortable(bar(kBarK + b), ph ^ 1, abort_flag);  // K(j+2)
-          PF_STAMP(j, 6);
-          fence_after_sync();
-          issue_s(j + 2);
-          PF_STAMP(j, 7);
-        }
+        mma_commit(bar(kBarS + b));  // S(j) is ready for the softmax warps, and its K stage is free for the loader
+        PF_STAMP(j, 7);
       }
     }
     __syncwarp();
@@ -181,7 +189,7 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
     if (ntiles > 1) tm_issue_tile<D>(&kvmap, k_s + L::kTile, bar(kBarK + 1), pg1, kTmBK, kvh, 0, p_shift, lane);
     for (uint32_t j = 0; j + 2 < ntiles; ++j) {  // K(j+2) takes the stage of K(j) once S(j) is done
       const int pg3 = tm_box_page(kv_indices, num_pages, (j + 3) * kTmBK, p_shift, lane, kv_end);
-      mbar_wait_abortable(bar(kBarS + (j & 1)), (j >> 1) & 1, abort_flag);
+      wait(kBarS + (j & 1), (j >> 1) & 1);
       if (lane == 0) PF_STAMP(j, 0);
       tm_issue_tile<D>(&kvmap, k_s + (j & 1) * L::kTile, bar(kBarK + (j & 1)), pg2, (j + 2) * kTmBK, kvh, 0, p_shift, lane);
       pg2 = pg3;
@@ -195,7 +203,7 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
     if (ntiles > 1) tm_issue_tile<D>(&kvmap, v_s + L::kTile, bar(kBarV + 1), pg1, kTmBK, kvh, 1, p_shift, lane);
     for (uint32_t j = 0; j + 2 < ntiles; ++j) {  // V(j+2) takes the stage of V(j) once PV(j) is done
       const int pg3 = tm_box_page(kv_indices, num_pages, (j + 3) * kTmBK, p_shift, lane, kv_end);
-      mbar_wait_abortable(bar(kBarVFree + (j & 1)), (j >> 1) & 1, abort_flag);
+      wait(kBarVFree + (j & 1), (j >> 1) & 1);
       if (lane == 0) PF_STAMP(j, 1);
       tm_issue_tile<D>(&kvmap, v_s + (j & 1) * L::kTile, bar(kBarV + (j & 1)), pg2, (j + 2) * kTmBK, kvh, 1, p_shift, lane);
       pg2 = pg3;
@@ -215,13 +223,17 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
     for (uint32_t j = 0; j < ntiles; ++j) {
       const uint32_t b = j & 1, t0 = j * kTmBK;
       if (tid == 0) PF_STAMP(j, 8);
-      mbar_wait_abortable(bar(kBarS + b), (j >> 1) & 1, abort_flag);
+      wait(kBarS + b, (j >> 1) & 1);
       if (tid == 0) PF_STAMP(j, 9);
       fence_after_sync();
       __syncwarp();
       tmem_ld32(tbase + b * 64 + lane_addr, sreg);
       tmem_ld32(tbase + b * 64 + 32 + lane_addr, sreg + 32);
       tmem_ld_wait();
+      if constexpr (!kPTmem) {
+        fence_before_sync();
+        mbar_arrive(bar(kBarSFree + b));  // the S warp may overwrite this buffer with S(j+2)
+      }
 
       if (t0 + kTmBK - 1 > mask_from) {
 #pragma unroll
@@ -263,12 +275,17 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
         dsum += a0 + a1;
       }
       if (tid == 0) PF_STAMP(j, 10);
-      if (j > 0) {  // PV(j-1) done: the P tile is free and O may be rescaled
-        mbar_wait_abortable(bar(kBarPV), (j - 1) & 1, abort_flag);
+      if (j > 0) {
+        // O may be rescaled (and, with P in shared memory, the P tile rewritten) once PV(j-1) is done; with P in
+        // tensor memory only the rare rescale needs that wait
+        const bool any_grow = __any_sync(0xffffffffu, grow);
+        if (!kPTmem || any_grow) {
+          wait(kBarPV, (j - 1) & 1);
+          fence_after_sync();
+          __syncwarp();
+        }
         if (tid == 0) PF_STAMP(j, 11);
-        fence_after_sync();
-        __syncwarp();
-        if (__any_sync(0xffffffffu, grow)) {
+        if (any_grow) {
 #pragma unroll 1
           for (uint32_t c0 = 0; c0 < D; c0 += 32) {
             uint32_t r[32];
@@ -281,12 +298,17 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
           tmem_st_wait();
         }
       }
+      if constexpr (kPTmem) {  // P(j) over the first half of S(j)'s own columns, this thread's lane
+        tmem_st32(tbase + b * 64 + lane_addr, pw);
+        tmem_st_wait();
+      } else {
 #pragma unroll
-      for (int c = 0; c < kTmBK / 8; ++c)
-        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" :: "r"(p_s + sw128_off(tid, c)), "r"(pw[4 * c]), "r"(pw[4 * c + 1]),
-                     "r"(pw[4 * c + 2]), "r"(pw[4 * c + 3]) : "memory");
+        for (int c = 0; c < kTmBK / 8; ++c)
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" :: "r"(p_s + sw128_off(tid, c)), "r"(pw[4 * c]), "r"(pw[4 * c + 1]),
+                       "r"(pw[4 * c + 2]), "r"(pw[4 * c + 3]) : "memory");
+      }
       if (j + 1 == ntiles && kv_end < t0 + kTmBK) {  // rows of V past the end of the sequence must be zero, not stale
-        mbar_wait_abortable(bar(kBarV + b), (j >> 1) & 1, abort_flag);
+        wait(kBarV + b, (j >> 1) & 1);
         if (tid < kTmBK && t0 + tid >= kv_end) {
 #pragma unroll
           for (uint32_t nb = 0; nb < D / 64; ++nb)
@@ -296,13 +318,13 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
                            "r"(0u) : "memory");
         }
       }
-      fence_smem_to_async();
+      if (!kPTmem || (j + 1 == ntiles && kv_end < t0 + kTmBK)) fence_smem_to_async();
       fence_before_sync();
-      mbar_arrive(bar(kBarP));
+      mbar_arrive(bar(kBarP + b));  // one barrier per S/P buffer: a warp that runs a tile ahead must not add to tile j's count
       if (tid == 0) PF_STAMP(j, 12);
     }
 
-    mbar_wait_abortable(bar(kBarPV), (ntiles - 1) & 1, abort_flag);
+    wait(kBarPV, (ntiles - 1) & 1);
     fence_after_sync();
     __syncwarp();
     const float inv = dsum > 0.f ? __fdividef(1.f, dsum) : 0.f;
@@ -348,13 +370,18 @@ static EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-template <int D>
+static bool p_in_tmem() {  // QUEST_PF_PTMEM=0: P through shared memory (A/B hook, read per call)
+  const char* e = std::getenv("QUEST_PF_PTMEM");
+  return !(e && e[0] == '0');
+}
+
+template <int D, bool kPTmem>
 static int launch_tma(const __half* q, __half* o, uint32_t qo_len, const __half* kv, const int32_t* kv_indices,
                       uint32_t num_pages, uint32_t kv_len, int causal, uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_shift,
                       float sc, cudaStream_t s) {
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return QUEST_ERR_UNSUPPORTED;
-  static const cudaError_t attr = cudaFuncSetAttribute(prefill_tma_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  static const cudaError_t attr = cudaFuncSetAttribute(prefill_tma_kernel<D, kPTmem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                        (int)TmSmem<D>::total);
   if (attr != cudaSuccess) return (int)attr;
   CUtensorMap qmap, kvmap;
@@ -381,7 +408,7 @@ static int launch_tma(const __half* q, __half* o, uint32_t qo_len, const __half*
       return QUEST_ERR_UNSUPPORTED;
   }
   dim3 grid((qo_len + kTmBQ - 1) / kTmBQ, Hq);
-  prefill_tma_kernel<D><<<grid, kTmThreads, TmSmem<D>::total, s>>>(qmap, kvmap, o, qo_len, kv_indices, num_pages, kv_len, causal, Hq,
+  prefill_tma_kernel<D, kPTmem><<<grid, kTmThreads, TmSmem<D>::total, s>>>(qmap, kvmap, o, qo_len, kv_indices, num_pages, kv_len, causal, Hq,
                                                                   Hkv, p_shift, sc);
   return QUEST_OK;
 }
@@ -394,11 +421,14 @@ int launch_prefill_tma(const __half* q, __half* o, uint32_t qo_len, const __half
   if (((uintptr_t)q | (uintptr_t)kv) & 15) return QUEST_ERR_UNSUPPORTED;
   uint32_t p_shift = 0;
   while ((1u << p_shift) < P) ++p_shift;
+#define QUEST_TMA_ARGS q, o, qo_len, kv, kv_indices, num_pages, kv_len, causal, Hq, Hkv, P, p_shift, sc, s
+  const bool pt = p_in_tmem();
   switch (D) {
-    case 64: return launch_tma<64>(q, o, qo_len, kv, kv_indices, num_pages, kv_len, causal, Hq, Hkv, P, p_shift, sc, s);
-    case 128: return launch_tma<128>(q, o, qo_len, kv, kv_indices, num_pages, kv_len, causal, Hq, Hkv, P, p_shift, sc, s);
+    case 64: return pt ? launch_tma<64, true>(QUEST_TMA_ARGS) : launch_tma<64, false>(QUEST_TMA_ARGS);
+    case 128: return pt ? launch_tma<128, true>(QUEST_TMA_ARGS) : launch_tma<128, false>(QUEST_TMA_ARGS);
     default: return QUEST_ERR_UNSUPPORTED;
   }
+#undef QUEST_TMA_ARGS
 }
 
 #ifdef QUEST_PF_CLOCKS
@@ -406,6 +436,10 @@ extern "C" int quest_debug_prefill_clocks(unsigned long long* out) {
   return (int)cudaMemcpyFromSymbol(out, g_pf_clk, sizeof(g_pf_clk));
 }
 #endif
+
+extern "C" int quest_debug_prefill_first_timeout(unsigned int* out4) {
+  return (int)cudaMemcpyFromSymbol(out4, g_pf_tma_first, 16);
+}
 
 unsigned int prefill_tma_timeouts() {
   unsigned int v = 0;

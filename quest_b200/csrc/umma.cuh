@@ -46,6 +46,15 @@ __device__ __forceinline__ void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uin
       :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same with the A operand in TMEM (lane = row, 16-bit elements packed two per 32-bit column, 8 columns per K = 16).
+__device__ __forceinline__ void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n}"
+      :: "r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // The mbarrier receives one arrival when every tcgen05.mma issued so far by this thread has completed.
 __device__ __forceinline__ void mma_commit(uint32_t bar_saddr) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar_saddr) : "memory");
@@ -130,7 +139,7 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar_saddr) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar_saddr, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar_saddr), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mbar_wait_abortable(uint32_t bar_saddr, uint32_t parity, volatile uint32_t* abort_flag) {
+__device__ __forceinline__ bool mbar_wait_abortable(uint32_t bar_saddr, uint32_t parity, volatile uint32_t* abort_flag) {
   for (uint32_t spin = 0; spin < (1u << 20); ++spin) {
     uint32_t done;
     asm volatile(
@@ -138,10 +147,11 @@ __device__ __forceinline__ void mbar_wait_abortable(uint32_t bar_saddr, uint32_t
         : "=r"(done)
         : "r"(bar_saddr), "r"(parity)
         : "memory");
-    if (done) return;
-    if ((spin & 63u) == 63u && *abort_flag) return;
+    if (done) return true;
+    if ((spin & 63u) == 63u && *abort_flag) return true;
   }
   *abort_flag = 1u;
+  return false;  // this wait is the one that ran out
 }
 
 // ---- TMA: one box of a tiled tensor map -> shared memory, completion counted in bytes on an mbarrier.

@@ -448,7 +448,7 @@ PREFILL_CASES = [(13, 33, 32, 32, 128, 16), (502, 1110, 8, 8, 128, 16), (64, 64,
 
 
 def _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, causal, impl):
-    if impl == "tma" and (P < 8 or P & (P - 1)):
+    if impl.startswith("tma") and (P < 8 or P & (P - 1)):
         pytest.skip("the TMA kernel covers page sizes 2^n >= 8")
     rounds = [kv_len - qo_len, qo_len] if kv_len > qo_len else [qo_len]
     oc, gc, k, v, rng = make_pair(0, P, Hkv, D, seed=qo_len, rounds=[r for r in rounds if r])
@@ -456,11 +456,14 @@ def _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, causal, impl):
     kvi, *_ = gc.tables()
     old = os.environ.get("QUEST_PF_IMPL")
     if impl:
-        os.environ["QUEST_PF_IMPL"] = impl
+        os.environ["QUEST_PF_IMPL"] = impl.split("_")[0]
+    if impl == "tma_smem":  # the TMA kernel with P handed over through shared memory instead of tensor memory
+        os.environ["QUEST_PF_PTMEM"] = "0"
     try:
         o = K.prefill_with_paged_kv_cache(t(q), gc.kv, kvi, oc.last_page_len, causal, 0, False, 1.0, 1e4)
         torch.cuda.synchronize()
     finally:
+        os.environ.pop("QUEST_PF_PTMEM", None)
         if old is None:
             os.environ.pop("QUEST_PF_IMPL", None)
         else:
@@ -470,7 +473,7 @@ def _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, causal, impl):
     assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL
 
 
-@pytest.mark.parametrize("impl", ["", "tma", "umma", "simt"])  # "": the library's own choice by shape
+@pytest.mark.parametrize("impl", ["", "tma", "tma_smem", "umma", "simt"])  # "": the library's own choice by shape
 @pytest.mark.parametrize("qo_len,kv_len,Hq,Hkv,D,P", PREFILL_CASES)
 def test_prefill_matches_dense_causal(qo_len, kv_len, Hq, Hkv, D, P, impl):
     """quest/tests/test_prefill_attention.py:46-87 + GQA cases of kernels/src/test/test_prefill.cu:407-467; both the

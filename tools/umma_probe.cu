@@ -2,6 +2,7 @@
 //   T1  S[128x64]  = Q[128xD] * K[64xD]^T      (A and B K-major, 128B swizzle; D = 128 -> two 64-wide blocks)
 //   T2  O[128xD]   = P[128x64] * V[64xD]       (A K-major, B MN-major), issued twice with accumulate -> 2x
 //   T3  O *= 0.5 through tcgen05.ld / tcgen05.st, read back
+//   T4  O[128xD]   = P[128x64] * V[64xD] with P in TENSOR MEMORY (fp16 pairs stored with tcgen05.st)
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O2 -std=c++17 -o tools/umma_probe tools/umma_probe.cu
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -18,7 +19,7 @@ using namespace quest::umma;
 constexpr int D = 128, BQ = 128, BK = 64;
 
 __global__ void __launch_bounds__(128) probe(const __half* q, const __half* k, const __half* p, const __half* v, float* s_out,
-                                             float* o_out, float* o_half, uint32_t* status) {
+                                             float* o_out, float* o_half, float* o_ts, uint32_t* status) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* q_s = smem;                    // 2 blocks x [128][128 B]
   uint8_t* k_s = q_s + 2 * BQ * 128;      // 2 blocks x [64][128 B]
@@ -106,6 +107,30 @@ __global__ void __launch_bounds__(128) probe(const __half* q, const __half* k, c
     tmem_ld_wait();
     for (int i = 0; i < 32; ++i) o_half[t * D + c0 + i] = __uint_as_float(r[i]);
   }
+  // T4: this thread's row of P as packed fp16 pairs -> TMEM columns [0,32) of the S region, then the TS form
+  {
+    uint32_t pw[32];
+    for (int i = 0; i < 32; ++i) pw[i] = *reinterpret_cast<const uint32_t*>(p + t * BK + 2 * i);
+    tmem_st32(lane_addr + t_s, pw);
+    tmem_st_wait();
+    fence_before_sync();
+    __syncthreads();
+    if (t == 0) {
+      fence_after_sync();
+      for (uint32_t kk = 0; kk < BK / 16; ++kk) {
+        const uint64_t b = desc_mn_major(smem_u32(v_s) + kk * 2048, BK * 128);
+        mma_f16_ts(t_o, t_s + kk * 8, b, idesc_f16(BQ, D, 1), kk > 0);
+      }
+      mma_commit(smem_u32(bars));
+    }
+    ok &= mbar_wait(smem_u32(bars), 1);
+    fence_after_sync();
+    for (uint32_t c0 = 0; c0 < D; c0 += 32) {
+      tmem_ld32(lane_addr + t_o + c0, r);
+      tmem_ld_wait();
+      for (int i = 0; i < 32; ++i) o_ts[t * D + c0 + i] = __uint_as_float(r[i]);
+    }
+  }
   if (!ok) atomicOr(status + 2, 1u);
   fence_before_sync();
   __syncthreads();
@@ -130,7 +155,7 @@ int main() {
   for (auto& x : p) x = __float2half(rnd());
   for (auto& x : v) x = __float2half(rnd());
   __half *dq, *dk, *dp, *dv;
-  float *ds, *dout, *dhalf;
+  float *ds, *dout, *dhalf, *dts;
   uint32_t* dst;
   CK(cudaMalloc(&dq, q.size() * 2));
   CK(cudaMalloc(&dk, k.size() * 2));
@@ -139,6 +164,7 @@ int main() {
   CK(cudaMalloc(&ds, BQ * BK * 4));
   CK(cudaMalloc(&dout, BQ * D * 4));
   CK(cudaMalloc(&dhalf, BQ * D * 4));
+  CK(cudaMalloc(&dts, BQ * D * 4));
   CK(cudaMalloc(&dst, 16));
   CK(cudaMemset(dst, 0, 16));
   CK(cudaMemcpy(dq, q.data(), q.size() * 2, cudaMemcpyHostToDevice));
@@ -147,17 +173,18 @@ int main() {
   CK(cudaMemcpy(dv, v.data(), v.size() * 2, cudaMemcpyHostToDevice));
   const int smem = 2 * BQ * 128 + 4 * BK * 128 + BQ * 128 + 64;
   CK(cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  probe<<<1, 128, smem>>>(dq, dk, dp, dv, ds, dout, dhalf, dst);
+  probe<<<1, 128, smem>>>(dq, dk, dp, dv, ds, dout, dhalf, dts, dst);
   CK(cudaGetLastError());
   CK(cudaDeviceSynchronize());
-  std::vector<float> s(BQ * BK), o(BQ * D), oh(BQ * D);
+  std::vector<float> s(BQ * BK), o(BQ * D), oh(BQ * D), ots(BQ * D);
   uint32_t st[4];
   CK(cudaMemcpy(s.data(), ds, s.size() * 4, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(o.data(), dout, o.size() * 4, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(oh.data(), dhalf, oh.size() * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(ots.data(), dts, ots.size() * 4, cudaMemcpyDeviceToHost));
   CK(cudaMemcpy(st, dst, 16, cudaMemcpyDeviceToHost));
   printf("smem base & 1023 = %u, tmem base = 0x%08x, barrier timeouts = %u\n", st[0], st[1], st[2]);
-  double e1 = 0, e2 = 0, e3 = 0;
+  double e1 = 0, e2 = 0, e3 = 0, e4 = 0;
   for (int i = 0; i < BQ; ++i)
     for (int j = 0; j < BK; ++j) {
       double acc = 0;
@@ -170,9 +197,11 @@ int main() {
       for (int j = 0; j < BK; ++j) acc += (double)__half2float(p[i * BK + j]) * __half2float(v[j * D + d]);
       e2 = fmax(e2, fabs(2 * acc - o[i * D + d]));
       e3 = fmax(e3, fabs(acc - oh[i * D + d]));
+      e4 = fmax(e4, fabs(acc - ots[i * D + d]));
     }
-  printf("T1 S=QK^T  max|err| = %.3e\nT2 O=2PV   max|err| = %.3e\nT3 O*0.5   max|err| = %.3e\n", e1, e2, e3);
-  const bool pass = e1 < 1e-3 && e2 < 1e-3 && e3 < 1e-3 && st[0] == 0 && st[2] == 0;
+  printf("T1 S=QK^T  max|err| = %.3e\nT2 O=2PV   max|err| = %.3e\nT3 O*0.5   max|err| = %.3e\nT4 O=PV(P in TMEM) max|err| = %.3e\n", e1,
+         e2, e3, e4);
+  const bool pass = e1 < 1e-3 && e2 < 1e-3 && e3 < 1e-3 && e4 < 1e-3 && st[0] == 0 && st[2] == 0;
   printf("%s\n", pass ? "UMMA PROBE PASS" : "UMMA PROBE FAIL");
   if (!pass) {  // a few entries help tell a layout error from a scaling one
     printf("S[0][0..3] = %f %f %f %f\n", s[0], s[1], s[2], s[3]);
