@@ -1,4 +1,4 @@
-"""GPU parity against the REFERENCE's own CUDA kernels (append + metadata, estimate, sparse decode + merge) compiled
+"""GPU parity against the REFERENCE's own CUDA kernels (append + metadata, estimate, sparse decode + merge, prefill) compiled
 for sm_100a from /root/reference by oracle/ref_build/build_ref.sh into oracle/_ref/libquest_ref.so (built in the
 authoring container by __graft_entry__.build(); the .so travels to the GPU box, the reference sources do not).
 
@@ -6,6 +6,7 @@ Same seeded inputs go through both libraries' C entry points:
   - KV pool + per-page min/max metadata: bit-exact
   - estimate scores (fp16): bit-exact
   - sparse decode attention output: max abs err <= 2e-3 (the reference stores fp16 partials, ours fp32)
+  - causal prefill attention output: max abs err <= 2e-3
 The reference's raft top-k is not buildable here; top-k parity is covered in test_gpu_parity.py.
 """
 import ctypes as C
@@ -140,3 +141,35 @@ def test_sparse_decode_vs_reference_kernel(ref, kv_len, budget):
     torch.cuda.synchronize()
     assert torch.isfinite(o_our).all() and torch.isfinite(o_ref).all()
     assert (o_ref.float() - o_our.float()).abs().max().item() <= ATTN_ATOL
+
+
+@pytest.mark.parametrize("qo_len,kv_len", [(200, 200), (1000, 1000), (333, 2100), (4096, 4096)])
+def test_prefill_vs_reference_kernel(ref, qo_len, kv_len):
+    """Causal prefill over the paged cache: our tcgen05 kernels against the reference's BatchPrefillWithPagedKVCache
+    kernel (prefill.cuh:674-869, built for sm_100a in its LongChat-7B configuration: 32 MHA heads x 128, page 16)."""
+    if not hasattr(ref, "ref_prefill"):
+        pytest.skip("libquest_ref.so predates ref_prefill")
+    import quest_b200._kernels as K
+    H, D, P = 32, 128, 16
+    g = torch.Generator(device="cpu").manual_seed(qo_len + kv_len)
+    n_pages = (kv_len + P - 1) // P
+    pool = torch.randn(n_pages + 3, 2, P, H, D, generator=g).half().to(DEV)
+    table = torch.randperm(n_pages + 3, generator=g)[:n_pages].to(torch.int32).to(DEV)
+    q = torch.randn(qo_len, H, D, generator=g).half().to(DEV)
+    last_len = (kv_len - 1) % P + 1
+    o_ref = torch.zeros_like(q)
+    qo_indptr = torch.tensor([0, qo_len], dtype=torch.int32, device=DEV)
+    kv_indptr = torch.tensor([0, n_pages], dtype=torch.int32, device=DEV)
+    torch.cuda.synchronize()
+    assert ref.ref_prefill(p(q), p(o_ref), qo_len, p(qo_indptr), p(pool), p(table), p(kv_indptr), last_len, int(table[-1]),
+                           H, H, D, P) == 0
+    torch.cuda.synchronize()
+    for impl in ("tma", "umma"):
+        os.environ["QUEST_PF_IMPL"] = impl
+        try:
+            o = K.prefill_with_paged_kv_cache(q, pool, table, last_len, True, 0, False, 1.0, 1e4)
+            torch.cuda.synchronize()
+        finally:
+            os.environ.pop("QUEST_PF_IMPL", None)
+        assert K.load_library().quest_debug_prefill_timeouts() == 0
+        assert (o.float() - o_ref.float()).abs().max().item() <= ATTN_ATOL, impl
