@@ -119,7 +119,10 @@ int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, uint32_t nu
 size_t quest_decode_workspace_bytes(uint32_t num_qo_heads, uint32_t head_dim, uint32_t num_chunks);
 /* q, o: [num_qo_heads, head_dim]; indices: [num_qo_heads, num_sel_pages] page ids with row stride
  * idx_row_stride; the page last_page_idx holding last_page_len tokens is always attended in
- * addition.  lse (fp32 [num_qo_heads], base-2, may be NULL). */
+ * addition.  lse (fp32 [num_qo_heads], base-2, may be NULL).
+ * Sequence-sharded use: an id < 0 in `indices` is a selected page that another shard holds and
+ * contributes no rows; last_page_len = 0 means this shard does not hold the last page.  A head with no rows at
+ * all gets o = 0 and lse = -inf, the identity of quest_merge_states. */
 int quest_decode_run(const void* q, void* o, float* lse,
                      const void* kv_data, const int32_t* indices, uint32_t idx_row_stride,
                      uint32_t num_sel_pages, uint32_t last_page_idx, uint32_t last_page_len,
@@ -173,8 +176,11 @@ int quest_prefill(const void* q, void* o, uint32_t qo_len,
 
 /* ---- combine of partial attention states (sequence-sharded multi-GPU path) ----------------------
  * Merges n partial states (o_i fp32 [n, num_heads, head_dim] normalised, lse_i fp32 [n, num_heads]
- * base-2) into o fp16 [num_heads, head_dim]: flashinfer state.cuh:53-62 / cascade.cuh:279-340. */
-int quest_merge_states(const float* o_parts, const float* lse_parts, uint32_t n,
+ * base-2) into o fp16 [num_heads, head_dim]: flashinfer state.cuh:53-62 / cascade.cuh:279-340.
+ * part_stride: floats between consecutive parts in BOTH arrays when each rank's (o, lse) pair travels as one
+ * packed record of an all-gather (o_parts = base, lse_parts = base + num_heads*head_dim); 0 = two dense arrays.
+ * A part with lse = -inf (a shard that held none of a head's pages) has weight 0. */
+int quest_merge_states(const float* o_parts, const float* lse_parts, uint32_t n, uint32_t part_stride,
                        void* o, float* lse, uint32_t num_heads, uint32_t head_dim, void* stream);
 
 /* Counters for bench/tests: number of kernels this library has launched since load / last reset. */

@@ -35,7 +35,7 @@ SIGNATURES = {
     "quest_decode_layer_step": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32,
                                            _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _c.c_int, _u32, _u32, _u32, _u32, _vp]),
-    "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _vp, _vp, _u32, _u32, _vp]),
+    "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _u32, _vp, _vp, _u32, _u32, _vp]),
     "quest_launch_count": (_c.c_uint64, []),
     "quest_launch_count_reset": (None, []),
 }

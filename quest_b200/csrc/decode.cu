@@ -114,8 +114,9 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
   uint32_t nv_ld = 0;  // valid tokens of the page under the cursor
   auto open_page = [&]() {
     if (pg_ld < npg) {
-      ptr = kvb + (uint64_t)(uint32_t)s_pages[pg_ld] * page_bytes;
-      nv_ld = pg_ld < n_sel_local ? P : last_page_len;
+      const int32_t pid = s_pages[pg_ld];  // < 0: a selected page another sequence shard holds -> no rows
+      ptr = kvb + (uint64_t)(uint32_t)pid * page_bytes;
+      nv_ld = pid < 0 ? 0u : (pg_ld < n_sel_local ? P : last_page_len);
     } else {
       nv_ld = 0;
     }
@@ -206,9 +207,9 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
       const uint32_t col = tid + c * kThreads;
-      if (col < D) o[(size_t)h * D + col] = __float2half_rn(__fdividef(osum[c], dsum));
+      if (col < D) o[(size_t)h * D + col] = __float2half_rn(dsum > 0.f ? __fdividef(osum[c], dsum) : 0.f);
     }
-    if (lse && tid == 0) lse[h] = M + lg2(dsum);
+    if (lse && tid == 0) lse[h] = dsum > 0.f ? M + lg2(dsum) : -INFINITY;
     return;
   }
   float* ws_o = reinterpret_cast<float*>(ws + ws_o_off(Hq, nchunks));
@@ -297,10 +298,10 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
     const uint32_t col = tid + c * kThreads;
-    if (col < D) o[(size_t)h * D + col] = __float2half_rn(__fdividef(of[c], df));
+    if (col < D) o[(size_t)h * D + col] = __float2half_rn(df > 0.f ? __fdividef(of[c], df) : 0.f);
   }
   if (tid == 0) {
-    if (lse) lse[h] = Mf + lg2(df);
+    if (lse) lse[h] = df > 0.f ? Mf + lg2(df) : -INFINITY;
     ticket[h] = 0;  // ready for the next launch
   }
   D_STAMP(5);  // head merged
@@ -367,7 +368,7 @@ extern "C" int quest_decode_run(const void* q, void* o, float* lse, const void* 
     return QUEST_ERR_BAD_ARG;
   if (num_sel_pages && !indices) return QUEST_ERR_BAD_ARG;
   if (num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
-  if (last_page_len < 1 || last_page_len > page_size) return QUEST_ERR_BAD_ARG;
+  if (last_page_len > page_size) return QUEST_ERR_BAD_ARG;  // 0: this shard does not hold the last page
   const uint32_t nchunks = (num_sel_pages + 1 + pages_per_chunk - 1) / pages_per_chunk;
   if (nchunks > 1) {
     if (!workspace || workspace_bytes < quest_decode_workspace_bytes(num_qo_heads, head_dim, nchunks))

@@ -83,19 +83,20 @@ rms_norm_kernel(const __half* __restrict__ in, const __half* __restrict__ w, __h
 }
 
 // o = sum_i o_i 2^(lse_i - L) / sum_i 2^(lse_i - L): merge of normalised partial states.
+// Part i's o block starts at o_parts + i*so, its lse block at lse_parts + i*sl (dense: so = H*D, sl = H).
 __global__ void merge_states_kernel(const float* __restrict__ o_parts, const float* __restrict__ lse_parts,
-                                    uint32_t n, __half* __restrict__ o, float* __restrict__ lse, uint32_t H,
-                                    uint32_t D) {
+                                    uint32_t n, size_t so, size_t sl, __half* __restrict__ o,
+                                    float* __restrict__ lse, uint32_t H, uint32_t D) {
   pdl_wait();
   const uint32_t h = blockIdx.x;
   float L = -1e30f;
-  for (uint32_t i = 0; i < n; ++i) L = fmaxf(L, lse_parts[(size_t)i * H + h]);
+  for (uint32_t i = 0; i < n; ++i) L = fmaxf(L, lse_parts[i * sl + h]);
   float den = 0.f;
-  for (uint32_t i = 0; i < n; ++i) den += ex2(lse_parts[(size_t)i * H + h] - L);
+  for (uint32_t i = 0; i < n; ++i) den += ex2(lse_parts[i * sl + h] - L);
   for (uint32_t c = threadIdx.x; c < D; c += blockDim.x) {
     float acc = 0.f;
     for (uint32_t i = 0; i < n; ++i)
-      acc += o_parts[((size_t)i * H + h) * D + c] * ex2(lse_parts[(size_t)i * H + h] - L);
+      acc += o_parts[i * so + (size_t)h * D + c] * ex2(lse_parts[i * sl + h] - L);
     o[(size_t)h * D + c] = __float2half_rn(__fdividef(acc, den));
   }
   if (lse && threadIdx.x == 0) lse[h] = L + lg2(den);
@@ -132,10 +133,12 @@ extern "C" int quest_rms_norm(const void* in, const void* weight, void* out, uin
   QUEST_RETURN_LAUNCH();
 }
 
-extern "C" int quest_merge_states(const float* o_parts, const float* lse_parts, uint32_t n, void* o, float* lse,
-                                  uint32_t num_heads, uint32_t head_dim, void* stream) {
+extern "C" int quest_merge_states(const float* o_parts, const float* lse_parts, uint32_t n, uint32_t part_stride,
+                                  void* o, float* lse, uint32_t num_heads, uint32_t head_dim, void* stream) {
   if (!o_parts || !lse_parts || !o || !n || !num_heads || !head_dim) return QUEST_ERR_BAD_ARG;
-  quest::merge_states_kernel<<<num_heads, 128, 0, (cudaStream_t)stream>>>(o_parts, lse_parts, n, (__half*)o, lse,
-                                                                          num_heads, head_dim);
+  if (part_stride && part_stride < num_heads * head_dim) return QUEST_ERR_BAD_ARG;
+  const size_t so = part_stride ? part_stride : (size_t)num_heads * head_dim, sl = part_stride ? part_stride : num_heads;
+  quest::merge_states_kernel<<<num_heads, 128, 0, (cudaStream_t)stream>>>(o_parts, lse_parts, n, so, sl, (__half*)o,
+                                                                          lse, num_heads, head_dim);
   QUEST_RETURN_LAUNCH();
 }

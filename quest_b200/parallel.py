@@ -14,10 +14,13 @@ decode_attn.cuh:454-457,1127):
   (2) the partial attention states (o, lse) over each rank's share of the selected pages are all-gathered and merged
   with the log-sum-exp rule (flashinfer state.cuh:53-62; quest_merge_states on the GPU).
 
-The functions take torch tensors on the process group's device (CUDA with NCCL; CPU with gloo in the tests) and use
-only torch ops plus the collectives: they are the host-side glue around the CUDA kernels, not a compute path.
+The module-level functions take torch tensors on the process group's device (CUDA with NCCL; CPU with gloo in the
+tests) and use only torch ops plus the collectives: they state the exchange protocol.  `SeqShardedDecode` is the
+CUDA path of the same protocol: every selection, attention and merge step is a libquest_b200 kernel, the two
+exchanges are one NCCL all-gather each.
 """
-from typing import Optional, Tuple
+import ctypes
+from typing import List, Optional, Sequence, Tuple
 
 import torch
 import torch.distributed as dist
@@ -92,3 +95,150 @@ def combine_partials(o: torch.Tensor, lse: torch.Tensor, group: Optional[dist.Pr
     w = torch.exp2(L - m)                              # state.cuh:53-62 with base-2 exponents
     w = torch.where(torch.isfinite(L), w, torch.zeros_like(w))
     return (O * w.unsqueeze(-1)).sum(dim=0) / w.sum(dim=0).unsqueeze(-1)
+
+
+class SeqShardedDecode:
+    """One rank's side of a sequence-sharded decode step on the GPU (BASELINE.json configs[4]).
+
+    The rank holds an ordinary `quest_b200.utils.InferenceController` over ITS pages only (own KV pool, own metadata
+    pool, own page tables; filled through append_kv like any sequence).  Ranks own ascending, contiguous ranges of
+    the sequence's pages; the last rank also holds the growing last page, which is always attended and never scored
+    (reference decode_page.cuh:325-351).  Per layer step:
+
+      1. candidates: [append on the last rank] -> quest_estimate over the local pages -> quest_topk keeps the best
+         c = min(k, n_local) of each head: scores into this rank's slot of the exchange buffer, LOCAL physical page
+         ids kept at home.
+      2. exchange 1 (all-gather of fp16 [Hq, c] scores, ~Hq*c*2 bytes per rank).  Only scores travel: ranks are
+         concatenated in page order and quest_topk breaks ties by input position, so the global selection is the
+         single-GPU one bit for bit, on every rank, without positions on the wire.
+      3. select: quest_topk over the [Hq, R*c] gathered scores with a payload row that holds this rank's physical
+         page ids in its own columns and -1 elsewhere -> [Hq, k] ids where -1 marks "another rank's page".
+      4. attend: quest_decode_run over those ids (negative ids contribute no rows; last_page_len = 0 off the last
+         rank) -> normalised partial o and base-2 lse per head (-inf if the rank held none of the head's pages).
+      5. exchange 2 (all-gather of one packed fp32 record [Hq*D + Hq] per rank) -> quest_merge_states
+         (flashinfer state.cuh:53-62) -> fp16 o, identical on every rank.
+
+    The phases are separate methods so that a single process can drive several shards and stand in for the
+    collectives (tests/test_gpu_parity.py); `layer_step` runs them with torch.distributed.
+    """
+
+    def __init__(self, ic, num_qo_heads: int, world: int, rank: int, page_budget: int,
+                 group: Optional[dist.ProcessGroup] = None):
+        from quest_b200 import _kernels
+        self._K = _kernels
+        self.lib = _kernels.load_library()
+        self.ic, self.Hq, self.R, self.r, self.group = ic, int(num_qo_heads), int(world), int(rank), group
+        self.k = int(page_budget) - 1  # pages selected among the scored ones; the last page comes on top
+        self.Hkv, self.D, self.P = ic.num_kv_heads, ic.head_dim, ic.page_size
+        self.has_last = self.r == self.R - 1
+        self.dev = ic.device
+        self._key = None
+        sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
+        ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
+        _kernels._rc(self.lib.quest_decode_plan(self.k, self.Hq, self.Hkv, self.D, self.P, sms, ctypes.byref(ppc),
+                                                ctypes.byref(nch)), "quest_decode_plan")
+        self.ppc = ppc.value
+        self.ws = torch.zeros(self.lib.quest_decode_workspace_bytes(self.Hq, self.D, nch.value), dtype=torch.uint8,
+                              device=self.dev)
+        self.sel = torch.full((self.Hq, max(self.k, 1)), -1, dtype=torch.int32, device=self.dev)
+        self.o16 = torch.empty(self.Hq, self.D, dtype=torch.float16, device=self.dev)
+        self.rec = torch.zeros(self.Hq * self.D + self.Hq, dtype=torch.float32, device=self.dev)
+        self.rec_all = torch.empty(self.R, self.Hq * self.D + self.Hq, dtype=torch.float32, device=self.dev)
+        self.out = torch.empty(1, self.Hq, self.D, dtype=torch.float16, device=self.dev)
+
+    # -- per-layout buffers (the layout changes only when a rank gains a page)
+    def begin_step(self, scored_pages_per_rank: Sequence[int]):
+        """scored_pages_per_rank[r] = pages of rank r that take part in the selection (all of its pages; on the last
+        rank all but the last).  Call after the controller reserved the new token (prepare_metadata on the last rank)."""
+        n = [int(x) for x in scored_pages_per_rank]
+        if len(n) != self.R:
+            raise ValueError("scored_pages_per_rank needs one entry per rank")
+        ic = self.ic
+        ic.sync_tables()
+        local_pages = len(ic.kv_cache.indicies)
+        if n[self.r] != local_pages - (1 if self.has_last else 0):
+            raise ValueError(f"rank {self.r}: controller holds {local_pages} pages, layout says {n[self.r]} scored")
+        if sum(n) < self.k:
+            raise ValueError("fewer scored pages than the budget selects: attend to everything instead")
+        key = tuple(n)
+        if key == self._key:
+            return
+        self._key = key
+        self.n_local = n[self.r]
+        self.c_max = min(self.k, max(n))
+        self.c_loc = min(self.k, self.n_local)
+        Hq, R, c = self.Hq, self.R, self.c_max
+        f16 = dict(dtype=torch.float16, device=self.dev)
+        self.scores = torch.empty(Hq, max(self.n_local, 1), **f16)
+        self.cand_s = torch.full((Hq, c), -float("inf"), **f16)        # my slot of exchange 1 (padding sorts last)
+        self.cand_tmp = self.cand_s if self.c_loc == c else torch.empty(Hq, max(self.c_loc, 1), **f16)
+        self.cand_p = torch.empty(Hq, max(self.c_loc, 1), dtype=torch.int32, device=self.dev)
+        self.gath = torch.empty(R, Hq, c, **f16)
+        self.all_s = torch.empty(Hq, R, c, **f16)
+        self.pay = torch.full((Hq, R, c), -1, dtype=torch.int32, device=self.dev)
+
+    def _st(self):
+        return torch.cuda.current_stream().cuda_stream
+
+    def candidates(self, q: torch.Tensor, k_new: Optional[torch.Tensor], v_new: Optional[torch.Tensor], layer: int):
+        """Phase 1.  q: [1, Hq, D] fp16; k_new, v_new: [1, Hkv, D] (used on the last rank only).  Returns this
+        rank's exchange-1 message, fp16 [Hq, c]."""
+        ic, lib, rc = self.ic, self.lib, self._K._rc
+        kv, meta = ic.kv_cache.buf_layer(layer), ic.metadata_cache.buf_layer(layer)
+        if self.has_last and k_new is not None:
+            rc(lib.quest_append_decode(k_new.data_ptr(), v_new.data_ptr(), kv.data_ptr(), ic.kv_indices_with_last.data_ptr(),
+                                       ic.kv_indices_with_last.numel(), ic.kv_cache.last_page_len, meta.data_ptr(),
+                                       ic.metadata_indices.data_ptr(), ic.metadata_indices.numel(),
+                                       ic.metadata_cache.last_page_len, self.Hkv, self.D, self.P, self._st()), "append")
+        if self.c_loc:
+            rc(lib.quest_estimate(q.data_ptr(), self.scores.data_ptr(), self.n_local, meta.data_ptr(),
+                                  ic.metadata_indices.data_ptr(), self.Hq, self.Hkv, self.D, self.P,
+                                  self._K.EST_META_ORDERED, self._st()), "estimate")
+            rc(lib.quest_topk(self.scores.data_ptr(), ic.kv_indices_with_last.data_ptr(), 0, self.cand_tmp.data_ptr(),
+                              self.cand_p.data_ptr(), self.Hq, self.n_local, self.c_loc, self._st()), "local top-k")
+            if self.cand_tmp is not self.cand_s:
+                self.cand_s[:, :self.c_loc].copy_(self.cand_tmp)
+        return self.cand_s
+
+    def select(self, gathered: torch.Tensor) -> torch.Tensor:
+        """Phase 3.  gathered: fp16 [R, Hq, c], the ranks' messages in rank order.  Returns int32 [Hq, k]: this rank's
+        physical page ids of the globally selected pages, -1 where another rank holds the page."""
+        if self.k == 0:
+            return self.sel[:, :0]
+        self.all_s.copy_(gathered.permute(1, 0, 2))
+        if self.c_loc:
+            self.pay[:, self.r, :self.c_loc].copy_(self.cand_p)
+        n = self.R * self.c_max
+        self._K._rc(self.lib.quest_topk(self.all_s.data_ptr(), self.pay.data_ptr(), n, None, self.sel.data_ptr(), self.Hq,
+                                        n, self.k, self._st()), "global top-k")
+        return self.sel[:, :self.k]
+
+    def attend(self, q: torch.Tensor, layer: int) -> torch.Tensor:
+        """Phase 4.  Returns this rank's exchange-2 message: fp32 [Hq*D + Hq] = normalised partial o, then lse."""
+        ic = self.ic
+        HD = self.Hq * self.D
+        last_idx = ic.kv_last_page_idx if self.has_last else 0
+        last_len = ic.kv_cache.last_page_len if self.has_last else 0
+        self._K._rc(self.lib.quest_decode_run(q.data_ptr(), self.o16.data_ptr(), self.rec.data_ptr() + HD * 4,
+                                              ic.kv_cache.buf_layer(layer).data_ptr(), self.sel.data_ptr(), self.k, self.k,
+                                              last_idx, last_len, self.Hq, self.Hkv, self.D, self.P, self.ppc,
+                                              self.ws.data_ptr(), self.ws.numel(), self._st()), "decode")
+        self.rec[:HD].copy_(self.o16.view(-1))
+        return self.rec
+
+    def merge(self, records: torch.Tensor) -> torch.Tensor:
+        """Phase 5.  records: fp32 [R, Hq*D + Hq].  Returns fp16 [1, Hq, D]."""
+        HD = self.Hq * self.D
+        self._K._rc(self.lib.quest_merge_states(records.data_ptr(), records.data_ptr() + HD * 4, self.R, HD + self.Hq,
+                                                self.out.data_ptr(), None, self.Hq, self.D, self._st()), "merge")
+        return self.out
+
+    def layer_step(self, q, k_new, v_new, layer: int) -> torch.Tensor:
+        """All five phases with the process group's collectives (NCCL).  Every rank passes the same q; k_new / v_new
+        matter on the last rank only.  Returns fp16 [1, Hq, D], identical on every rank."""
+        msg = self.candidates(q, k_new, v_new, layer)
+        dist.all_gather_into_tensor(self.gath, msg, group=self.group)
+        self.select(self.gath)
+        rec = self.attend(q, layer)
+        dist.all_gather_into_tensor(self.rec_all, rec, group=self.group)
+        return self.merge(self.rec_all)

@@ -84,19 +84,25 @@ class InferenceController:
             self._indptr_cache[n] = t
         return t
 
+    def sync_tables(self):
+        """Bring the device page tables up to date with the host lists (one small H2D copy per newly allocated page)
+        and refresh the views / host ids derived from them."""
+        kv_ids, meta_ids = self.kv_cache.indicies, self.metadata_cache.indicies
+        self._kv_synced = self._sync_table(self._kv_table, kv_ids, self._kv_synced)
+        self._meta_synced = self._sync_table(self._meta_table, meta_ids, self._meta_synced)
+        self.kv_indptr_for_append = self._indptr(len(kv_ids))
+        self.metadata_indptr_for_append = self._indptr(len(meta_ids))
+        self.kv_last_page_idx = kv_ids[-1]
+        self.metadata_last_page_idx = meta_ids[-1]
+        self.kv_indices_with_last = self._kv_table[:len(kv_ids)]
+        self.metadata_indices = self._meta_table[:len(meta_ids)]
+
     # Prepare metadata used for inference under certain PAGE_BUDGET (called per budget change).
     def begin_forward(self, seq_len: int, updateTensor: bool = True):
         self._step = None
-        kv_ids, meta_ids = self.kv_cache.indicies, self.metadata_cache.indicies
+        kv_ids = self.kv_cache.indicies
         if updateTensor:
-            self._kv_synced = self._sync_table(self._kv_table, kv_ids, self._kv_synced)
-            self._meta_synced = self._sync_table(self._meta_table, meta_ids, self._meta_synced)
-            self.kv_indptr_for_append = self._indptr(len(kv_ids))
-            self.metadata_indptr_for_append = self._indptr(len(meta_ids))
-            self.kv_last_page_idx = kv_ids[-1]
-            self.metadata_last_page_idx = meta_ids[-1]
-            self.kv_indices_with_last = self._kv_table[:len(kv_ids)]
-            self.metadata_indices = self._meta_table[:len(meta_ids)]
+            self.sync_tables()
 
         if seq_len > 1:
             return  # prefill: append_kv_cache_prefill and prefill_with_paged_kv_cache need nothing else

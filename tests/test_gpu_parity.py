@@ -523,11 +523,21 @@ def test_merge_states():
     l = torch.empty(H, dtype=torch.float32, device=DEV)
     lib = K.load_library()
     to, tl = t(o_parts), t(lse)
-    assert lib.quest_merge_states(to.data_ptr(), tl.data_ptr(), n, o.data_ptr(), l.data_ptr(), H, D,
+    assert lib.quest_merge_states(to.data_ptr(), tl.data_ptr(), n, 0, o.data_ptr(), l.data_ptr(), H, D,
                                   torch.cuda.current_stream().cuda_stream) == 0
     wo, wl = orc.merge_states(o_parts, lse)
     np.testing.assert_allclose(o.float().cpu().numpy(), wo, rtol=2e-3, atol=2e-3)
     np.testing.assert_allclose(l.cpu().numpy(), wl, rtol=1e-4, atol=1e-4)
+    # packed records (one all-gather message per rank: o then lse), one part without any rows (lse = -inf)
+    lse2 = lse.copy()
+    lse2[2] = -np.inf
+    rec = t(np.concatenate([o_parts.reshape(n, -1), lse2], axis=1))
+    o2 = torch.empty_like(o)
+    assert lib.quest_merge_states(rec.data_ptr(), rec.data_ptr() + H * D * 4, n, H * D + H, o2.data_ptr(), None, H, D,
+                                  torch.cuda.current_stream().cuda_stream) == 0
+    keep = [0, 1, 3, 4]
+    wo2, _ = orc.merge_states(o_parts[keep], lse[keep])
+    np.testing.assert_allclose(o2.float().cpu().numpy(), wo2, rtol=2e-3, atol=2e-3)
 
 
 def test_error_behaviour_matches_reference_checks():
