@@ -155,13 +155,17 @@ __device__ __forceinline__ float reduce4_transposed(const float a[4], uint32_t l
   return v;
 }
 
-// kG = 1: MHA, q and sign mask of the lane's head live in registers.  kG = 0: any group size, q/mask in smem.
+// kG = 1: every lane row keeps ONE q head for the whole kernel, q and its sign mask in registers.  MHA, and GQA with a
+// power-of-two group (g_shift = log2 G) whose q heads divide the row tile: the G lane rows of a group read the same
+// kv-head row (the two rows of one warp-wide load coalesce; rows in different warps are served by L2), so the
+// arithmetic per lane and the refill-after-use ring are exactly the MHA ones and DRAM still sees every byte once.
+// kG = 0: any group size, one lane row per kv head looping over its q heads, q/mask in smem.
 template <int D, int kOrdered, int kG>
 __global__ void __launch_bounds__(kTileWarps * 32, 2)
 estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t len,
                      const __half* __restrict__ meta, const int32_t* __restrict__ meta_indices,
                      uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_magic /* ceil(2^32/P), 0 for P=1 */,
-                     uint32_t meta_stable, const AppendArgs ap) {
+                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap) {
   constexpr int LPR = D / 8, RPL = 32 / LPR, kThreads = kTileWarps * 32, kDepth = 4;
   constexpr uint32_t T_r = kTileWarps * RPL;  // metadata rows per CTA pass; Hkv divides T_r
   extern __shared__ __align__(16) uint8_t est_smem[];
@@ -172,9 +176,10 @@ estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
   const uint32_t G = kG ? kG : Hq / Hkv;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lir = lane % LPR, rsub = lane / LPR;
-  const uint32_t PPP = T_r / Hkv;                       // pages per CTA pass
+  const uint32_t HV = kG == 1 ? Hq : Hkv;               // heads a pass walks per page: q heads (kG = 1) or kv heads
+  const uint32_t PPP = T_r / HV;                        // pages per CTA pass
   const uint32_t rt = warp * RPL + rsub;                // this lane's row in the pass
-  const uint32_t pg_in = rt / Hkv, kvh = rt - pg_in * Hkv;
+  const uint32_t pg_in = rt / HV, kvh = rt - pg_in * HV;  // kG = 1: kvh is the lane's q head
   // contiguous page range of this CTA, balanced to one page
   // with an append to carry, the last CTA does only that and the scan is shared by the others
   const uint32_t n_scan = ap.k != nullptr ? gridDim.x - 1 : gridDim.x;
@@ -182,7 +187,7 @@ estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
   const uint32_t p_begin = scans ? (uint32_t)(((uint64_t)blockIdx.x * len) / n_scan) : 0u;
   const uint32_t p_end = scans ? (uint32_t)(((uint64_t)(blockIdx.x + 1) * len) / n_scan) : 0u;
   const uint32_t row_bytes = Hkv * D * 2, slab_bytes = P * row_bytes;
-  const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + (size_t)kvh * (D * 2) + lir * 16;
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + (size_t)(kG == 1 ? kvh >> g_shift : kvh) * (D * 2) + lir * 16;
 
   // append_kv of the step's new token rides on one extra CTA of this launch.  The entry it updates (the last
   // page's) is not one of the scored ones; the decode kernel two launches later reads the new K/V row.
@@ -328,18 +333,22 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     if (num_sms <= 0) num_sms = 148;
   }
-  const uint32_t G = Hq / Hkv, PPP = T_r / Hkv;
+  const uint32_t G = Hq / Hkv;
+  const bool per_q = (G & (G - 1)) == 0 && T_r % Hq == 0;  // one q head per lane row (MHA and power-of-two groups)
+  uint32_t g_shift = 0;
+  while ((1u << g_shift) < G) ++g_shift;
+  const uint32_t PPP = T_r / (per_q ? Hq : Hkv);
   uint32_t grid = 2 * num_sms - (ap.k != nullptr ? 1u : 0u);  // scanning CTAs
   const uint32_t need = (len + PPP - 1) / PPP;  // at least one pass of pages per CTA
   if (grid > need) grid = need;
   if (ap.k != nullptr) ++grid;  // + the CTA that carries the append
   const uint32_t n_meta = (len + P - 1) / P;
   size_t smem = ((size_t)n_meta * 4 + 15) & ~(size_t)15;
-  if (G != 1) smem += (size_t)Hq * D * 6;
+  if (!per_q) smem += (size_t)Hq * D * 6;
   if (smem > 100 * 1024) return QUEST_ERR_UNSUPPORTED;
   const bool ord = flags & QUEST_EST_META_ORDERED;
-  auto kern = G == 1 ? (ord ? estimate_tile_kernel<D, 1, 1> : estimate_tile_kernel<D, 0, 1>)
-                     : (ord ? estimate_tile_kernel<D, 1, 0> : estimate_tile_kernel<D, 0, 0>);
+  auto kern = per_q ? (ord ? estimate_tile_kernel<D, 1, 1> : estimate_tile_kernel<D, 0, 1>)
+                    : (ord ? estimate_tile_kernel<D, 1, 0> : estimate_tile_kernel<D, 0, 0>);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -356,7 +365,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   cfg.numAttrs = 1;
   const uint32_t p_magic = P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P);
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta, meta_indices,
-                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, ap);
+                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }

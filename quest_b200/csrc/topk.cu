@@ -34,33 +34,33 @@ topk_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_
                  out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr);
 }
 
-template <int W>
+template <int W, int G>
 __global__ void __launch_bounds__(32 * W)
 topk_fast_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_idx, uint32_t in_stride,
                  uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx, uint32_t len, uint32_t k) {
-  __shared__ __align__(16) uint16_t keys[4 * 32 * W];
-  __shared__ TopkFastScratch<W> sc;
+  constexpr int NK = 4 * G;  // keys per thread
+  __shared__ __align__(16) uint16_t keys[NK * 32 * W];
+  __shared__ TopkFastScratch<W, G> sc;
   constexpr uint32_t T = 32 * W;
   const uint32_t head = blockIdx.x, tid = threadIdx.x;
   const uint16_t* s = scores + (size_t)head * len;
-  const uint32_t len8 = (len + 7) & ~7u;
 #if QUEST_TRIG_TOPK
   pdl_trigger();
 #endif
   pdl_wait();  // scores come from the estimate kernel
-  // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent (4 per thread)
-  uint16_t v[4];
+  // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent (NK per thread); the whole key
+  // array is written (0xffff -> key 0 past the row's end)
+  uint16_t v[NK];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) v[j] = tid + j * T < len ? s[tid + j * T] : (uint16_t)0xffffu;  // 0xffff -> key 0
+  for (int j = 0; j < NK; ++j) v[j] = tid + j * T < len ? s[tid + j * T] : (uint16_t)0xffffu;
 #pragma unroll
-  for (int j = 0; j < 4; ++j)
-    if (tid + j * T < len8) keys[tid + j * T] = key_of(v[j]);
+  for (int j = 0; j < NK; ++j) keys[tid + j * T] = key_of(v[j]);
   __syncthreads();
-  topk_select_fast<W>(keys, len, k, tid, 1, &sc, in_idx ? in_idx + (size_t)head * in_stride : nullptr,
-                      out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr);
+  topk_select_fast<W, TopkNoHook, G>(keys, len, k, tid, 1, &sc, in_idx ? in_idx + (size_t)head * in_stride : nullptr,
+                                     out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr);
 }
 
-template <int W>
+template <int W, int G>
 static int launch_topk_fast(const void* scores, const int32_t* in_idx, uint32_t in_stride, void* out_val, int32_t* out_idx,
                             uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream) {
   cudaLaunchConfig_t cfg = {};
@@ -72,7 +72,7 @@ static int launch_topk_fast(const void* scores, const int32_t* in_idx, uint32_t 
   attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_fast_kernel<W>, (const uint16_t*)scores, in_idx, in_stride,
+  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_fast_kernel<W, G>, (const uint16_t*)scores, in_idx, in_stride,
                                      (uint16_t*)out_val, out_idx, len, k);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
@@ -115,9 +115,11 @@ extern "C" int quest_topk(const void* scores, const int32_t* in_idx, uint32_t in
   if (len > quest::kTopkMaxLen) return QUEST_ERR_UNSUPPORTED;
   cudaStream_t s = (cudaStream_t)stream;
   static const bool no_fast = getenv("QUEST_TOPK_GENERIC") != nullptr;  // test hook: force the generic kernels
-  if (!no_fast && len <= 1024) return quest::launch_topk_fast<8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
-  if (!no_fast && len <= 2048) return quest::launch_topk_fast<16>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
-  if (!no_fast && len <= 4096) return quest::launch_topk_fast<32>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (!no_fast && len <= 1024) return quest::launch_topk_fast<8, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (!no_fast && len <= 2048) return quest::launch_topk_fast<16, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (!no_fast && len <= 4096) return quest::launch_topk_fast<32, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (!no_fast && len <= 8192) return quest::launch_topk_fast<32, 2>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (!no_fast && len <= 16384) return quest::launch_topk_fast<32, 4>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (len <= 2048) return quest::launch_topk<16, 4>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (len <= 8192) return quest::launch_topk<32, 8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   return quest::launch_topk<32, 8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);

@@ -43,18 +43,20 @@ __device__ __forceinline__ uint64_t shl64_clamped(uint32_t s) {  // 1 << s, 0 fo
 #define TOPK_FAST_STAMP(i) do { } while (0)  // fused.cu's timeline build stamps the passes
 #endif
 
-template <int W>
+template <int W, int G = 1>
 struct TopkFastScratch {
-  uint8_t histT[2][16][W];  // [pass parity][bin][warp]: per-warp bin totals (<= 128 each)
+  uint8_t histT[2][16][W * G];  // [pass parity][bin][warp * G + key group]: bin totals of 128 keys (<= 128 each)
   uint32_t wgt[W], weq[W];
 };
 
-// Fast path for n <= 4 * 32 * W: every thread owns 4 consecutive keys (two packed words) held in registers for
-// the whole selection.  The counting loop is bound by the integer pipe (half rate on this part), so it is
+// Fast path for n <= 4 * G * 32 * W: every thread owns 4*G consecutive keys (2*G packed words) held in registers
+// for the whole selection.  The counting loop is bound by the integer pipe (half rate on this part), so it is
 // written for instruction count: per key a 128-bit one-hot (8-bit field per bin) is built with two clamped
-// 64-bit shifts and added into 4 words (fields cannot carry: a thread adds at most 4, a warp at most 128, so
-// REDUX runs on the 8-bit fields directly); bin totals are published transposed so that lane b sums its bin
-// over all warps with one 128-bit load and dp4a.
+// 64-bit shifts and added into 4 words per group of 4 keys (fields cannot carry: a thread adds at most 4 per
+// group, a warp at most 128, so REDUX runs on the 8-bit fields directly); bin totals are published transposed so
+// that lane b sums its bin over all warps and groups with 128-bit loads and dp4a.
+// G > 1 (8 or 16 keys per thread: rows of up to 8192 / 16384 pages on 32 warps) needs the key array zero-padded to
+// the full 4*G*32*W entries.
 // Hook: called by every thread of the group once the selection is decided and before the ids are written, with
 // the selection as one word for consumers that hold the keys themselves (fused.cu): position i is selected iff
 // key > tau or (key == tau and i < tie_cut); word = 1<<63 | tie_cut<<16 | tau.  `holder` is true for the one thread
@@ -63,23 +65,39 @@ struct TopkNoHook {
   __device__ __forceinline__ void operator()(bool, unsigned long long) const {}
 };
 
-template <int W, class Hook = TopkNoHook>
+template <int W, class Hook = TopkNoHook, int G = 1>
 __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t n, uint32_t k, uint32_t t,
-                                                 uint32_t bar_id, TopkFastScratch<W>* sc,
+                                                 uint32_t bar_id, TopkFastScratch<W, G>* sc,
                                                  const int32_t* __restrict__ in_idx, int32_t* __restrict__ out_idx,
                                                  uint16_t* __restrict__ out_val, Hook hook = Hook()) {
   static_assert(W == 4 || W == 8 || W == 16 || W == 32, "W bytes per bin row are read as 32-bit words");
+  static_assert(G == 1 || G == 2 || G == 4, "4, 8 or 16 keys per thread");
   constexpr uint32_t T = 32 * W;
+  constexpr int NW = 2 * G, NK = 4 * G;
   const uint32_t lane = t & 31, warp = t >> 5;
-  const uint32_t i0 = t * 4;  // first key of this thread (keys are zero-padded to a multiple of 8 past n)
-  uint32_t wd[2] = {0, 0};
-  if (i0 < ((n + 7) & ~7u)) {
-    const uint2 v = reinterpret_cast<const uint2*>(keys)[t];
-    wd[0] = v.x, wd[1] = v.y;
-  }
-  int32_t pay[4];
+  const uint32_t i0 = t * NK;  // first key of this thread
+  uint32_t wd[NW];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) pay[j] = i0 + j < n ? (in_idx ? __ldg(in_idx + i0 + j) : (int32_t)(i0 + j)) : 0;
+  for (int x = 0; x < NW; ++x) wd[x] = 0;
+  if (G == 1) {  // keys are zero-padded to a multiple of 8 past n
+    if (i0 < ((n + 7) & ~7u)) {
+      const uint2 v = reinterpret_cast<const uint2*>(keys)[t];
+      wd[0] = v.x, wd[1] = v.y;
+    }
+  } else {  // keys are zero-padded to the whole array
+#pragma unroll
+    for (int x = 0; x < G / 2; ++x) {
+      const uint4 v = reinterpret_cast<const uint4*>(keys)[t * (G / 2) + x];
+      wd[4 * x] = v.x, wd[4 * x + 1] = v.y, wd[4 * x + 2] = v.z, wd[4 * x + 3] = v.w;
+    }
+  }
+  // payload ids fetched now so the compaction does not wait on them (G = 4: fetched at the end, registers)
+  constexpr bool kPre = G <= 2;
+  int32_t pay[kPre ? NK : 1];
+  if (kPre) {
+#pragma unroll
+    for (int j = 0; j < NK; ++j) pay[j] = i0 + j < n ? (in_idx ? __ldg(in_idx + i0 + j) : (int32_t)(i0 + j)) : 0;
+  }
 
   uint32_t prefix = 0, kk = k;
 #pragma unroll
@@ -87,35 +105,38 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
     constexpr uint32_t kOnes = 0x00010001u;
     const uint32_t shift = 12 - 4 * pass;
     const uint32_t hi_mask = (0xffffu >> (shift + 4)) * kOnes, pp = prefix * kOnes;
-    uint32_t c[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int x = 0; x < 2; ++x) {
-      const uint32_t y = ((wd[x] >> (shift + 4)) & hi_mask) ^ pp;      // 0 in a half <=> that key matches the prefix
-      const uint32_t d8lo = ((wd[x] << 3) >> shift) & 0x78u;           // 8 * digit of the low key
-      const uint32_t d8hi = ((wd[x] >> 13) >> shift) & 0x78u;          // 8 * digit of the high key
-      const uint32_t slo = (y & 0xffffu) == 0 ? d8lo : 255u, shi = (y >> 16) == 0 ? d8hi : 255u;
-      const uint64_t a0 = shl64_clamped(slo), a1 = shl64_clamped(slo - 64u);
-      const uint64_t b0 = shl64_clamped(shi), b1 = shl64_clamped(shi - 64u);
-      c[0] += (uint32_t)a0 + (uint32_t)b0;
-      c[1] += (uint32_t)(a0 >> 32) + (uint32_t)(b0 >> 32);
-      c[2] += (uint32_t)a1 + (uint32_t)b1;
-      c[3] += (uint32_t)(a1 >> 32) + (uint32_t)(b1 >> 32);
-    }
-    // zero-padded / out-of-range keys: key 0 never matches a non-zero prefix and sits in the lowest bin otherwise,
-    // below every real key, so it cannot change which bin holds the k-th largest.
-    uint32_t tot[4];
+    for (int g = 0; g < G; ++g) {
+      uint32_t c[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int x = 0; x < 4; ++x) tot[x] = __reduce_add_sync(0xffffffffu, c[x]);  // warp-uniform
-    if (lane < 16) {
-      const uint32_t wsel = (lane >> 2) == 0 ? tot[0] : (lane >> 2) == 1 ? tot[1] : (lane >> 2) == 2 ? tot[2] : tot[3];
-      sc->histT[pass & 1][lane][warp] = (uint8_t)(wsel >> ((lane & 3) * 8));
+      for (int x = 2 * g; x < 2 * g + 2; ++x) {
+        const uint32_t y = ((wd[x] >> (shift + 4)) & hi_mask) ^ pp;      // 0 in a half <=> that key matches the prefix
+        const uint32_t d8lo = ((wd[x] << 3) >> shift) & 0x78u;           // 8 * digit of the low key
+        const uint32_t d8hi = ((wd[x] >> 13) >> shift) & 0x78u;          // 8 * digit of the high key
+        const uint32_t slo = (y & 0xffffu) == 0 ? d8lo : 255u, shi = (y >> 16) == 0 ? d8hi : 255u;
+        const uint64_t a0 = shl64_clamped(slo), a1 = shl64_clamped(slo - 64u);
+        const uint64_t b0 = shl64_clamped(shi), b1 = shl64_clamped(shi - 64u);
+        c[0] += (uint32_t)a0 + (uint32_t)b0;
+        c[1] += (uint32_t)(a0 >> 32) + (uint32_t)(b0 >> 32);
+        c[2] += (uint32_t)a1 + (uint32_t)b1;
+        c[3] += (uint32_t)(a1 >> 32) + (uint32_t)(b1 >> 32);
+      }
+      // zero-padded / out-of-range keys: key 0 never matches a non-zero prefix and sits in the lowest bin otherwise,
+      // below every real key, so it cannot change which bin holds the k-th largest.
+      uint32_t tot[4];
+#pragma unroll
+      for (int x = 0; x < 4; ++x) tot[x] = __reduce_add_sync(0xffffffffu, c[x]);  // warp-uniform
+      if (lane < 16) {
+        const uint32_t wsel = (lane >> 2) == 0 ? tot[0] : (lane >> 2) == 1 ? tot[1] : (lane >> 2) == 2 ? tot[2] : tot[3];
+        sc->histT[pass & 1][lane][warp * G + g] = (uint8_t)(wsel >> ((lane & 3) * 8));
+      }
     }
     group_bar(bar_id, T);
     uint32_t s = 0;
     if (lane < 16) {
       const uint32_t* row = reinterpret_cast<const uint32_t*>(sc->histT[pass & 1][lane]);
 #pragma unroll
-      for (int x = 0; x < W / 4; ++x) s = __dp4a(row[x], 0x01010101u, s);
+      for (int x = 0; x < W * G / 4; ++x) s = __dp4a(row[x], 0x01010101u, s);
     }
     uint32_t suf = s;  // suffix sums over the 16 bin lanes (lanes 16..31 carry zeros)
 #pragma unroll
@@ -132,11 +153,12 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
   }
   const uint32_t tau = prefix, need = kk;
 
-  uint32_t key[4];
-  key[0] = wd[0] & 0xffffu, key[1] = wd[0] >> 16, key[2] = wd[1] & 0xffffu, key[3] = wd[1] >> 16;
+  uint32_t key[NK];
+#pragma unroll
+  for (int x = 0; x < NW; ++x) key[2 * x] = wd[x] & 0xffffu, key[2 * x + 1] = wd[x] >> 16;
   uint32_t ngt = 0, neq = 0;
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
+  for (int j = 0; j < NK; ++j) {
     const bool in = i0 + j < n;
     ngt += in && key[j] > tau;
     neq += in && key[j] == tau;
@@ -157,17 +179,17 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
   {
     uint32_t e = eq_before, cut = 0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < NK; ++j)
       if (i0 + j < n && key[j] == tau && ++e == need) cut = i0 + j + 1;
     hook(cut != 0, (1ull << 63) | ((unsigned long long)cut << 16) | tau);
   }
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
+  for (int j = 0; j < NK; ++j) {
     const bool in = i0 + j < n;
     const bool gt = in && key[j] > tau, eq = in && key[j] == tau;
     if (gt || (eq && eq_before < need)) {
       const uint32_t pos = gt_before + min(eq_before, need);
-      out_idx[pos] = pay[j];
+      out_idx[pos] = kPre ? pay[kPre ? j : 0] : in_idx ? __ldg(in_idx + i0 + j) : (int32_t)(i0 + j);
       if (out_val) out_val[pos] = half_of((uint16_t)key[j]);
     }
     gt_before += gt;

@@ -156,7 +156,7 @@ def run_topk(scores, payload, k):
 
 
 @pytest.mark.parametrize("n,k", [(13, 2), (24, 24), (77, 19), (311, 69), (1024, 1024), (1025, 7), (1110, 251), (2047, 127), (2047, 1), (2048, 2048), (3001, 640), (4096, 1), (4097, 333),
-                                 (8191, 255), (8192, 4095), (65535, 511)])
+                                 (8191, 255), (8192, 4095), (8193, 511), (12000, 300), (16384, 1023), (16385, 64), (65535, 511)])
 @pytest.mark.parametrize("dist", ["normal", "ties", "const"])
 def test_topk_exact(n, k, dist):
     H = 32 if n < 10000 else 4
