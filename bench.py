@@ -311,8 +311,8 @@ def main():
         t = timed(gk.replay, args.steps, 3, dist_on) / (args.steps * n)
         kern[name] = {"us": t * 1e6, "GBps": nbytes / t / 1e9}
     peak, peak_kind = peaks()
-    # DRAM read+write bytes per launch from the ncu --set full capture of this command (profiles/r01_b_layer_step.md)
-    ncu_traffic = {"estimate": 33603840, "decode": 33630976}
+    # DRAM read+write bytes per launch from the ncu --set full capture of this command (profiles/r01_c_layer_step.md)
+    ncu_traffic = {"estimate": 33598976, "decode": 33626112}
     dom = max(("estimate", "decode"), key=lambda k_: kern[k_]["us"])
     dom_bytes = {"estimate": BYTES_ESTIMATE, "decode": BYTES_DECODE}[dom]
     dom_name = {"estimate": "estimate_tile_kernel", "decode": "decode_kernel"}[dom]
@@ -340,7 +340,7 @@ def main():
         "kernels": kern,
         "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": kern[dom]["GBps"], "peak": peak, "peak_kind": peak_kind,
                      "unit": "GB/s", "frac": kern[dom]["GBps"] / peak, "traffic": ncu_traffic[dom],
-                     "traffic_source": "profiles/r01_b_layer_step.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)",
+                     "traffic_source": "profiles/r01_c_layer_step.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)",
                      "algorithmic_bytes_per_launch": dom_bytes},
         "e2e": {"value": world * BYTES_STEP * L / sec_e2e / 1e9, "unit": UNIT, "ms_per_step": sec_e2e * 1e3,
                 "h2d_bytes_per_step": wl.h_qkv.numel() * 2, "d2h_bytes_per_step": wl.h_out.numel() * 2,

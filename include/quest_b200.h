@@ -183,6 +183,23 @@ int quest_prefill(const void* q, void* o, uint32_t qo_len,
 int quest_merge_states(const float* o_parts, const float* lse_parts, uint32_t n, uint32_t part_stride,
                        void* o, float* lse, uint32_t num_heads, uint32_t head_dim, void* stream);
 
+/* ---- all-gather of a small message over NVLink peer memory (sequence-sharded path) ---------
+ * The reference has no multi-GPU path; this replaces the NCCL all-gather that BASELINE.json's north_star names for
+ * the two per-layer exchanges (top-k candidates, (o, lse) records) with one kernel per exchange.  Every rank calls
+ * it with the same shapes: src (rows x row_bytes, dense, row_bytes % 16 == 0) is stored into slot `rank` of every
+ * peer's staging area, published with a system-scope release of this call's epoch into the peer's flag word, and
+ * once all `world` epochs have arrived in this rank's own flag words the staging area is unpacked into
+ * dst = [rows][world][row_bytes].  peer_staging[p] / peer_flags[p]: rank p's staging area
+ * (quest_peer_staging_bytes) and flag words (world x uint32, zero at start) as mapped into THIS process (host
+ * arrays of `world` device pointers; peer-mapped symmetric memory, or plain device memory when world == 1).
+ * state: 2 x uint32 of local device memory, zero at start: [0] epoch (advanced by the kernel, so the call can be
+ * captured in a CUDA graph), [1] number of waits that ran into timeout_ms (0 = 2000) -- nonzero means dst is not valid.
+ * world <= 8. */
+size_t quest_peer_staging_bytes(uint32_t rows, uint32_t row_bytes, uint32_t world);
+int quest_peer_allgather(const void* src, uint32_t rows, uint32_t row_bytes, void* const* peer_staging,
+                         void* const* peer_flags, void* state, void* dst, uint32_t world, uint32_t rank,
+                         uint32_t timeout_ms, void* stream);
+
 /* Counters for bench/tests: number of kernels this library has launched since load / last reset. */
 uint64_t quest_launch_count(void);
 void quest_launch_count_reset(void);

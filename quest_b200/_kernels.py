@@ -36,6 +36,8 @@ SIGNATURES = {
                                            _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _c.c_int, _u32, _u32, _u32, _u32, _vp]),
     "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _u32, _vp, _vp, _u32, _u32, _vp]),
+    "quest_peer_staging_bytes": (_sz, [_u32, _u32, _u32]),
+    "quest_peer_allgather": (_c.c_int, [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _vp]),
     "quest_launch_count": (_c.c_uint64, []),
     "quest_launch_count_reset": (None, []),
 }

@@ -4,7 +4,7 @@ set -euo pipefail
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="${QUEST_EXTRA_FLAGS:-} -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo --expt-relaxed-constexpr -Xcompiler -fPIC -Xptxas -v"
-SRCS="capi.cu fused.cu estimate.cu page.cu topk.cu decode.cu rope_norm.cu prefill.cu prefill_tma.cu"
+SRCS="capi.cu fused.cu estimate.cu page.cu topk.cu decode.cu rope_norm.cu prefill.cu prefill_tma.cu peer.cu"
 # QUEST_LIB_SUFFIX=_dbg (with QUEST_EXTRA_FLAGS) builds an instrumented copy next to the product library
 SUF="${QUEST_LIB_SUFFIX:-}"
 B="build$SUF"

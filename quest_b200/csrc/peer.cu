@@ -1,0 +1,119 @@
+// All-gather of a small message over NVLink peer memory in ONE kernel: push + signal + wait + unpack.
+// The two exchanges of the sequence-sharded decode step (top-k candidates, (o, lse) partials) are
+// 16-32 KB per rank -- pure latency for a collective library (two NCCL all-gathers cost ~20 us per layer at 2 GPUs,
+// profiles/r01_s15_long_context_multi_gpu.md).  Here every rank's kernel
+//   1. stores its message straight into every peer's staging buffer (symmetric memory mapped over NVLink / NVSwitch:
+//      16-byte stores, one CTA -- the message is far below the bandwidth-delay product of a link),
+//   2. publishes it: __threadfence_system by every writer, CTA barrier, then one st.release.sys per peer of this
+//      step's epoch into the peer's flag word for this rank,
+//   3. waits (ld.acquire.sys on its OWN flag words, so the polling never crosses the link) until every rank's epoch
+//      arrived, bounded by a wall-clock limit so that a lost peer is an error code, not a hung GPU,
+//   4. unpacks the staging area into a private, fixed-address buffer in the layout the consumer wants
+//      ([rows][world][row_bytes]: the gathered candidate scores come out as [head][rank][c], ready for quest_topk).
+// The epoch lives in device memory and is advanced by the kernel itself, so the call can sit in a CUDA graph; staging
+// is double-buffered on the epoch's parity: a rank can only finish exchange e+1 after every peer has entered it, i.e.
+// after every peer has left exchange e, so pushes of e+2 never meet readers of e.
+#include "common.cuh"
+
+namespace quest {
+
+constexpr int kPeerMax = 8;
+constexpr int kPeerThreads = 1024;
+
+struct PeerTable {
+  uint4* staging[kPeerMax];     // rank p's staging area as mapped into this process: [2][world][msg_vecs]
+  uint32_t* flags[kPeerMax];    // rank p's flag words: [world]
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__global__ void __launch_bounds__(kPeerThreads)
+peer_allgather_kernel(const uint4* __restrict__ src, uint32_t rows, uint32_t row_vecs, const PeerTable tbl,
+                      uint32_t* __restrict__ state /* [0] epoch, [1] timeouts */, uint4* __restrict__ dst,
+                      uint32_t world, uint32_t rank, unsigned long long timeout_ns) {
+  __shared__ uint32_t s_epoch;
+  const uint32_t tid = threadIdx.x;
+  pdl_wait();  // the message comes from the kernel before this one
+  if (tid == 0) {
+    s_epoch = state[0] + 1;
+    state[0] = s_epoch;
+  }
+  __syncthreads();
+  const uint32_t epoch = s_epoch, par = epoch & 1u;
+  const uint32_t msg_vecs = rows * row_vecs;
+  const size_t slot = ((size_t)par * world + rank) * msg_vecs;  // my slot in anybody's staging area
+  for (uint32_t j = tid; j < msg_vecs; j += kPeerThreads) {
+    const uint4 v = src[j];
+    for (uint32_t p = 0; p < world; ++p) tbl.staging[p][slot + j] = v;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid < world) {
+    st_release_sys(tbl.flags[tid] + rank, epoch);
+    // wait for rank `tid`'s message of this epoch (flag words are monotonic; compare modulo 2^32)
+    const uint32_t* f = tbl.flags[rank] + tid;
+    const unsigned long long t0 = global_ns();
+    uint32_t spins = 0;
+    while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+      if ((++spins & 1023u) == 0 && global_ns() - t0 > timeout_ns) {
+        atomicAdd(state + 1, 1u);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  // unpack: dst[row][r][vec] = staging[par][r][row][vec]
+  const uint4* mine = tbl.staging[rank] + (size_t)par * world * msg_vecs;
+  const uint32_t total = world * msg_vecs;
+  for (uint32_t i = tid; i < total; i += kPeerThreads) {
+    const uint32_t r = i / msg_vecs, j = i - r * msg_vecs;
+    const uint32_t row = j / row_vecs, vec = j - row * row_vecs;
+    dst[((size_t)row * world + r) * row_vecs + vec] = mine[i];
+  }
+}
+
+}  // namespace quest
+
+extern "C" int quest_peer_allgather(const void* src, uint32_t rows, uint32_t row_bytes, void* const* peer_staging,
+                                    void* const* peer_flags, void* state, void* dst, uint32_t world, uint32_t rank,
+                                    uint32_t timeout_ms, void* stream) {
+  if (!src || !peer_staging || !peer_flags || !state || !dst || !rows || !row_bytes) return QUEST_ERR_BAD_ARG;
+  if (world < 1 || world > quest::kPeerMax || rank >= world) return QUEST_ERR_UNSUPPORTED;
+  if (row_bytes % 16 || ((uintptr_t)src & 15) || ((uintptr_t)dst & 15)) return QUEST_ERR_BAD_ARG;
+  quest::PeerTable tbl = {};
+  for (uint32_t p = 0; p < world; ++p) {
+    if (!peer_staging[p] || !peer_flags[p] || ((uintptr_t)peer_staging[p] & 15)) return QUEST_ERR_BAD_ARG;
+    tbl.staging[p] = (uint4*)peer_staging[p];
+    tbl.flags[p] = (uint32_t*)peer_flags[p];
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1);
+  cfg.blockDim = dim3(quest::kPeerThreads);
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const unsigned long long timeout_ns = (unsigned long long)(timeout_ms ? timeout_ms : 2000u) * 1000000ull;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, quest::peer_allgather_kernel, (const uint4*)src, rows, row_bytes / 16, tbl,
+                                     (uint32_t*)state, (uint4*)dst, world, rank, timeout_ns);
+  if (e != cudaSuccess) return (int)e;
+  QUEST_RETURN_LAUNCH();
+}
+
+extern "C" size_t quest_peer_staging_bytes(uint32_t rows, uint32_t row_bytes, uint32_t world) {
+  return (size_t)2 * world * rows * row_bytes;
+}

@@ -123,7 +123,12 @@ class SeqShardedDecode:
     """
 
     def __init__(self, ic, num_qo_heads: int, world: int, rank: int, page_budget: int,
-                 group: Optional[dist.ProcessGroup] = None):
+                 group: Optional[dist.ProcessGroup] = None, exchange: str = "nccl",
+                 peer_buffers: Optional[Sequence[torch.Tensor]] = None):
+        """exchange: "nccl" (all_gather_into_tensor) or "peer" (quest_peer_allgather: one kernel per exchange that
+        stores into every rank's symmetric-memory staging area over NVLink and waits on flag words).
+        peer_buffers: for a single process that plays all ranks on one device (tests): the ranks' exchange areas as
+        uint8 tensors of peer_area_bytes() each, in rank order; by default the areas are torch symmetric memory."""
         from quest_b200 import _kernels
         self._K = _kernels
         self.lib = _kernels.load_library()
@@ -145,6 +150,60 @@ class SeqShardedDecode:
         self.rec = torch.zeros(self.Hq * self.D + self.Hq, dtype=torch.float32, device=self.dev)
         self.rec_all = torch.empty(self.R, self.Hq * self.D + self.Hq, dtype=torch.float32, device=self.dev)
         self.out = torch.empty(1, self.Hq, self.D, dtype=torch.float16, device=self.dev)
+        if exchange not in ("nccl", "peer"):
+            raise ValueError("exchange must be 'nccl' or 'peer'")
+        self.exchange = exchange
+        if exchange == "peer":
+            self._setup_peer(peer_buffers)
+
+    # -- exchange areas for the peer-memory all-gather: [candidate staging][record staging][flags cand][flags rec]
+    @staticmethod
+    def _peer_layout(lib, Hq, D, k, R):
+        c_cap = (max(k, 1) + 7) // 8 * 8
+        a = lib.quest_peer_staging_bytes(Hq, c_cap * 2, R)
+        b = lib.quest_peer_staging_bytes(1, (Hq * D + Hq) * 4, R)
+        off_flags = (a + b + 15) // 16 * 16
+        return a, off_flags, off_flags + (2 * R * 4 + 15) // 16 * 16
+
+    def peer_area_bytes(self) -> int:
+        return self._peer_layout(self.lib, self.Hq, self.D, self.k, self.R)[2]
+
+    def _setup_peer(self, peer_buffers):
+        if (self.Hq * self.D + self.Hq) * 4 % 16:
+            raise ValueError("peer exchange needs num_qo_heads % 4 == 0")
+        off_rec, off_flags, total = self._peer_layout(self.lib, self.Hq, self.D, self.k, self.R)
+        if peer_buffers is not None:
+            if len(peer_buffers) != self.R or any(b.numel() < total or b.dtype != torch.uint8 for b in peer_buffers):
+                raise ValueError("peer_buffers: one uint8 tensor of peer_area_bytes() per rank")
+            self._peer_keep = list(peer_buffers)
+            bases = [b.data_ptr() for b in peer_buffers]
+        else:
+            import torch.distributed._symmetric_memory as symm
+            area = symm.empty(total, dtype=torch.uint8, device=self.dev)
+            area.zero_()
+            hdl = symm.rendezvous(area, self.group if self.group is not None else dist.group.WORLD)
+            hdl.barrier()  # every rank's flags are zero before anybody's first push
+            self._peer_keep = [area, hdl]
+            bases = [int(p) for p in hdl.buffer_ptrs]
+        arr = ctypes.c_void_p * self.R
+        self._peer_ptrs = {
+            "cand": (arr(*bases), arr(*[b + off_flags for b in bases])),
+            "rec": (arr(*[b + off_rec for b in bases]), arr(*[b + off_flags + self.R * 4 for b in bases])),
+        }
+        self.peer_state = torch.zeros(2, 2, dtype=torch.int32, device=self.dev)  # [cand | rec][epoch, timeouts]
+
+    def _peer_gather(self, kind: str, src: torch.Tensor, rows: int, row_bytes: int, dst: torch.Tensor):
+        staging, flags = self._peer_ptrs[kind]
+        state = self.peer_state[0 if kind == "cand" else 1]
+        self._K._rc(self.lib.quest_peer_allgather(src.data_ptr(), rows, row_bytes, staging, flags, state.data_ptr(),
+                                                  dst.data_ptr(), self.R, self.r, 0, self._st()), "peer all-gather")
+
+    def check_peer(self):
+        """Synchronise and raise if any peer wait ran into its time limit (a rank missing from the exchange)."""
+        if self.exchange == "peer":
+            n = int(self.peer_state[:, 1].sum().item())
+            if n:
+                raise RuntimeError(f"quest_peer_allgather: {n} waits timed out (a rank did not take part)")
 
     # -- per-layout buffers (the layout changes only when a rank gains a page)
     def begin_step(self, scored_pages_per_rank: Sequence[int]):
@@ -166,7 +225,9 @@ class SeqShardedDecode:
         self._key = key
         self.n_local = n[self.r]
         self.c_max = min(self.k, max(n))
-        self.c_loc = min(self.k, self.n_local)
+        if self.exchange == "peer":  # 16-byte rows on the wire: a few extra candidates (or -inf padding) per rank
+            self.c_max = (self.c_max + 7) // 8 * 8
+        self.c_loc = min(self.c_max, self.n_local)
         Hq, R, c = self.Hq, self.R, self.c_max
         f16 = dict(dtype=torch.float16, device=self.dev)
         self.scores = torch.empty(Hq, max(self.n_local, 1), **f16)
@@ -200,12 +261,13 @@ class SeqShardedDecode:
                 self.cand_s[:, :self.c_loc].copy_(self.cand_tmp)
         return self.cand_s
 
-    def select(self, gathered: torch.Tensor) -> torch.Tensor:
+    def select(self, gathered: Optional[torch.Tensor]) -> torch.Tensor:
         """Phase 3.  gathered: fp16 [R, Hq, c], the ranks' messages in rank order.  Returns int32 [Hq, k]: this rank's
         physical page ids of the globally selected pages, -1 where another rank holds the page."""
         if self.k == 0:
             return self.sel[:, :0]
-        self.all_s.copy_(gathered.permute(1, 0, 2))
+        if gathered is not None:  # None: all_s already holds [Hq, R, c] (peer exchange unpacks straight into it)
+            self.all_s.copy_(gathered.permute(1, 0, 2))
         if self.c_loc:
             self.pay[:, self.r, :self.c_loc].copy_(self.cand_p)
         n = self.R * self.c_max
@@ -237,6 +299,13 @@ class SeqShardedDecode:
         """All five phases with the process group's collectives (NCCL).  Every rank passes the same q; k_new / v_new
         matter on the last rank only.  Returns fp16 [1, Hq, D], identical on every rank."""
         msg = self.candidates(q, k_new, v_new, layer)
+        if self.exchange == "peer":
+            if self.k:
+                self._peer_gather("cand", msg, self.Hq, self.c_max * 2, self.all_s)
+            self.select(None)
+            rec = self.attend(q, layer)
+            self._peer_gather("rec", rec, 1, rec.numel() * 4, self.rec_all)
+            return self.merge(self.rec_all)
         dist.all_gather_into_tensor(self.gath, msg, group=self.group)
         self.select(self.gath)
         rec = self.attend(q, layer)

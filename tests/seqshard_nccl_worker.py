@@ -21,13 +21,14 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     try:
-        for kv_len, Hq, Hkv, D, P, budget in ((6000, 32, 32, 128, 16, 48), (9000, 32, 8, 128, 16, 64)):
+        modes = os.environ.get("QUEST_SEQSHARD_EXCHANGES", "nccl,peer").split(",")
+        for exchange, kv_len, Hq, Hkv, D, P, budget in [(m, *c) for m in modes for c in ((6000, 32, 32, 128, 16, 48), (9000, 32, 8, 128, 16, 64))]:
             steps = 3
             k, v, dec = sc.seeded_case(kv_len, kv_len, Hq, Hkv, D, steps)
             full = sc.filled_controller(k, v, Hq, Hkv, D, P, budget, kv_len + steps + P, dev)
             ranges = sc.shard_token_ranges(kv_len, P, world)
             ic = sc.shard_controller(k, v, ranges[rank], rank, world, Hq, Hkv, D, P, budget, steps, dev)
-            shard = par.SeqShardedDecode(ic, Hq, world, rank, budget)
+            shard = par.SeqShardedDecode(ic, Hq, world, rank, budget, exchange=exchange)
             n_scored = [b - a for a, b in ranges]
             for q, k1, v1 in dec:
                 q, k1, v1 = q.to(dev), k1.to(dev), v1.to(dev)
@@ -44,6 +45,7 @@ def main():
                 shard.begin_step(n_scored)
                 got = shard.layer_step(q, k1, v1, 0)
                 torch.cuda.synchronize()
+                shard.check_peer()
                 err = (got.float() - want.float()).abs().max().item()
                 assert err <= 2e-3, (rank, err)
                 # the selection: my share + the others' = the single-GPU set
@@ -60,7 +62,7 @@ def main():
                 assert got_sel == want_sel, rank
         dist.barrier()
         if rank == 0:
-            print("seqshard nccl ok")
+            print("seqshard nccl ok (" + ",".join(modes) + ")")
     finally:
         dist.destroy_process_group()
 

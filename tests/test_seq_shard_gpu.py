@@ -22,7 +22,7 @@ DEV = "cuda:0"
 ATTN_ATOL = 2e-3  # north_star: fp16 attention output max abs error
 
 
-def _run_case(seed, kv_len, Hq, Hkv, D, P, budget, world, steps=3, ties=False):
+def _run_case(seed, kv_len, Hq, Hkv, D, P, budget, world, steps=3, ties=False, exchange="emulated"):
     dev = torch.device(DEV)
     k, v, dec = sc.seeded_case(seed, kv_len, Hq, Hkv, D, steps)
     if ties:  # repeat a block of keys: equal metadata -> equal scores across shards, the tie rule decides
@@ -32,7 +32,16 @@ def _run_case(seed, kv_len, Hq, Hkv, D, P, budget, world, steps=3, ties=False):
     full = sc.filled_controller(k, v, Hq, Hkv, D, P, budget, kv_len + steps + P, dev)
     ranges = sc.shard_token_ranges(kv_len, P, world)
     ics = [sc.shard_controller(k, v, ranges[r], r, world, Hq, Hkv, D, P, budget, steps, dev) for r in range(world)]
-    shards = [par.SeqShardedDecode(ics[r], Hq, world, r, budget) for r in range(world)]
+    if exchange == "peer":
+        # all ranks in this process: their exchange areas are plain device buffers, every rank's kernels run on its own
+        # stream so that the ranks' waits can be met by one another (the kernels are single-CTA and co-resident)
+        probe = par.SeqShardedDecode(ics[0], Hq, 1, 0, budget)
+        nbytes = par.SeqShardedDecode._peer_layout(probe.lib, Hq, D, budget - 1, world)[2]
+        areas = [torch.zeros(nbytes, dtype=torch.uint8, device=dev) for _ in range(world)]
+        shards = [par.SeqShardedDecode(ics[r], Hq, world, r, budget, exchange="peer", peer_buffers=areas) for r in range(world)]
+        streams = [torch.cuda.Stream() for _ in range(world)]
+    else:
+        shards = [par.SeqShardedDecode(ics[r], Hq, world, r, budget) for r in range(world)]
     for q, k1, v1 in dec:
         q, k1, v1 = q.to(dev), k1.to(dev), v1.to(dev)
         # single-GPU truth
@@ -49,11 +58,23 @@ def _run_case(seed, kv_len, Hq, Hkv, D, P, budget, world, steps=3, ties=False):
         n_scored = [len(ic.kv_cache.indicies) - (1 if r == world - 1 else 0) for r, ic in enumerate(ics)]
         for s in shards:
             s.begin_step(n_scored)
-        gath = torch.stack([s.candidates(q, k1, v1, 0) for s in shards])
-        sels = [s.select(gath).clone() for s in shards]
-        recs = torch.stack([s.attend(q, 0) for s in shards])
-        outs = [s.merge(recs).clone() for s in shards]
-        torch.cuda.synchronize()
+        if exchange == "peer":
+            torch.cuda.synchronize()
+            outs = [None] * world
+            for r, s in enumerate(shards):  # enqueue every rank's whole step before waiting for any of them
+                with torch.cuda.stream(streams[r]):
+                    outs[r] = s.layer_step(q, k1, v1, 0)
+            torch.cuda.synchronize()
+            for s in shards:
+                s.check_peer()
+            outs = [o.clone() for o in outs]
+            sels = [s.sel[:, :s.k].clone() for s in shards]
+        else:
+            gath = torch.stack([s.candidates(q, k1, v1, 0) for s in shards])
+            sels = [s.select(gath).clone() for s in shards]
+            recs = torch.stack([s.attend(q, 0) for s in shards])
+            outs = [s.merge(recs).clone() for s in shards]
+            torch.cuda.synchronize()
         first = np.concatenate([[0], np.cumsum(n_scored)[:-1]])
         got_sel = [[] for _ in range(Hq)]
         for r in range(world):
@@ -94,6 +115,64 @@ def _run_case(seed, kv_len, Hq, Hkv, D, P, budget, world, steps=3, ties=False):
 ])
 def test_sharded_step_equals_single_gpu(kv_len, Hq, Hkv, D, P, budget, world):
     _run_case(kv_len + world, kv_len, Hq, Hkv, D, P, budget, world)
+
+
+@pytest.mark.parametrize("kv_len,Hq,Hkv,D,P,budget,world", [
+    (3000, 32, 32, 128, 16, 24, 2),
+    (5000, 32, 8, 128, 16, 40, 4),
+    (700, 32, 32, 128, 16, 30, 4),      # ragged candidate counts: -inf padding travels
+    (32768, 32, 32, 128, 16, 128, 8),
+    (2100, 32, 32, 128, 16, 24, 1),     # world 1: the exchange degenerates to a local copy
+])
+def test_sharded_step_peer_memory_exchange(kv_len, Hq, Hkv, D, P, budget, world):
+    """The same step with both exchanges done by quest_peer_allgather (push into every rank's staging area, flags,
+    wait, unpack) instead of being stood in for: all ranks' kernels run concurrently on one GPU."""
+    _run_case(kv_len + world, kv_len, Hq, Hkv, D, P, budget, world, steps=4, exchange="peer")
+
+
+def test_peer_allgather_kernel_layout_and_epochs():
+    """quest_peer_allgather alone: dst = [rows][world][row_bytes], repeated calls (epoch parity), a missing rank (timeout instead of a hang), argument checks."""
+    import ctypes
+    import quest_b200._kernels as K
+    lib = K.load_library()
+    R, rows, row_bytes = 3, 5, 48
+    nst = lib.quest_peer_staging_bytes(rows, row_bytes, R)
+    stg = [torch.zeros(nst, dtype=torch.uint8, device=DEV) for _ in range(R)]
+    flg = [torch.zeros(R, dtype=torch.int32, device=DEV) for _ in range(R)]
+    state = [torch.zeros(2, dtype=torch.int32, device=DEV) for _ in range(R)]
+    src = [torch.zeros(rows, row_bytes, dtype=torch.uint8, device=DEV) for _ in range(R)]
+    dst = [torch.zeros(rows, R, row_bytes, dtype=torch.uint8, device=DEV) for _ in range(R)]
+    arr = ctypes.c_void_p * R
+    ps, pf = arr(*[x.data_ptr() for x in stg]), arr(*[x.data_ptr() for x in flg])
+    streams = [torch.cuda.Stream() for _ in range(R)]
+
+    def round_():
+        for r in range(R):
+            with torch.cuda.stream(streams[r]):
+                assert lib.quest_peer_allgather(src[r].data_ptr(), rows, row_bytes, ps, pf, state[r].data_ptr(), dst[r].data_ptr(),
+                                                R, r, 500, torch.cuda.current_stream().cuda_stream) == 0
+
+    g = torch.Generator().manual_seed(0)
+    for it in range(5):
+        msgs = [torch.randint(0, 256, (rows, row_bytes), generator=g, dtype=torch.uint8) for _ in range(R)]
+        for r in range(R):
+            src[r].copy_(msgs[r].to(DEV))
+        torch.cuda.synchronize()
+        round_()
+        torch.cuda.synchronize()
+        want = torch.stack(msgs, dim=1)  # [rows, R, row_bytes]
+        for r in range(R):
+            assert torch.equal(dst[r].cpu(), want), (it, r)
+            assert state[r].tolist() == [it + 1, 0]
+    # a rank missing from the exchange: the others time out and say so instead of hanging
+    with torch.cuda.stream(streams[0]):
+        assert lib.quest_peer_allgather(src[0].data_ptr(), rows, row_bytes, ps, pf, state[0].data_ptr(), dst[0].data_ptr(),
+                                        R, 0, 50, torch.cuda.current_stream().cuda_stream) == 0
+    torch.cuda.synchronize()
+    assert state[0].tolist()[1] == 2
+    # argument checks
+    assert lib.quest_peer_allgather(src[0].data_ptr(), rows, 40, ps, pf, state[0].data_ptr(), dst[0].data_ptr(), R, 0, 50, 0) == -1
+    assert lib.quest_peer_allgather(src[0].data_ptr(), rows, row_bytes, ps, pf, state[0].data_ptr(), dst[0].data_ptr(), 9, 0, 50, 0) == -2
 
 
 def test_sharded_step_ties_across_shards():

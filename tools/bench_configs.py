@@ -152,7 +152,7 @@ def config5(args, rank, world, dev):
     fill(ic, L, tokens, H, dev)
     if rank == world - 1:
         ic.prepare_metadata(1)
-    shard = par.SeqShardedDecode(ic, H, world, rank, budget)
+    shard = par.SeqShardedDecode(ic, H, world, rank, budget, exchange=args.exchange)
     n_scored = [pages_per_rank] * (world - 1) + [pages_per_rank - 1]
     shard.begin_step(n_scored)
     torch.manual_seed(77)  # the same q on every rank
@@ -177,12 +177,14 @@ def config5(args, rank, world, dev):
     by_meta = n_scored[rank] * H * D * 2 * 2
     by_kv_total = H * budget * P * 2 * D * 2            # the selected pages, wherever they live
     per_layer_rank = by_meta + by_kv_total // world     # uniform split of the selection (data dependent in reality)
-    extra = {"compute_only": compute_only,
+    extra = {"compute_only": compute_only, "shard": shard,
              "exchange_bytes_per_rank": {"candidates": H * min(k, pages_per_rank) * 2, "partials": (H * D + H) * 4}}
     return step, L, per_layer_rank, {
         "workload": f"Yarn-Llama2-7B-128K shape (32 heads x 128, fp16), {world * pages_per_rank * P} ctx "
                     f"({pages_per_rank} pages per GPU), page 16, budget 8192, batch 1, one sequence over all ranks",
-        "parallelism": f"sequence (page) sharded x{world}, 2 NCCL all-gathers per layer step", "scaling": "weak"}, extra
+        "parallelism": f"sequence (page) sharded x{world}, 2 all-gathers per layer step ("
+                       + ("NCCL" if args.exchange == "nccl" else "quest_peer_allgather over symmetric memory") + ")",
+        "exchange": args.exchange, "scaling": "weak"}, extra
 
 
 def main():
@@ -190,6 +192,8 @@ def main():
     ap.add_argument("--config", type=int, required=True, choices=[4, 5])
     ap.add_argument("--layers", type=int, default=2)
     ap.add_argument("--streams", type=int, default=8, help="config 4: concurrent sequences per layer (0 = one stream)")
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"], help="config 5: how the two all-gathers are done")
+    ap.add_argument("--graph-collectives", action="store_true", help="config 5, N > 1: also capture the NCCL step in a CUDA graph")
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     args = ap.parse_args()
@@ -211,21 +215,41 @@ def main():
         step, L, by_rank, cfg, extra = config5(args, rank, world, dev)
     step()
     torch.cuda.synchronize()
-    res = {"eager_us_per_layer": timed(step, args.steps, args.warmup, dist_on) / L * 1e6}
-    g = try_graph(step)
+
+    def agreed_graph(fn, allowed=True):
+        """Capture fn on every rank or on none: a rank whose capture failed must not fall out of step with the others."""
+        g = try_graph(fn) if allowed else None
+        ok = torch.tensor([1 if g is not None else 0], device=dev)
+        if dist_on:
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        return g if int(ok.item()) else None
+
+    def note(k, v):
+        res[k] = v
+        if rank == 0:
+            sys.stderr.write(f"[bench_configs] {k} = {v:.2f}\n")
+            sys.stderr.flush()
+
+    res = {}
+    note("eager_us_per_layer", timed(step, args.steps, args.warmup, dist_on) / L * 1e6)
+    # collectives inside a captured graph only on request (NCCL capture is all-or-nothing across the ranks)
+    g = agreed_graph(step, allowed=(args.config == 4 or world == 1 or args.graph_collectives or args.exchange == "peer"))
     if g is not None:
-        res["graph_us_per_layer"] = timed(g, args.steps, args.warmup, dist_on) / L * 1e6
+        note("graph_us_per_layer", timed(g, args.steps, args.warmup, dist_on) / L * 1e6)
     if "compute_only" in extra:
         co = extra.pop("compute_only")
-        res["compute_only_eager_us_per_layer"] = timed(co, args.steps, args.warmup, dist_on) / L * 1e6
-        gc = try_graph(co)
+        note("compute_only_eager_us_per_layer", timed(co, args.steps, args.warmup, dist_on) / L * 1e6)
+        gc = agreed_graph(co)
         if gc is not None:
-            res["compute_only_graph_us_per_layer"] = timed(gc, args.steps, args.warmup, dist_on) / L * 1e6
+            note("compute_only_graph_us_per_layer", timed(gc, args.steps, args.warmup, dist_on) / L * 1e6)
     best = min(v for k, v in res.items() if k in ("eager_us_per_layer", "graph_us_per_layer"))
     by = torch.tensor([float(by_rank)], device=dev)
     if dist_on:
         dist.all_reduce(by)
     total_bytes = float(by.item())
+    if args.config == 5:
+        shard_obj = extra.pop("shard")
+        shard_obj.check_peer()
     if rank == 0:
         gbps = total_bytes / (best * 1e-6) / 1e9
         print(json.dumps({"config": args.config, "n_gpus": world, "us_per_layer": best, "algorithmic_bytes_per_layer_all_ranks":
