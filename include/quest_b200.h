@@ -164,6 +164,41 @@ int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new,
                             uint32_t page_size, uint32_t pages_per_chunk,
                             void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- layer step for a batch of sequences, replayable from a CUDA graph ------------------------------------
+ * Same work as quest_decode_layer_step for `batch` independent sequences in three launches (grid.y / grid.z = sequence),
+ * with everything that changes from token to token read from DEVICE memory: one 64-byte record per sequence.  The host
+ * refreshes the records (one small H2D copy per token, e.g. from a pinned buffer inside the captured graph) and replays
+ * the graph; no argument of the call changes while max_kv_pages holds.  This is the reference's per-token
+ * InferenceController.begin_forward + four operator calls per layer (controller.py:72-129, QuestAttention.py:100-150)
+ * with the per-token index tensors replaced by the records (the reference asserts batch 1,
+ * QuestAttention.py:68).
+ * q, o: [batch, num_qo_heads, head_dim]; k_new, v_new: [batch, num_kv_heads, head_dim]; scores: per sequence
+ * [num_qo_heads, num_kv_pages-1] at scores + b*scores_seq_stride (elements); topk_idx: [batch, num_qo_heads, k];
+ * workspace: batch blocks of workspace_seq_bytes (>= quest_decode_workspace_bytes, multiple of 16, zero at start).
+ * kv_layer_offset / meta_layer_offset: byte offset of this layer inside every sequence's pools.
+ * max_kv_pages: upper bound on num_kv_pages over the batch (sizes grids, the top-k variant, shared memory; <= 16385).
+ * A sequence with fewer than k scored pages attends to all of them (the rest of its topk_idx row is -1). */
+typedef struct QuestSeqDesc {
+  const void* kv_data;          /* the sequence's KV pool, layer 0 */
+  const void* meta_data;        /* its metadata pool, layer 0 */
+  const int32_t* kv_indices;    /* device page tables */
+  const int32_t* meta_indices;
+  uint32_t num_kv_pages, kv_last_page_len, num_meta_pages, meta_last_page_len; /* the new token already counted */
+  uint32_t rope_pos;            /* position of the new token (quest_rope_decode_batch) */
+  uint32_t reserved[3];
+} QuestSeqDesc;                 /* 64 bytes */
+int quest_decode_layer_step_batch(const void* q, const void* k_new, const void* v_new, void* o,
+                                  const QuestSeqDesc* descs, uint32_t batch, size_t kv_layer_offset,
+                                  size_t meta_layer_offset, uint32_t max_kv_pages, void* scores,
+                                  size_t scores_seq_stride, int32_t* topk_idx, uint32_t k,
+                                  uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                                  uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                                  size_t workspace_seq_bytes, void* stream);
+/* RoPE of one new token per sequence at the position in its record: q [batch, num_qo_heads, head_dim],
+ * k [batch, num_kv_heads, head_dim] (apply_rope_in_place with a device-resident past_kv_len, page.cu:212-253). */
+int quest_rope_decode_batch(void* q, void* k, const QuestSeqDesc* descs, uint32_t batch, uint32_t num_qo_heads,
+                            uint32_t num_kv_heads, uint32_t head_dim, float rope_scale, float rope_theta, void* stream);
+
 /* ---- paged causal prefill ----------------------------------------------------------------------
  * Replaces prefill_with_paged_kv_cache (bsk_ops.h:78-86, batch_prefill.cu:27-117, prefill.cuh:674-1115).
  * q, o: [qo_len, num_qo_heads, head_dim]; the KV sequence is the num_kv_pages pages of kv_indices

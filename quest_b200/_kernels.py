@@ -34,6 +34,9 @@ SIGNATURES = {
     "quest_sparse_decode_step": (_c.c_int, [_vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_decode_layer_step": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32,
                                            _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
+    "quest_decode_layer_step_batch": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _u32, _sz, _sz, _u32, _vp, _sz, _i32p, _u32, _u32, _u32,
+                                                 _u32, _u32, _u32, _vp, _sz, _vp]),
+    "quest_rope_decode_batch": (_c.c_int, [_vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _f32, _vp]),
     "quest_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _c.c_int, _u32, _u32, _u32, _u32, _vp]),
     "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _u32, _vp, _vp, _u32, _u32, _vp]),
     "quest_peer_staging_bytes": (_sz, [_u32, _u32, _u32]),

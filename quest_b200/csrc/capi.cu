@@ -14,7 +14,12 @@ int launch_fused_step(const void* q, void* o, const void* kv_data, const int32_t
                       cudaStream_t stream);  // fused.cu
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
-                      uint32_t flags, const AppendArgs& ap, cudaStream_t s);  // estimate.cu
+                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba = BatchArgs{},
+                      uint32_t batch = 1);  // estimate.cu
+int topk_batch(const void* scores, int32_t* out_idx, uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba,
+               uint32_t batch, cudaStream_t s);  // topk.cu
+int decode_batch(const void* q, void* o, const int32_t* indices, uint32_t n_sel, uint32_t Hq, uint32_t Hkv, uint32_t D,
+                 uint32_t P, uint32_t ppc, void* ws, const BatchArgs& ba, uint32_t batch, cudaStream_t s);  // decode.cu
 int pdl_enabled() {
   static int v = -1;
   if (v < 0) {
@@ -89,4 +94,34 @@ extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const v
   if (rc) return rc;
   return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, kv_last_page_idx, kv_last_page_len, num_qo_heads, num_kv_heads,
                           head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
+}
+
+// The layer step for a batch of sequences, driven by per-sequence records in device memory (see include/quest_b200.h).
+extern "C" int quest_decode_layer_step_batch(const void* q, const void* k_new, const void* v_new, void* o,
+                                             const QuestSeqDesc* descs, uint32_t batch, size_t kv_layer_offset,
+                                             size_t meta_layer_offset, uint32_t max_kv_pages, void* scores,
+                                             size_t scores_seq_stride, int32_t* topk_idx, uint32_t k,
+                                             uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                                             uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                                             size_t workspace_seq_bytes, void* stream) {
+  if (!q || !k_new || !v_new || !o || !descs || !batch || !scores || !topk_idx || !workspace) return QUEST_ERR_BAD_ARG;
+  if (!num_qo_heads || !num_kv_heads || !page_size || !pages_per_chunk || num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
+  if (max_kv_pages < 2 || k == 0 || batch > 65535) return QUEST_ERR_BAD_ARG;
+  const uint32_t max_len = max_kv_pages - 1;
+  if (scores_seq_stride < (size_t)num_qo_heads * max_len) return QUEST_ERR_BAD_ARG;
+  const uint32_t nchunks = (k + 1 + pages_per_chunk - 1) / pages_per_chunk;
+  if (workspace_seq_bytes % 16 || workspace_seq_bytes < quest_decode_workspace_bytes(num_qo_heads, head_dim, nchunks))
+    return QUEST_ERR_WORKSPACE;
+  quest::BatchArgs ba = {reinterpret_cast<const quest::SeqDesc*>(descs), kv_layer_offset, meta_layer_offset,
+                         scores_seq_stride, workspace_seq_bytes};
+  // the append rides on the estimate launch; its pointers and lengths are taken from the records inside the kernel
+  quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, nullptr, nullptr, nullptr, 0, 0, 0, 0};
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = quest::estimate_dispatch(q, scores, max_len, nullptr, nullptr, num_qo_heads, num_kv_heads, head_dim, page_size,
+                                    QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, s, ba, batch);
+  if (rc) return rc;
+  rc = quest::topk_batch(scores, topk_idx, num_qo_heads, max_len, k, ba, batch, s);
+  if (rc) return rc;
+  return quest::decode_batch(q, o, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
+                             ba, batch, s);
 }

@@ -144,6 +144,25 @@ struct AppendArgs {
   uint32_t num_kv_pages, kv_last_len, num_meta_pages, meta_last_len;
 };
 
+// Descriptor-driven launches (quest_decode_layer_step_batch): everything that changes from token to token lives in one
+// 64-byte record per sequence in DEVICE memory (== QuestSeqDesc of include/quest_b200.h), so that a captured CUDA graph of
+// the step can be replayed for the next token after the records were refreshed.  descs == nullptr: scalar arguments.
+struct SeqDesc {
+  const uint8_t* kv_data;        // the sequence's KV pool (all layers), bytes
+  const uint8_t* meta_data;      // its metadata pool
+  const int32_t* kv_indices;     // device page tables
+  const int32_t* meta_indices;
+  uint32_t num_kv_pages, kv_last_page_len, num_meta_pages, meta_last_page_len;  // the new token already counted
+  uint32_t rope_pos, reserved[3];
+};
+static_assert(sizeof(SeqDesc) == 64, "SeqDesc is part of the C ABI");
+struct BatchArgs {
+  const SeqDesc* descs;
+  size_t kv_layer_off, meta_layer_off;  // byte offset of the layer inside every sequence's pools
+  size_t score_stride;                  // elements between the sequences' score blocks
+  size_t ws_stride;                     // bytes between the sequences' decode workspaces
+};
+
 constexpr float kLog2e = 1.44269504088896340736f;
 
 // Decode workspace layout (caller-owned bytes, zero-filled once when allocated):

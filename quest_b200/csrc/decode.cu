@@ -44,10 +44,30 @@ __device__ __forceinline__ uint32_t div_p(uint32_t t, uint32_t p_magic) { return
 // stay in flight, ~128 KB per SM at 8 CTAs/SM, and the softmax arithmetic hides under them.
 template <int D, int kThreads, int kMinBlocks>
 __global__ void __launch_bounds__(kThreads, kMinBlocks)
-decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __restrict__ lse,
-              const __half* __restrict__ kv, const int32_t* __restrict__ indices, uint32_t idx_stride,
-              uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len, uint32_t Hkv, uint32_t G,
-              uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws) {
+decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __restrict__ lse_,
+              const __half* __restrict__ kv_, const int32_t* __restrict__ indices_, uint32_t idx_stride,
+              uint32_t n_sel, uint32_t last_page_idx_, uint32_t last_page_len_, uint32_t Hkv, uint32_t G,
+              uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws_,
+              const BatchArgs ba) {
+  const __half* __restrict__ q = q_;
+  __half* __restrict__ o = o_;
+  float* __restrict__ lse = lse_;
+  const __half* __restrict__ kv = kv_;
+  const int32_t* __restrict__ indices = indices_;
+  uint32_t last_page_idx = last_page_idx_, last_page_len = last_page_len_;
+  uint8_t* __restrict__ ws = ws_;
+  if (ba.descs != nullptr) {  // descriptor mode: blockIdx.z = sequence (its record is constant during the step)
+    const SeqDesc* d = ba.descs + blockIdx.z;
+    const size_t b = blockIdx.z, Hq_ = gridDim.y;
+    q += b * Hq_ * D;
+    o += b * Hq_ * D;
+    if (lse) lse += b * Hq_;
+    kv = reinterpret_cast<const __half*>(d->kv_data + ba.kv_layer_off);
+    indices += b * Hq_ * idx_stride;
+    last_page_len = d->kv_last_page_len;
+    last_page_idx = (uint32_t)d->kv_indices[d->num_kv_pages - 1];
+    ws += b * ba.ws_stride;
+  }
   constexpr int kWarps = kThreads / 32;
   constexpr int LPR = D / 8;
   constexpr int TPL = 32 / LPR;           // token rows per warp-wide load
@@ -310,13 +330,14 @@ decode_kernel(const __half* __restrict__ q, __half* __restrict__ o, float* __res
 template <int D>
 static int launch_decode(const void* q, void* o, float* lse, const void* kv, const int32_t* indices,
                          uint32_t idx_stride, uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len,
-                         uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t ppc, void* ws, cudaStream_t stream) {
+                         uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t ppc, void* ws, cudaStream_t stream,
+                         const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
   const uint32_t nchunks = (n_sel + 1 + ppc - 1) / ppc;
   const uint32_t npg_max = ppc < n_sel + 1 ? ppc : n_sel + 1;
   const size_t smem = (size_t)npg_max * sizeof(int32_t);
   if (smem > 32 * 1024) return QUEST_ERR_UNSUPPORTED;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(nchunks, Hq);
+  cfg.gridDim = dim3(nchunks, Hq, batch);
   cfg.blockDim = dim3(kDecThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
@@ -328,9 +349,20 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
   const float sm_scale_log2 = kLog2e / sqrtf((float)D);
   cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<D, kDecThreads, 7>, (const __half*)q, (__half*)o, lse,
                                      (const __half*)kv, indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv,
-                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws);
+                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
+}
+
+// descriptor mode (quest_decode_layer_step_batch)
+int decode_batch(const void* q, void* o, const int32_t* indices, uint32_t n_sel, uint32_t Hq, uint32_t Hkv, uint32_t D,
+                 uint32_t P, uint32_t ppc, void* ws, const BatchArgs& ba, uint32_t batch, cudaStream_t s) {
+  switch (D) {
+    case 64: return launch_decode<64>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch);
+    case 128: return launch_decode<128>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch);
+    case 256: return launch_decode<256>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch);
+    default: return QUEST_ERR_UNSUPPORTED;
+  }
 }
 
 }  // namespace quest

@@ -162,10 +162,37 @@ __device__ __forceinline__ float reduce4_transposed(const float a[4], uint32_t l
 // kG = 0: any group size, one lane row per kv head looping over its q heads, q/mask in smem.
 template <int D, int kOrdered, int kG>
 __global__ void __launch_bounds__(kTileWarps * 32, 2)
-estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t len,
-                     const __half* __restrict__ meta, const int32_t* __restrict__ meta_indices,
+estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uint32_t len_,
+                     const __half* __restrict__ meta_, const int32_t* __restrict__ meta_indices_,
                      uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_magic /* ceil(2^32/P), 0 for P=1 */,
-                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap) {
+                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap_, const BatchArgs ba) {
+  // descriptor mode: blockIdx.y = sequence; lengths, page tables and pools come from its device record
+  const __half* __restrict__ q = q_;
+  __half* __restrict__ o = o_;
+  uint32_t len = len_;
+  const __half* __restrict__ meta = meta_;
+  const int32_t* __restrict__ meta_indices = meta_indices_;
+  AppendArgs ap = ap_;
+  if (ba.descs != nullptr) {
+    const SeqDesc* d = ba.descs + blockIdx.y;
+    const uint32_t npg = d->num_kv_pages;
+    len = npg - 1;
+    meta = reinterpret_cast<const __half*>(d->meta_data + ba.meta_layer_off);
+    meta_indices = d->meta_indices;
+    q += (size_t)blockIdx.y * Hq * (D);
+    o += (size_t)blockIdx.y * ba.score_stride;
+    if (ap.k != nullptr) {
+      ap.k += (size_t)blockIdx.y * Hkv * (D);
+      ap.v += (size_t)blockIdx.y * Hkv * (D);
+      ap.kv = reinterpret_cast<__half*>(const_cast<uint8_t*>(d->kv_data) + ba.kv_layer_off);
+      ap.kv_indices = d->kv_indices;
+      ap.meta = const_cast<__half*>(meta);
+      ap.num_kv_pages = npg;
+      ap.kv_last_len = d->kv_last_page_len;
+      ap.num_meta_pages = d->num_meta_pages;
+      ap.meta_last_len = d->meta_last_page_len;
+    }
+  }
   constexpr int LPR = D / 8, RPL = 32 / LPR, kThreads = kTileWarps * 32, kDepth = 4;
   constexpr uint32_t T_r = kTileWarps * RPL;  // metadata rows per CTA pass; Hkv divides T_r
   extern __shared__ __align__(16) uint8_t est_smem[];
@@ -192,6 +219,7 @@ estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
   // append_kv of the step's new token rides on one extra CTA of this launch.  The entry it updates (the last
   // page's) is not one of the scored ones; the decode kernel two launches later reads the new K/V row.
   const bool carries_append = !scans;
+  if (len == 0 && !carries_append) return;  // descriptor mode: a sequence with nothing to score yet
   if (!meta_stable || carries_append) pdl_wait();  // see QUEST_EST_META_STABLE
   if (carries_append) {
     const uint32_t row_vecs = Hkv * D / 8;
@@ -324,7 +352,8 @@ estimate_tile_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
 template <int D>
 static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void* meta, const int32_t* meta_indices,
                                 uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t flags, const AppendArgs& ap,
-                                cudaStream_t stream) {
+                                cudaStream_t stream, const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
+  // descriptor mode (ba.descs): `len` is an upper bound over the batch (sizes the grid and the page-table staging)
   constexpr uint32_t T_r = kTileWarps * (32 / (D / 8));
   static int num_sms = 0;
   if (!num_sms) {
@@ -338,7 +367,9 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   uint32_t g_shift = 0;
   while ((1u << g_shift) < G) ++g_shift;
   const uint32_t PPP = T_r / (per_q ? Hq : Hkv);
-  uint32_t grid = 2 * num_sms - (ap.k != nullptr ? 1u : 0u);  // scanning CTAs
+  uint32_t grid = 2 * num_sms / batch;  // CTAs per sequence
+  if (grid < 8) grid = 8;
+  grid -= (ap.k != nullptr ? 1u : 0u);  // scanning CTAs
   const uint32_t need = (len + PPP - 1) / PPP;  // at least one pass of pages per CTA
   if (grid > need) grid = need;
   if (ap.k != nullptr) ++grid;  // + the CTA that carries the append
@@ -354,7 +385,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
     if (e != cudaSuccess) return (int)e;
   }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(grid);
+  cfg.gridDim = dim3(grid, batch);
   cfg.blockDim = dim3(kTileWarps * 32);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
@@ -365,7 +396,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   cfg.numAttrs = 1;
   const uint32_t p_magic = P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P);
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta, meta_indices,
-                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap);
+                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap, ba);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -420,7 +451,7 @@ namespace quest {
 // estimate, optionally carrying the step's append_kv (ap.k != nullptr) on the tile kernel's first CTA
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
-                      uint32_t flags, const AppendArgs& ap, cudaStream_t s) {
+                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba, uint32_t batch) {
   if ((size_t)num_qo_heads * head_dim * 6 > 160 * 1024) return QUEST_ERR_UNSUPPORTED;
   {  // product path: the tile kernel, whenever the kv heads divide its row tile
     const uint32_t T_r = kTileWarps * (32 / (head_dim / 8));
@@ -431,12 +462,13 @@ int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_dat
     }
     if (!force_rows && len && T_r % num_kv_heads == 0 && (head_dim == 64 || head_dim == 128 || head_dim == 256)) {
       switch (head_dim) {
-        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s);
-        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s);
-        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s);
+        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
+        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
+        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
       }
     }
   }
+  if (ba.descs != nullptr) return QUEST_ERR_UNSUPPORTED;  // descriptor mode exists for the tile kernel only
   if (ap.k != nullptr) {  // generic path: append as its own launch
     const int rc = quest_append_decode(ap.k, ap.v, ap.kv, ap.kv_indices, ap.num_kv_pages, ap.kv_last_len, ap.meta,
                                        meta_indices, ap.num_meta_pages, ap.meta_last_len, num_kv_heads, head_dim,
@@ -463,5 +495,5 @@ extern "C" int quest_estimate(const void* q, void* o, uint32_t len, const void* 
   if (len == 0) return QUEST_OK;
   quest::AppendArgs none = {};
   return quest::estimate_dispatch(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                  flags, none, (cudaStream_t)stream);
+                                  flags, none, (cudaStream_t)stream, quest::BatchArgs{}, 1);
 }

@@ -11,7 +11,7 @@ namespace quest {
 template <int D>
 __global__ void __launch_bounds__(256)
 rope_kernel(__half* __restrict__ q, __half* __restrict__ k, uint32_t seq_len, uint32_t past_len, uint32_t Hq,
-            uint32_t Hkv, float rcp_scale, float rcp_theta) {
+            uint32_t Hkv, float rcp_scale, float rcp_theta, const SeqDesc* __restrict__ descs) {
   constexpr int LPR = D / 8;
   pdl_wait();
   const uint32_t lir = threadIdx.x % LPR;
@@ -25,7 +25,8 @@ rope_kernel(__half* __restrict__ q, __half* __restrict__ k, uint32_t seq_len, ui
     const bool is_q = r < q_rows;
     const size_t rr = is_q ? r : r - q_rows;
     const uint32_t H = is_q ? Hq : Hkv;
-    const uint32_t pos = past_len + (uint32_t)(rr / H);
+    // descs: row i is the new token of sequence i, rotated at that sequence's own position (read from its device record)
+    const uint32_t pos = descs ? descs[rr / H].rope_pos : past_len + (uint32_t)(rr / H);
     __half* x = (is_q ? q : k) + rr * D;
     const bool lo_half = lir * 8 < D / 2;
     float a[8], b[8];
@@ -104,9 +105,9 @@ __global__ void merge_states_kernel(const float* __restrict__ o_parts, const flo
 
 }  // namespace quest
 
-extern "C" int quest_rope_inplace(void* q, void* k, uint32_t seq_len, uint32_t past_kv_len, uint32_t num_qo_heads,
-                                  uint32_t num_kv_heads, uint32_t head_dim, float rope_scale, float rope_theta,
-                                  void* stream) {
+static int rope_launch(void* q, void* k, uint32_t seq_len, uint32_t past_kv_len, uint32_t num_qo_heads,
+                       uint32_t num_kv_heads, uint32_t head_dim, float rope_scale, float rope_theta, const void* descs,
+                       void* stream) {
   if (!q || !k || !num_qo_heads || !num_kv_heads) return QUEST_ERR_BAD_ARG;
   if (seq_len == 0) return QUEST_OK;
   const float rs = 1.f / rope_scale, rt = 1.f / rope_theta;
@@ -115,9 +116,9 @@ extern "C" int quest_rope_inplace(void* q, void* k, uint32_t seq_len, uint32_t p
   const uint32_t grid = (uint32_t)((rows + rows_per_cta - 1) / rows_per_cta < 148 * 8 ? (rows + rows_per_cta - 1) / rows_per_cta : 148 * 8);
   cudaStream_t s = (cudaStream_t)stream;
   switch (head_dim) {
-    case 64: quest::rope_kernel<64><<<grid, 256, 0, s>>>((__half*)q, (__half*)k, seq_len, past_kv_len, num_qo_heads, num_kv_heads, rs, rt); break;
-    case 128: quest::rope_kernel<128><<<grid, 256, 0, s>>>((__half*)q, (__half*)k, seq_len, past_kv_len, num_qo_heads, num_kv_heads, rs, rt); break;
-    case 256: quest::rope_kernel<256><<<grid, 256, 0, s>>>((__half*)q, (__half*)k, seq_len, past_kv_len, num_qo_heads, num_kv_heads, rs, rt); break;
+    case 64: quest::rope_kernel<64><<<grid, 256, 0, s>>>((__half*)q, (__half*)k, seq_len, past_kv_len, num_qo_heads, num_kv_heads, rs, rt, (const quest::SeqDesc*)descs); break;
+    case 128: quest::rope_kernel<128><<<grid, 256, 0, s>>>((__half*)q, (__half*)k, seq_len, past_kv_len, num_qo_heads, num_kv_heads, rs, rt, (const quest::SeqDesc*)descs); break;
+    case 256: quest::rope_kernel<256><<<grid, 256, 0, s>>>((__half*)q, (__half*)k, seq_len, past_kv_len, num_qo_heads, num_kv_heads, rs, rt, (const quest::SeqDesc*)descs); break;
     default: return QUEST_ERR_UNSUPPORTED;
   }
   QUEST_RETURN_LAUNCH();
@@ -141,4 +142,17 @@ extern "C" int quest_merge_states(const float* o_parts, const float* lse_parts, 
   quest::merge_states_kernel<<<num_heads, 128, 0, (cudaStream_t)stream>>>(o_parts, lse_parts, n, so, sl, (__half*)o,
                                                                           lse, num_heads, head_dim);
   QUEST_RETURN_LAUNCH();
+}
+
+extern "C" int quest_rope_inplace(void* q, void* k, uint32_t seq_len, uint32_t past_kv_len, uint32_t num_qo_heads,
+                                  uint32_t num_kv_heads, uint32_t head_dim, float rope_scale, float rope_theta,
+                                  void* stream) {
+  return rope_launch(q, k, seq_len, past_kv_len, num_qo_heads, num_kv_heads, head_dim, rope_scale, rope_theta, nullptr, stream);
+}
+
+extern "C" int quest_rope_decode_batch(void* q, void* k, const QuestSeqDesc* descs, uint32_t batch, uint32_t num_qo_heads,
+                                       uint32_t num_kv_heads, uint32_t head_dim, float rope_scale, float rope_theta,
+                                       void* stream) {
+  if (!descs) return QUEST_ERR_BAD_ARG;
+  return rope_launch(q, k, batch, 0, num_qo_heads, num_kv_heads, head_dim, rope_scale, rope_theta, descs, stream);
 }

@@ -36,18 +36,38 @@ topk_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_
 
 template <int W, int G>
 __global__ void __launch_bounds__(32 * W)
-topk_fast_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_idx, uint32_t in_stride,
-                 uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx, uint32_t len, uint32_t k) {
+topk_fast_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_idx_, uint32_t in_stride_,
+                 uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_,
+                 const BatchArgs ba) {
   constexpr int NK = 4 * G;  // keys per thread
   __shared__ __align__(16) uint16_t keys[NK * 32 * W];
   __shared__ TopkFastScratch<W, G> sc;
   constexpr uint32_t T = 32 * W;
   const uint32_t head = blockIdx.x, tid = threadIdx.x;
-  const uint16_t* s = scores + (size_t)head * len;
+  const int32_t* __restrict__ in_idx = in_idx_;
+  int32_t* __restrict__ out_idx = out_idx_;
+  uint32_t in_stride = in_stride_, len = len_, k = k_;
 #if QUEST_TRIG_TOPK
   pdl_trigger();
 #endif
   pdl_wait();  // scores come from the estimate kernel
+  if (ba.descs != nullptr) {
+    // descriptor mode: blockIdx.y = sequence; row length and payload (the sequence's page table) from its record.
+    // A sequence with fewer scored pages than k selects all of them; the rest of its row is -1 (no page).
+    const SeqDesc* d = ba.descs + blockIdx.y;
+    len = d->num_kv_pages - 1;
+    in_idx = d->kv_indices;
+    in_stride = 0;
+    scores += (size_t)blockIdx.y * ba.score_stride;
+    out_idx += (size_t)blockIdx.y * gridDim.x * k_;
+    if (len > (uint32_t)(NK * T)) len = NK * T;  // never: the host sizes the variant by its bound
+    if (k > len) {
+      for (uint32_t i = len + tid; i < k_; i += T) out_idx[(size_t)head * k_ + i] = -1;
+      k = len;
+    }
+    if (k == 0) return;
+  }
+  const uint16_t* s = scores + (size_t)head * len;
   // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent (NK per thread); the whole key
   // array is written (0xffff -> key 0 past the row's end)
   uint16_t v[NK];
@@ -57,14 +77,15 @@ topk_fast_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict_
   for (int j = 0; j < NK; ++j) keys[tid + j * T] = key_of(v[j]);
   __syncthreads();
   topk_select_fast<W, TopkNoHook, G>(keys, len, k, tid, 1, &sc, in_idx ? in_idx + (size_t)head * in_stride : nullptr,
-                                     out_idx + (size_t)head * k, out_val ? out_val + (size_t)head * k : nullptr);
+                                     out_idx + (size_t)head * k_, out_val ? out_val + (size_t)head * k_ : nullptr);
 }
 
 template <int W, int G>
 static int launch_topk_fast(const void* scores, const int32_t* in_idx, uint32_t in_stride, void* out_val, int32_t* out_idx,
-                            uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream) {
+                            uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream,
+                            const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(num_heads);
+  cfg.gridDim = dim3(num_heads, batch);
   cfg.blockDim = dim3(32 * W);
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -73,9 +94,20 @@ static int launch_topk_fast(const void* scores, const int32_t* in_idx, uint32_t 
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaError_t e = cudaLaunchKernelEx(&cfg, topk_fast_kernel<W, G>, (const uint16_t*)scores, in_idx, in_stride,
-                                     (uint16_t*)out_val, out_idx, len, k);
+                                     (uint16_t*)out_val, out_idx, len, k, ba);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
+}
+
+// descriptor mode (quest_decode_layer_step_batch): max_len bounds every sequence's row; fast variants only
+int topk_batch(const void* scores, int32_t* out_idx, uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba,
+               uint32_t batch, cudaStream_t s) {
+  if (max_len <= 1024) return launch_topk_fast<8, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+  if (max_len <= 2048) return launch_topk_fast<16, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+  if (max_len <= 4096) return launch_topk_fast<32, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+  if (max_len <= 8192) return launch_topk_fast<32, 2>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+  if (max_len <= 16384) return launch_topk_fast<32, 4>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+  return QUEST_ERR_UNSUPPORTED;
 }
 
 template <int W, int KPC>
