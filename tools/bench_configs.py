@@ -110,6 +110,21 @@ def config4(args, rank, world, dev):
     out = torch.empty(batch, L, 1, Hq, D, dtype=torch.float16, device=dev)
 
     side = [torch.cuda.Stream() for _ in range(min(args.streams, batch))]
+    bsteps = []
+    if args.batched:
+        # descriptor-driven batched launches (quest_decode_layer_step_batch): `--batched` groups of sequences, each group
+        # three launches per layer on its own stream
+        from quest_b200.utils.batch import BatchDecodeStep
+        ng = max(1, min(args.batched, batch))
+        groups = [list(range(g, batch, ng)) for g in range(ng)]
+        for grp in groups:
+            bs = BatchDecodeStep([ics[b] for b in grp])
+            bs.update_host()
+            bs.upload()
+            idx = torch.tensor(grp, device=dev)
+            bsteps.append((bs, q[idx].transpose(0, 1).contiguous(), kn[idx].transpose(0, 1).contiguous(),
+                           vn[idx].transpose(0, 1).contiguous(), torch.empty(L, len(grp), Hq, D, dtype=torch.float16, device=dev)))
+        side = [torch.cuda.Stream() for _ in range(ng)] if ng > 1 else []
 
     def step():
         # The sequences of a batch are independent: per layer they are forked over `--streams` streams (inside the
@@ -118,6 +133,15 @@ def config4(args, rank, world, dev):
         # the others' metadata / KV streams.
         cur = torch.cuda.current_stream()
         for l in range(L):
+            if bsteps:
+                for st in side:
+                    st.wait_stream(cur)
+                for g, (bs, bq, bk, bv, bo) in enumerate(bsteps):
+                    with torch.cuda.stream(side[g] if side else cur):
+                        bs.layer_step(bq[l, :, 0], bk[l, :, 0], bv[l, :, 0], l, out=bo[l])
+                for st in side:
+                    cur.wait_stream(st)
+                continue
             if not side:
                 for b in range(batch):
                     qu.decode_layer_step(q[b, l], kn[b, l], vn[b, l], ics[b], l, out=out[b, l])
@@ -139,7 +163,7 @@ def config4(args, rank, world, dev):
     return step, L, per_layer_rank, {
         "workload": "Llama-3.1-8B GQA shape (32q/8kv x 128, fp16), 128K ctx, page 16, budget 4096, batch 8",
         "parallelism": f"kv-head sharded x{world} ({Hkv} kv / {Hq} q heads per rank), no collective", "scaling": "strong",
-        "streams": len(side),
+        "streams": len(side), "batched_groups": len(bsteps),
         "selection": "per q head (reference semantics, evaluation/quest_attention.py:139-140)"}
 
 
@@ -192,6 +216,7 @@ def main():
     ap.add_argument("--config", type=int, required=True, choices=[4, 5])
     ap.add_argument("--layers", type=int, default=2)
     ap.add_argument("--streams", type=int, default=8, help="config 4: concurrent sequences per layer (0 = one stream)")
+    ap.add_argument("--batched", type=int, default=0, help="config 4: N groups of sequences, one batched launch chain each")
     ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"], help="config 5: how the two all-gathers are done")
     ap.add_argument("--graph-collectives", action="store_true", help="config 5, N > 1: also capture the NCCL step in a CUDA graph")
     ap.add_argument("--steps", type=int, default=30)

@@ -75,6 +75,26 @@ class Decoder:
         last = qu.rms_norm_forward(x[-1:].unsqueeze(0), self.norm, EPS).squeeze(0)
         return last @ self.lm_head
 
+    def decode_body(self, x, step_full, step_quest):
+        """One decode token with the descriptor-driven step (BatchDecodeStep, batch 1): no host-side value changes from
+        token to token, so the whole body is captured once and replayed.  x: [1, HID] static input buffer."""
+        step_full.upload()
+        if step_quest is not step_full:
+            step_quest.upload()
+        for i, ly in enumerate(self.layers):
+            st = step_full if i < SKIP_LAYERS else step_quest
+            h = qu.rms_norm_forward(x.unsqueeze(0), ly["n1"], EPS).squeeze(0)
+            qkv = (h @ ly["wqkv"]).view(3, H, D)
+            q, k, v = qkv[0:1], qkv[1:2], qkv[2:3]          # [1, H, D] each, contiguous
+            st.rope(q, k, rope_scale=ROPE_SCALE)
+            o = st.layer_step(q, k, v, i)
+            x = x + o.view(1, HID) @ ly["wo"]
+            h = qu.rms_norm_forward(x.unsqueeze(0), ly["n2"], EPS).squeeze(0)
+            gu = h @ ly["wgu"]
+            x = x + (torch.nn.functional.silu(gu[:, :INTER]) * gu[:, INTER:]) @ ly["wd"]
+        last = qu.rms_norm_forward(x.unsqueeze(0), self.norm, EPS).squeeze(0)
+        return last @ self.lm_head
+
 
 @torch.inference_mode()
 def main():
@@ -84,6 +104,8 @@ def main():
     ap.add_argument("--token_budget", type=int, default=2048, help="0 = full cache on every layer")
     ap.add_argument("--layers", type=int, default=L)
     ap.add_argument("--prefill_chunk", type=int, default=8192)
+    ap.add_argument("--graph", action="store_true", help="decode through ONE captured CUDA graph replayed per token "
+                    "(descriptor-driven step, quest_decode_layer_step_batch) instead of eager operator calls")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
@@ -104,6 +126,8 @@ def main():
     torch.cuda.synchronize()
     prefill_s = time.perf_counter() - t0
 
+    if a.graph:
+        return graph_decode(a, model, ic, budget_pages, max_pages, prefill_s, dev)
     lat = []
     for step in range(a.decode_len):
         x = torch.randn(1, HID, dtype=torch.float16, device=dev)
@@ -129,6 +153,55 @@ def main():
                       "page_size": P, "layers": a.layers, "attention_path_ms_per_token": attn, "attention_share": attn / ms,
                       "model": "LongChat-7B-v1.5-32K shape, random init fp16, batch 1; torch matmuls + quest_b200 operators, eager",
                       "protocol": "reference scripts/bench_textgen.py (random embeddings in, mean decode latency)"}))
+
+
+def graph_decode(a, model, ic, budget_pages, max_pages, prefill_s, dev):
+    from quest_b200.utils.batch import BatchDecodeStep
+    ic.set_page_budget(max_pages)
+    step_full = BatchDecodeStep([ic])            # layers 0-1: every page selected (k >= pages -> the rest of the row is -1)
+    ic.set_page_budget(budget_pages)
+    step_quest = step_full if budget_pages >= max_pages else BatchDecodeStep([ic])
+    x = torch.zeros(1, HID, dtype=torch.float16, device=dev)
+
+    def host_token():
+        ic.prepare_metadata(1)
+        step_full.update_host()
+        if step_quest is not step_full:
+            step_quest.update_host()
+        x.copy_(torch.randn(1, HID, dtype=torch.float16, device=dev))
+
+    host_token()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        model.decode_body(x, step_full, step_quest)     # warm-up (also token 0)
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        logits = model.decode_body(x, step_full, step_quest)
+    lat, dev_ms = [], []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for t in range(a.decode_len):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        host_token()
+        assert step_quest.fits() and step_full.fits()
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        lat.append(time.perf_counter() - t0)
+        dev_ms.append(e0.elapsed_time(e1))
+    assert torch.isfinite(logits.float()).all()
+    warm = lat[8:] if len(lat) > 16 else lat
+    ms = sum(warm) / len(warm) * 1e3
+    print(json.dumps({"metric": "e2e_decode_tok_per_s", "value": 1e3 / ms, "ms_per_token": ms, "prefill_s": prefill_s,
+                      "graph_device_ms_per_token": sorted(dev_ms)[len(dev_ms) // 2],
+                      "context_len": a.context_len, "decode_len": a.decode_len, "token_budget": a.token_budget or "full",
+                      "page_size": P, "layers": a.layers, "mode": "one CUDA graph replayed per token (records refreshed by the host)",
+                      "model": "LongChat-7B-v1.5-32K shape, random init fp16, batch 1; torch matmuls + quest_b200 operators",
+                      "protocol": "reference scripts/bench_textgen.py (random embeddings in, mean decode latency, host work included)"}))
 
 
 if __name__ == "__main__":
