@@ -98,6 +98,8 @@ def _check_token(step, ics_a, ics_b, got_o, L, want_o, want_sel, want_sc, topk_p
     ((3000, 2047), 32, 8, 128, 16, 40),          # GQA
     ((700, 300, 90, 1023), 8, 8, 64, 8, 30),     # 90 tokens = 12 pages < budget: attends to everything
     ((2040,), 32, 32, 128, 16, 16),              # batch of one
+    ((3000, 2047, 5000), 4, 1, 128, 16, 40),     # one kv head per rank (configs[3] sharded over 8 GPUs)
+    ((1500, 1501), 16, 4, 128, 16, 20),
 ])
 def test_batch_step_equals_per_sequence_path(lens, Hq, Hkv, D, P, budget):
     L, T, rope_scale = 2, 4, 2.0
