@@ -6,6 +6,8 @@
 // here is deterministic: lowest position first.
 #include <stdlib.h>
 
+#include <cooperative_groups.h>
+
 #include "topk.cuh"
 
 namespace quest {
@@ -99,11 +101,136 @@ static int launch_topk_fast(const void* scores, const int32_t* in_idx, uint32_t 
   QUEST_RETURN_LAUNCH();
 }
 
+// ---- one row shared by a thread-block cluster --------------------------------------------------------------------
+// The selection is bound by the integer pipe of the ONE SM that holds a row (a 8191-page row: 11.3 us, a 2047-page
+// row: 3.5 us), and only `heads` of the 148 SMs are busy.  Rows longer than 2048 pages are therefore split over a
+// cluster of C CTAs (C x 2048 keys, 4 per thread): every CTA counts its slice, the 16 bin totals of each pass and the
+// (greater, equal) totals of the final compaction are exchanged through distributed shared memory with one cluster
+// barrier each (slots double-buffered on the pass parity), and every CTA takes the same decisions.
+template <int C>
+struct TopkClusterXc {
+  uint32_t (*bins)[C][16];   // [parity][rank][bin] in this CTA's shared memory
+  uint32_t* tot;             // [rank]
+  uint32_t rank;
+  __device__ __forceinline__ uint32_t all_bins(uint32_t s, uint32_t lane, int pass) const {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
+    if (threadIdx.x < 16) {
+#pragma unroll
+      for (int r = 0; r < C; ++r) cl.map_shared_rank(&bins[pass & 1][rank][0], r)[threadIdx.x] = s;
+    }
+    cl.sync();
+    uint32_t a = 0;
+    if (lane < 16) {
+#pragma unroll
+      for (int r = 0; r < C; ++r) a += bins[pass & 1][r][lane];
+    }
+    return a;
+  }
+  __device__ __forceinline__ uint32_t before_me(uint32_t cta_total, uint32_t t) const {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
+    if (t == 0) {
+#pragma unroll
+      for (int r = 0; r < C; ++r) *cl.map_shared_rank(&tot[rank], r) = cta_total;
+    }
+    cl.sync();  // also the last remote access to anybody's shared memory: CTAs may exit after it
+    uint32_t a = 0;
+#pragma unroll
+    for (int r = 0; r < C; ++r)
+      if ((uint32_t)r < rank) a += tot[r];
+    return a;
+  }
+};
+
+template <int W, int C>
+__global__ void __launch_bounds__(32 * W)
+topk_cluster_kernel(const uint16_t* __restrict__ scores, const int32_t* __restrict__ in_idx_, uint32_t in_stride_,
+                    uint16_t* __restrict__ out_val, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_,
+                    const BatchArgs ba) {
+  namespace cg = cooperative_groups;
+  constexpr uint32_t T = 32 * W, NK = 4;
+  __shared__ __align__(16) uint16_t keys[NK * T];
+  __shared__ TopkFastScratch<W, 1> sc;
+  __shared__ uint32_t x_bins[2][C][16];
+  __shared__ uint32_t x_tot[C];
+  const uint32_t rank = cg::this_cluster().block_rank();
+  const uint32_t head = blockIdx.x / C, n_heads = gridDim.x / C, tid = threadIdx.x;
+  const int32_t* __restrict__ in_idx = in_idx_;
+  int32_t* __restrict__ out_idx = out_idx_;
+  uint32_t in_stride = in_stride_, len = len_, k = k_;
+  pdl_wait();  // scores come from the estimate kernel
+  if (ba.descs != nullptr) {  // descriptor mode, as in topk_fast_kernel (uniform over the cluster)
+    const SeqDesc* d = ba.descs + blockIdx.y;
+    len = d->num_kv_pages - 1;
+    in_idx = d->kv_indices;
+    in_stride = 0;
+    scores += (size_t)blockIdx.y * ba.score_stride;
+    out_idx += (size_t)blockIdx.y * n_heads * k_;
+    if (len > C * NK * T) len = C * NK * T;
+    if (k > len) {
+      if (rank == 0)
+        for (uint32_t i = len + tid; i < k_; i += T) out_idx[(size_t)head * k_ + i] = -1;
+      k = len;
+    }
+    if (k == 0) return;  // the whole cluster returns: nobody waits at a cluster barrier
+  }
+  const uint16_t* s = scores + (size_t)head * len;
+  const uint32_t pos0 = rank * NK * T;
+  uint16_t v[NK];
+#pragma unroll
+  for (uint32_t j = 0; j < NK; ++j) v[j] = pos0 + tid + j * T < len ? s[pos0 + tid + j * T] : (uint16_t)0xffffu;
+#pragma unroll
+  for (uint32_t j = 0; j < NK; ++j) keys[tid + j * T] = key_of(v[j]);
+  cg::this_cluster().sync();  // keys visible to the CTA; every CTA of the cluster is running before anyone writes into it
+  TopkClusterXc<C> xc = {x_bins, x_tot, rank};
+  topk_select_fast<W, TopkNoHook, 1, TopkClusterXc<C>>(
+      keys, len, k, tid, 1, &sc, in_idx ? in_idx + (size_t)head * in_stride : nullptr, out_idx + (size_t)head * k_,
+      out_val ? out_val + (size_t)head * k_ : nullptr, TopkNoHook(), xc, pos0);
+}
+
+template <int W, int C>
+static int launch_topk_cluster(const void* scores, const int32_t* in_idx, uint32_t in_stride, void* out_val, int32_t* out_idx,
+                               uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream,
+                               const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_heads * C, batch);
+  cfg.blockDim = dim3(32 * W);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = C;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_cluster_kernel<W, C>, (const uint16_t*)scores, in_idx, in_stride,
+                                     (uint16_t*)out_val, out_idx, len, k, ba);
+  if (e != cudaSuccess) return (int)e;
+  QUEST_RETURN_LAUNCH();
+}
+
+static bool topk_use_cluster() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("QUEST_TOPK_CLUSTER");  // A/B hook: 0 = one CTA per row for every length
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+
 // descriptor mode (quest_decode_layer_step_batch): max_len bounds every sequence's row; fast variants only
 int topk_batch(const void* scores, int32_t* out_idx, uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba,
                uint32_t batch, cudaStream_t s) {
   if (max_len <= 1024) return launch_topk_fast<8, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
   if (max_len <= 2048) return launch_topk_fast<16, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+  if (topk_use_cluster()) {
+    if (max_len <= 4096) return launch_topk_fast<32, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);  // measured equal
+    if (max_len <= 8192) return launch_topk_cluster<16, 4>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+    if (max_len <= 16384) return launch_topk_cluster<16, 8>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+  }
   if (max_len <= 4096) return launch_topk_fast<32, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
   if (max_len <= 8192) return launch_topk_fast<32, 2>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
   if (max_len <= 16384) return launch_topk_fast<32, 4>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
@@ -149,6 +276,11 @@ extern "C" int quest_topk(const void* scores, const int32_t* in_idx, uint32_t in
   static const bool no_fast = getenv("QUEST_TOPK_GENERIC") != nullptr;  // test hook: force the generic kernels
   if (!no_fast && len <= 1024) return quest::launch_topk_fast<8, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 2048) return quest::launch_topk_fast<16, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  if (!no_fast && quest::topk_use_cluster()) {
+    if (len <= 4096) return quest::launch_topk_fast<32, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);  // measured equal
+    if (len <= 8192) return quest::launch_topk_cluster<16, 4>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+    if (len <= 16384) return quest::launch_topk_cluster<16, 8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+  }
   if (!no_fast && len <= 4096) return quest::launch_topk_fast<32, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 8192) return quest::launch_topk_fast<32, 2>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 16384) return quest::launch_topk_fast<32, 4>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);

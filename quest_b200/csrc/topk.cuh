@@ -65,22 +65,31 @@ struct TopkNoHook {
   __device__ __forceinline__ void operator()(bool, unsigned long long) const {}
 };
 
-template <int W, class Hook = TopkNoHook, int G = 1>
+// Xc: how the CTAs of a thread-block cluster that share one row combine their bin counts and output offsets
+// (topk.cu: TopkClusterXc over distributed shared memory); the default is a single CTA per row.
+struct TopkNoXc {
+  __device__ __forceinline__ uint32_t all_bins(uint32_t s, uint32_t, int) const { return s; }
+  __device__ __forceinline__ uint32_t before_me(uint32_t, uint32_t) const { return 0u; }
+};
+
+// pos0: position of this CTA's first key in the row (0 unless a cluster splits the row); n is the row length.
+template <int W, class Hook = TopkNoHook, int G = 1, class Xc = TopkNoXc>
 __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t n, uint32_t k, uint32_t t,
                                                  uint32_t bar_id, TopkFastScratch<W, G>* sc,
                                                  const int32_t* __restrict__ in_idx, int32_t* __restrict__ out_idx,
-                                                 uint16_t* __restrict__ out_val, Hook hook = Hook()) {
+                                                 uint16_t* __restrict__ out_val, Hook hook = Hook(), Xc xc = Xc(),
+                                                 uint32_t pos0 = 0) {
   static_assert(W == 4 || W == 8 || W == 16 || W == 32, "W bytes per bin row are read as 32-bit words");
   static_assert(G == 1 || G == 2 || G == 4, "4, 8 or 16 keys per thread");
   constexpr uint32_t T = 32 * W;
   constexpr int NW = 2 * G, NK = 4 * G;
   const uint32_t lane = t & 31, warp = t >> 5;
-  const uint32_t i0 = t * NK;  // first key of this thread
+  const uint32_t i0 = pos0 + t * NK;  // row position of this thread's first key
   uint32_t wd[NW];
 #pragma unroll
   for (int x = 0; x < NW; ++x) wd[x] = 0;
   if (G == 1) {  // keys are zero-padded to a multiple of 8 past n
-    if (i0 < ((n + 7) & ~7u)) {
+    if (i0 - pos0 < ((n + 7) & ~7u)) {
       const uint2 v = reinterpret_cast<const uint2*>(keys)[t];
       wd[0] = v.x, wd[1] = v.y;
     }
@@ -138,6 +147,7 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
 #pragma unroll
       for (int x = 0; x < W * G / 4; ++x) s = __dp4a(row[x], 0x01010101u, s);
     }
+    s = xc.all_bins(s, lane, pass);  // the row's bin totals when several CTAs share it
     uint32_t suf = s;  // suffix sums over the 16 bin lanes (lanes 16..31 carry zeros)
 #pragma unroll
     for (int off = 1; off < 16; off <<= 1) {
@@ -171,10 +181,14 @@ __device__ __forceinline__ void topk_select_fast(const uint16_t* keys, uint32_t 
   }
   if (lane == 31) sc->wgt[warp] = spk;
   group_bar(bar_id, T);
-  uint32_t before = spk - pk;
+  uint32_t before = spk - pk, cta_total = 0;
 #pragma unroll
-  for (int w2 = 0; w2 < W; ++w2)
-    if ((uint32_t)w2 < warp) before += sc->wgt[w2];
+  for (int w2 = 0; w2 < W; ++w2) {
+    const uint32_t x = sc->wgt[w2];
+    cta_total += x;
+    if ((uint32_t)w2 < warp) before += x;
+  }
+  before += xc.before_me(cta_total, t);  // (greater, equal) counts of the CTAs that hold earlier positions
   uint32_t gt_before = before >> 16, eq_before = before & 0xffffu;
   {
     uint32_t e = eq_before, cut = 0;
