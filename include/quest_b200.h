@@ -227,9 +227,9 @@ int quest_merge_states(const float* o_parts, const float* lse_parts, uint32_t n,
  * dst = [rows][world][row_bytes].  peer_staging[p] / peer_flags[p]: rank p's staging area
  * (quest_peer_staging_bytes) and flag words (world x uint32, zero at start) as mapped into THIS process (host
  * arrays of `world` device pointers; peer-mapped symmetric memory, or plain device memory when world == 1).
- * state: 2 x uint32 of local device memory, zero at start: [0] epoch (advanced by the kernel, so the call can be
- * captured in a CUDA graph), [1] number of waits that ran into timeout_ms (0 = 2000) -- nonzero means dst is not valid.
- * world <= 8. */
+ * state: (1 + world) x uint32 of local device memory, zero at start: [0] number of waits that ran into timeout_ms
+ * (0 = 2000) -- nonzero means dst is not valid; [1 + p] epoch of the exchange with rank p (advanced by the kernel, so
+ * the call can be captured in a CUDA graph).  One CTA per peer: the pairwise exchanges overlap.  world <= 8. */
 size_t quest_peer_staging_bytes(uint32_t rows, uint32_t row_bytes, uint32_t world);
 int quest_peer_allgather(const void* src, uint32_t rows, uint32_t row_bytes, void* const* peer_staging,
                          void* const* peer_flags, void* state, void* dst, uint32_t world, uint32_t rank,

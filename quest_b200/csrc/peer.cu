@@ -3,7 +3,7 @@
 // 16-32 KB per rank -- pure latency for a collective library (two NCCL all-gathers cost ~20 us per layer at 2 GPUs,
 // profiles/r01_s15_long_context_multi_gpu.md).  Here every rank's kernel
 //   1. stores its message straight into every peer's staging buffer (symmetric memory mapped over NVLink / NVSwitch:
-//      16-byte stores, one CTA -- the message is far below the bandwidth-delay product of a link),
+//      16-byte stores, one CTA per peer -- the message is far below the bandwidth-delay product of a link),
 //   2. publishes it: __threadfence_system by every writer, CTA barrier, then one st.release.sys per peer of this
 //      step's epoch into the peer's flag word for this rank,
 //   3. waits (ld.acquire.sys on its OWN flag words, so the polling never crosses the link) until every rank's epoch
@@ -39,48 +39,48 @@ __device__ __forceinline__ unsigned long long global_ns() {
   return t;
 }
 
+// One CTA per peer: CTA p pushes this rank's message into rank p's staging area, publishes it to p, waits for p's
+// message of the same epoch and unpacks it -- the pairwise exchanges are independent, so the remote stores, the fences
+// and the waits of the world-1 links overlap instead of queueing in one CTA.  state[0] counts timed-out waits,
+// state[1 + p] is the epoch of the exchange with rank p (advanced here, so the launch can sit in a CUDA graph).
 __global__ void __launch_bounds__(kPeerThreads)
 peer_allgather_kernel(const uint4* __restrict__ src, uint32_t rows, uint32_t row_vecs, const PeerTable tbl,
-                      uint32_t* __restrict__ state /* [0] epoch, [1] timeouts */, uint4* __restrict__ dst,
-                      uint32_t world, uint32_t rank, unsigned long long timeout_ns) {
+                      uint32_t* __restrict__ state, uint4* __restrict__ dst, uint32_t world, uint32_t rank,
+                      unsigned long long timeout_ns) {
   __shared__ uint32_t s_epoch;
-  const uint32_t tid = threadIdx.x;
+  const uint32_t tid = threadIdx.x, p = blockIdx.x;
   pdl_wait();  // the message comes from the kernel before this one
   if (tid == 0) {
-    s_epoch = state[0] + 1;
-    state[0] = s_epoch;
+    s_epoch = state[1 + p] + 1;
+    state[1 + p] = s_epoch;
   }
   __syncthreads();
   const uint32_t epoch = s_epoch, par = epoch & 1u;
   const uint32_t msg_vecs = rows * row_vecs;
-  const size_t slot = ((size_t)par * world + rank) * msg_vecs;  // my slot in anybody's staging area
-  for (uint32_t j = tid; j < msg_vecs; j += kPeerThreads) {
-    const uint4 v = src[j];
-    for (uint32_t p = 0; p < world; ++p) tbl.staging[p][slot + j] = v;
-  }
+  // push: my slot in rank p's staging area
+  uint4* out = tbl.staging[p] + ((size_t)par * world + rank) * msg_vecs;
+  for (uint32_t j = tid; j < msg_vecs; j += kPeerThreads) out[j] = src[j];
   __threadfence_system();
   __syncthreads();
-  if (tid < world) {
-    st_release_sys(tbl.flags[tid] + rank, epoch);
-    // wait for rank `tid`'s message of this epoch (flag words are monotonic; compare modulo 2^32)
-    const uint32_t* f = tbl.flags[rank] + tid;
+  if (tid == 0) {
+    st_release_sys(tbl.flags[p] + rank, epoch);
+    // wait for rank p's message of this epoch (flag words are monotonic; compare modulo 2^32)
+    const uint32_t* f = tbl.flags[rank] + p;
     const unsigned long long t0 = global_ns();
     uint32_t spins = 0;
     while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
       if ((++spins & 1023u) == 0 && global_ns() - t0 > timeout_ns) {
-        atomicAdd(state + 1, 1u);
+        atomicAdd(state, 1u);
         break;
       }
     }
   }
   __syncthreads();
-  // unpack: dst[row][r][vec] = staging[par][r][row][vec]
-  const uint4* mine = tbl.staging[rank] + (size_t)par * world * msg_vecs;
-  const uint32_t total = world * msg_vecs;
-  for (uint32_t i = tid; i < total; i += kPeerThreads) {
-    const uint32_t r = i / msg_vecs, j = i - r * msg_vecs;
+  // unpack rank p's slot of my staging area: dst[row][p][vec] = staging[par][p][row][vec]
+  const uint4* mine = tbl.staging[rank] + ((size_t)par * world + p) * msg_vecs;
+  for (uint32_t j = tid; j < msg_vecs; j += kPeerThreads) {
     const uint32_t row = j / row_vecs, vec = j - row * row_vecs;
-    dst[((size_t)row * world + r) * row_vecs + vec] = mine[i];
+    dst[((size_t)row * world + p) * row_vecs + vec] = mine[j];
   }
 }
 
@@ -99,7 +99,7 @@ extern "C" int quest_peer_allgather(const void* src, uint32_t rows, uint32_t row
     tbl.flags[p] = (uint32_t*)peer_flags[p];
   }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(1);
+  cfg.gridDim = dim3(world);
   cfg.blockDim = dim3(quest::kPeerThreads);
   cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute attr[1];

@@ -190,7 +190,7 @@ class SeqShardedDecode:
             "cand": (arr(*bases), arr(*[b + off_flags for b in bases])),
             "rec": (arr(*[b + off_rec for b in bases]), arr(*[b + off_flags + self.R * 4 for b in bases])),
         }
-        self.peer_state = torch.zeros(2, 2, dtype=torch.int32, device=self.dev)  # [cand | rec][epoch, timeouts]
+        self.peer_state = torch.zeros(2, 1 + self.R, dtype=torch.int32, device=self.dev)  # [cand | rec][timeouts, epochs..]
 
     def _peer_gather(self, kind: str, src: torch.Tensor, rows: int, row_bytes: int, dst: torch.Tensor):
         staging, flags = self._peer_ptrs[kind]
@@ -201,7 +201,7 @@ class SeqShardedDecode:
     def check_peer(self):
         """Synchronise and raise if any peer wait ran into its time limit (a rank missing from the exchange)."""
         if self.exchange == "peer":
-            n = int(self.peer_state[:, 1].sum().item())
+            n = int(self.peer_state[:, 0].sum().item())
             if n:
                 raise RuntimeError(f"quest_peer_allgather: {n} waits timed out (a rank did not take part)")
 

@@ -139,7 +139,7 @@ def test_peer_allgather_kernel_layout_and_epochs():
     nst = lib.quest_peer_staging_bytes(rows, row_bytes, R)
     stg = [torch.zeros(nst, dtype=torch.uint8, device=DEV) for _ in range(R)]
     flg = [torch.zeros(R, dtype=torch.int32, device=DEV) for _ in range(R)]
-    state = [torch.zeros(2, dtype=torch.int32, device=DEV) for _ in range(R)]
+    state = [torch.zeros(1 + R, dtype=torch.int32, device=DEV) for _ in range(R)]
     src = [torch.zeros(rows, row_bytes, dtype=torch.uint8, device=DEV) for _ in range(R)]
     dst = [torch.zeros(rows, R, row_bytes, dtype=torch.uint8, device=DEV) for _ in range(R)]
     arr = ctypes.c_void_p * R
@@ -163,13 +163,13 @@ def test_peer_allgather_kernel_layout_and_epochs():
         want = torch.stack(msgs, dim=1)  # [rows, R, row_bytes]
         for r in range(R):
             assert torch.equal(dst[r].cpu(), want), (it, r)
-            assert state[r].tolist() == [it + 1, 0]
+            assert state[r].tolist() == [0] + [it + 1] * R
     # a rank missing from the exchange: the others time out and say so instead of hanging
     with torch.cuda.stream(streams[0]):
         assert lib.quest_peer_allgather(src[0].data_ptr(), rows, row_bytes, ps, pf, state[0].data_ptr(), dst[0].data_ptr(),
                                         R, 0, 50, torch.cuda.current_stream().cuda_stream) == 0
     torch.cuda.synchronize()
-    assert state[0].tolist()[1] == 2
+    assert state[0].tolist()[0] == 2
     # argument checks
     assert lib.quest_peer_allgather(src[0].data_ptr(), rows, 40, ps, pf, state[0].data_ptr(), dst[0].data_ptr(), R, 0, 50, 0) == -1
     assert lib.quest_peer_allgather(src[0].data_ptr(), rows, row_bytes, ps, pf, state[0].data_ptr(), dst[0].data_ptr(), 9, 0, 50, 0) == -2
