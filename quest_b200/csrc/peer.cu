@@ -4,8 +4,8 @@
 // profiles/r01_s15_long_context_multi_gpu.md).  Here every rank's kernel
 //   1. stores its message straight into every peer's staging buffer (symmetric memory mapped over NVLink / NVSwitch:
 //      16-byte stores, one CTA per peer -- the message is far below the bandwidth-delay product of a link),
-//   2. publishes it: __threadfence_system by every writer, CTA barrier, then one st.release.sys per peer of this
-//      step's epoch into the peer's flag word for this rank,
+//   2. publishes it: CTA barrier, then one cumulative st.release.sys of this step's epoch into the peer's flag word
+//      for this rank,
 //   3. waits (ld.acquire.sys on its OWN flag words, so the polling never crosses the link) until every rank's epoch
 //      arrived, bounded by a wall-clock limit so that a lost peer is an error code, not a hung GPU,
 //   4. unpacks the staging area into a private, fixed-address buffer in the layout the consumer wants
@@ -18,7 +18,7 @@
 namespace quest {
 
 constexpr int kPeerMax = 8;
-constexpr int kPeerThreads = 1024;
+constexpr int kPeerThreads = 512;
 
 struct PeerTable {
   uint4* staging[kPeerMax];     // rank p's staging area as mapped into this process: [2][world][msg_vecs]
@@ -60,7 +60,8 @@ peer_allgather_kernel(const uint4* __restrict__ src, uint32_t rows, uint32_t row
   // push: my slot in rank p's staging area
   uint4* out = tbl.staging[p] + ((size_t)par * world + rank) * msg_vecs;
   for (uint32_t j = tid; j < msg_vecs; j += kPeerThreads) out[j] = src[j];
-  __threadfence_system();
+  // publish: the CTA barrier orders every thread's stores before thread 0, whose system-scope release store is
+  // cumulative over them (the semaphore pattern: barrier, then one st.release) -- no per-thread fence
   __syncthreads();
   if (tid == 0) {
     st_release_sys(tbl.flags[p] + rank, epoch);

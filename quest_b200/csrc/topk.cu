@@ -212,6 +212,19 @@ static int launch_topk_cluster(const void* scores, const int32_t* in_idx, uint32
   QUEST_RETURN_LAUNCH();
 }
 
+// A cluster pays off while all its CTAs (512 threads, 4 per SM) run in one wave; beyond that the single-CTA rows
+// (1024 threads, 2 per SM) finish sooner (configs[3] on one GPU: 8 x 32 rows).
+static bool topk_cluster_fits(uint32_t rows, uint32_t c) {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  return (uint64_t)rows * c <= (uint64_t)4 * sms;
+}
+
 static bool topk_use_cluster() {
   static int v = -1;
   if (v < 0) {
@@ -228,8 +241,10 @@ int topk_batch(const void* scores, int32_t* out_idx, uint32_t num_heads, uint32_
   if (max_len <= 2048) return launch_topk_fast<16, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
   if (topk_use_cluster()) {
     if (max_len <= 4096) return launch_topk_fast<32, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);  // measured equal
-    if (max_len <= 8192) return launch_topk_cluster<16, 4>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
-    if (max_len <= 16384) return launch_topk_cluster<16, 8>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+    if (max_len > 4096 && max_len <= 8192 && topk_cluster_fits(num_heads * batch, 4))
+      return launch_topk_cluster<16, 4>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
+    if (max_len > 8192 && max_len <= 16384 && topk_cluster_fits(num_heads * batch, 8))
+      return launch_topk_cluster<16, 8>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
   }
   if (max_len <= 4096) return launch_topk_fast<32, 1>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
   if (max_len <= 8192) return launch_topk_fast<32, 2>(scores, nullptr, 0, nullptr, out_idx, num_heads, max_len, k, s, ba, batch);
@@ -278,8 +293,10 @@ extern "C" int quest_topk(const void* scores, const int32_t* in_idx, uint32_t in
   if (!no_fast && len <= 2048) return quest::launch_topk_fast<16, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && quest::topk_use_cluster()) {
     if (len <= 4096) return quest::launch_topk_fast<32, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);  // measured equal
-    if (len <= 8192) return quest::launch_topk_cluster<16, 4>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
-    if (len <= 16384) return quest::launch_topk_cluster<16, 8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+    if (len > 4096 && len <= 8192 && quest::topk_cluster_fits(num_heads, 4))
+      return quest::launch_topk_cluster<16, 4>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
+    if (len > 8192 && len <= 16384 && quest::topk_cluster_fits(num_heads, 8))
+      return quest::launch_topk_cluster<16, 8>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   }
   if (!no_fast && len <= 4096) return quest::launch_topk_fast<32, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 8192) return quest::launch_topk_fast<32, 2>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
