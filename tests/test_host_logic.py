@@ -55,3 +55,35 @@ def test_controller_tables_and_budget():
     assert ic.inference_page_budget == 7 and not ic.need_estimate()
     ic.clean_states()
     assert ic.kv_cache.seqlen == 0
+
+
+def test_argument_checks_of_the_batched_and_peer_entry_points_need_no_gpu():
+    """quest_decode_layer_step_batch / quest_peer_allgather / quest_merge_states reject bad arguments on the host,
+    before any CUDA call (include/quest_b200.h: negative return codes)."""
+    import ctypes
+
+    import quest_b200._kernels as K
+    from quest_b200.parallel import SeqShardedDecode
+    lib = K.load_library()
+    one = ctypes.c_void_p(16)  # any non-null, 16-byte aligned address: never dereferenced on these paths
+    # batched layer step: null records, k = 0, workspace too small
+    args = [one, one, one, one, None, 1, 0, 0, 2048, one, 32 * 2047, one, 127, 32, 32, 128, 16, 4, one, 1 << 20, None]
+    assert lib.quest_decode_layer_step_batch(*args) == -1
+    args[4] = one
+    args[12] = 0
+    assert lib.quest_decode_layer_step_batch(*args) == -1
+    args[12] = 127
+    args[19] = 16
+    assert lib.quest_decode_layer_step_batch(*args) == -3
+    # peer all-gather: row size not a multiple of 16 bytes, world > 8, rank >= world
+    arr = (ctypes.c_void_p * 8)(*[16] * 8)
+    assert lib.quest_peer_allgather(one, 4, 40, arr, arr, one, one, 2, 0, 0, None) == -1
+    assert lib.quest_peer_allgather(one, 4, 48, arr, arr, one, one, 9, 0, 0, None) == -2
+    assert lib.quest_peer_allgather(one, 4, 48, arr, arr, one, one, 2, 2, 0, None) == -2
+    assert lib.quest_peer_staging_bytes(4, 48, 3) == 2 * 3 * 4 * 48
+    # merge of packed records: a stride smaller than one record's o block
+    assert lib.quest_merge_states(one, one, 2, 100, one, None, 32, 128, None) == -1
+    # exchange-area layout of the sequence-sharded step: staging for candidates and records, then the flag words
+    off_rec, off_flags, total = SeqShardedDecode._peer_layout(lib, 32, 128, 511, 8)
+    assert off_rec == 2 * 8 * 32 * 512 * 2 and off_flags >= off_rec + 2 * 8 * (32 * 128 + 32) * 4
+    assert off_flags % 16 == 0 and total >= off_flags + 2 * 8 * 4
