@@ -81,7 +81,7 @@ peer_allgather_kernel(const uint4* __restrict__ src, uint32_t rows, uint32_t row
   const uint4* mine = tbl.staging[rank] + ((size_t)par * world + p) * msg_vecs;
   for (uint32_t j = tid; j < msg_vecs; j += kPeerThreads) {
     const uint32_t row = j / row_vecs, vec = j - row * row_vecs;
-    dst[((size_t)row * world + p) * row_vecs + vec] = mine[j];
+    dst[((size_t)row * world + p) * row_vecs + vec] = __ldcg(mine + j);  // written by another GPU: read at L2, never a stale L1 line
   }
 }
 
