@@ -212,7 +212,7 @@ static int launch_topk_cluster(const void* scores, const int32_t* in_idx, uint32
   QUEST_RETURN_LAUNCH();
 }
 
-// A cluster pays off while all its CTAs (512 threads, 4 per SM) run in one wave; beyond that the single-CTA rows
+// A cluster pays off while all its CTAs (512 threads at 40 registers: 3 per SM) run in one wave; beyond that the single-CTA rows
 // (1024 threads, 2 per SM) finish sooner (configs[3] on one GPU: 8 x 32 rows).
 static bool topk_cluster_fits(uint32_t rows, uint32_t c) {
   static int sms = 0;
@@ -222,7 +222,7 @@ static bool topk_cluster_fits(uint32_t rows, uint32_t c) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (sms <= 0) sms = 148;
   }
-  return (uint64_t)rows * c <= (uint64_t)4 * sms;
+  return (uint64_t)rows * c <= (uint64_t)3 * sms;
 }
 
 static bool topk_use_cluster() {
