@@ -28,6 +28,9 @@ __device__ unsigned long long g_dec_clk[4096 * 8];
 #define D_STAMP(i) do { } while (0)
 #endif
 
+#ifndef QUEST_DEC_MINBLOCKS
+#define QUEST_DEC_MINBLOCKS 7  // resident CTAs per SM the kernel is compiled for (72 registers); 8 = 64 registers, A/B in profiles/
+#endif
 constexpr int kDecThreads = 128;
 constexpr int kDecWarps = kDecThreads / 32;
 constexpr float kNegBig = -1e30f;
@@ -347,7 +350,7 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const float sm_scale_log2 = kLog2e / sqrtf((float)D);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<D, kDecThreads, 7>, (const __half*)q, (__half*)o, lse,
+  cudaError_t e = cudaLaunchKernelEx(&cfg, decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS>, (const __half*)q, (__half*)o, lse,
                                      (const __half*)kv, indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv,
                                      Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba);
   if (e != cudaSuccess) return (int)e;
@@ -374,7 +377,7 @@ extern "C" int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, 
   if (head_dim != 64 && head_dim != 128 && head_dim != 256) return QUEST_ERR_UNSUPPORTED;
   if (num_sms == 0) num_sms = 148;
   const uint32_t total = num_sel_pages + 1;
-  const uint32_t slots = num_sms * 7;  // resident 128-thread CTAs per SM at 72 registers/thread
+  const uint32_t slots = num_sms * QUEST_DEC_MINBLOCKS;  // resident 128-thread CTAs per SM
   // Smallest chunk that keeps every CTA resident in one wave, but at least two items per warp.
   const uint32_t item_tokens = 2 * (32 / (head_dim / 8));
   uint32_t min_ppc = (quest::kDecWarps * item_tokens * 2 + page_size - 1) / page_size;
