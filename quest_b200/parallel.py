@@ -17,7 +17,8 @@ decode_attn.cuh:454-457,1127):
 The module-level functions take torch tensors on the process group's device (CUDA with NCCL; CPU with gloo in the
 tests) and use only torch ops plus the collectives: they state the exchange protocol.  `SeqShardedDecode` is the
 CUDA path of the same protocol: every selection, attention and merge step is a libquest_b200 kernel, the two
-exchanges are one NCCL all-gather each.
+exchanges are one NCCL all-gather each or one quest_peer_allgather kernel each (stores into the peers' symmetric memory over
+NVLink, flag words, bounded wait; csrc/peer.cu).
 """
 import ctypes
 from typing import List, Optional, Sequence, Tuple
@@ -108,7 +109,7 @@ class SeqShardedDecode:
       1. candidates: [append on the last rank] -> quest_estimate over the local pages -> quest_topk keeps the best
          c = min(k, n_local) of each head: scores into this rank's slot of the exchange buffer, LOCAL physical page
          ids kept at home.
-      2. exchange 1 (all-gather of fp16 [Hq, c] scores, ~Hq*c*2 bytes per rank).  Only scores travel: ranks are
+      2. exchange 1 (all-gather of fp16 [Hq, c] scores, ~Hq*c*2 bytes per rank; exchange="nccl" or "peer").  Only scores travel: ranks are
          concatenated in page order and quest_topk breaks ties by input position, so the global selection is the
          single-GPU one bit for bit, on every rank, without positions on the wire.
       3. select: quest_topk over the [Hq, R*c] gathered scores with a payload row that holds this rank's physical

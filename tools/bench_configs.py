@@ -6,8 +6,9 @@
                q heads; no collective on the path.  Strong scaling: total work fixed.
   --config 5   Yarn-Llama2-7B-128K shape (32 heads MHA, D 128), token budget 8192, SEQUENCE sharded: every rank holds
                8192 pages (128K tokens) of one sequence, so R = 8 is the 1M-token context of configs[4]; smaller R run
-               the same per-GPU share of a shorter context (weak scaling).  Two NCCL all-gathers per layer step
-               (quest_b200.parallel.SeqShardedDecode).
+               the same per-GPU share of a shorter context (weak scaling).  Two all-gathers per layer step
+               (quest_b200.parallel.SeqShardedDecode): --exchange nccl | peer (quest_peer_allgather over symmetric memory).
+  --batched G  (config 4) G groups of sequences, each one descriptor-driven batched launch chain (BatchDecodeStep).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/bench_configs.py --config 5
 Prints one JSON line per run on rank 0.  Times are CUDA-event device times, max over ranks; a step walks `--layers`
