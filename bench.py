@@ -168,10 +168,11 @@ class Workload:
             ppc.value = int(os.environ["BENCH_PPC"])
             nch.value = (K_SEL + 1 + ppc.value - 1) // ppc.value
         self.plan = (ppc.value, nch.value)
-        sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
-        # sized for both the stand-alone decode plan and the fused layer-step kernel (2 CTAs/SM shared by the heads)
-        self.ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, max(nch.value, 2 * sms // H)), dtype=torch.uint8,
-                              device=self.dev)
+        # room for the selection's key rows: the layer step runs as two launches (estimate publishing keys and bin totals,
+        # decode selecting its own pages); BENCH_UNFUSED=1 sizes it for the three stand-alone kernels instead (A/B)
+        unfused = os.environ.get("BENCH_UNFUSED", "0") == "1"
+        self.ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, nch.value) if unfused else
+                              lib.quest_step_workspace_bytes(H, D, nch.value, N_SCORED), dtype=torch.uint8, device=self.dev)
         kvi, mi = ic.kv_indices_with_last, ic.metadata_indices
         n_meta = mi.numel()
         kv_last_len, meta_last_len = ic.kv_cache.last_page_len, ic.metadata_cache.last_page_len
@@ -192,7 +193,7 @@ class Workload:
                 calls.append((lib.quest_estimate, (q, s, N_SCORED, mp, mi.data_ptr(), H, H, D, P, 3)))  # QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED
             if "topk" in parts:
                 calls.append((lib.quest_topk, (s, kvi.data_ptr(), 0, None, ti, H, N_SCORED, K_SEL)))
-            if "step" in parts:  # estimate + top-k + decode in one call (one persistent kernel, csrc/fused.cu)
+            if "step" in parts:  # estimate + selection + decode in one call, without the append
                 calls.append((lib.quest_sparse_decode_step, (q, o, kvp, kvi.data_ptr(), N_SCORED, last_idx, kv_last_len, mp,
                                                              mi.data_ptr(), s, ti, K_SEL, H, H, D, P, ppc.value,
                                                              self.ws.data_ptr(), self.ws.numel())))
@@ -288,6 +289,8 @@ def main():
 
     import quest_b200._kernels as K
     lib = K.load_library()  # fails loudly if the CUDA library is missing
+    if os.environ.get("BENCH_UNFUSED", "0") == "1":  # A/B: the three stand-alone kernels behind the same entry points
+        lib.quest_debug_set_option(K.DBG_STEP_UNFUSED, 1)
     wl = Workload(dev, 1234 + rank)
 
     step, launches_per_step = wl.make_raw_step()

@@ -30,6 +30,8 @@ extern "C" {
 #define QUEST_ERR_BAD_ARG (-1)      /* null pointer / zero size / inconsistent sizes            */
 #define QUEST_ERR_UNSUPPORTED (-2)  /* head_dim / group size / length outside the built variants */
 #define QUEST_ERR_WORKSPACE (-3)    /* caller-provided workspace too small                       */
+#define QUEST_ERR_DEVICE (-4)       /* an earlier kernel of this library gave up on a bounded wait: its
+                                       output was not valid (see quest_device_error)             */
 
 /* Library identification: "quest_b200 <version> sm_100a". */
 const char* quest_version(void);
@@ -117,6 +119,13 @@ int quest_decode_plan(uint32_t num_sel_pages, uint32_t num_qo_heads, uint32_t nu
 /* Bytes of workspace for a plan; the workspace must be zero-filled once before first use
  * (the kernel restores its arrival counters to zero). */
 size_t quest_decode_workspace_bytes(uint32_t num_qo_heads, uint32_t head_dim, uint32_t num_chunks);
+/* Workspace for the layer-step entry points below (quest_sparse_decode_step, quest_decode_layer_step,
+ * quest_decode_layer_step_batch): quest_decode_workspace_bytes plus room for the 16-bit score keys of up to
+ * max_scored_pages pages per q head, which lets the step run as TWO launches (the estimate kernel publishes keys and
+ * bin totals, every decode CTA selects its own pages from them: csrc/select.cuh).  With a smaller workspace the same
+ * entry points run the three stand-alone kernels (estimate, top-k, decode); results are identical.  Zero-filled once. */
+size_t quest_step_workspace_bytes(uint32_t num_qo_heads, uint32_t head_dim, uint32_t num_chunks,
+                                  uint32_t max_scored_pages);
 /* q, o: [num_qo_heads, head_dim]; indices: [num_qo_heads, num_sel_pages] page ids with row stride
  * idx_row_stride; the page last_page_idx holding last_page_len tokens is always attended in
  * addition.  lse (fp32 [num_qo_heads], base-2, may be NULL).
@@ -132,7 +141,8 @@ int quest_decode_run(const void* q, void* o, float* lse,
 
 /* ---- fused layer step: estimate -> top-k -> sparse decode ---------------------------------------
  * The three calls QuestAttention.forward makes per layer per token (quest/models/QuestAttention.py:
- * 135-158) behind one entry; kernels are chained with programmatic dependent launch.  scores
+ * 135-158) behind one entry; kernels are chained with programmatic dependent launch, and with a
+ * quest_step_workspace_bytes workspace the top-k runs inside the decode kernel's prologue (2 launches).  scores
  * ([num_qo_heads, len] fp16) and topk_idx ([num_qo_heads, k] int32) are caller-provided
  * intermediates and hold the same values the separate calls would produce.
  * kv_indices: the sequence's page table (device, first `len` entries are the scored pages);
@@ -153,7 +163,8 @@ int quest_sparse_decode_step(const void* q, void* o,
  * and lengths already count it (as for quest_append_decode); kv_last_page_idx = kv_indices[num_kv_pages-1]
  * as a host value (the reference passes it the same way, controller.py:86-87).  k pages are selected among
  * the num_kv_pages-1 full pages (k = 0: attend to the last page only); scores [num_qo_heads, num_kv_pages-1]
- * fp16 and topk_idx [num_qo_heads, k] are outputs.  The append rides on the estimate kernel (3 launches). */
+ * fp16 and topk_idx [num_qo_heads, k] are outputs.  The append rides on the estimate kernel and, given a
+ * quest_step_workspace_bytes workspace, the page selection on the decode kernel: 2 launches (else 3). */
 int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new, void* o,
                             void* kv_data, const int32_t* kv_indices, uint32_t num_kv_pages,
                             uint32_t kv_last_page_idx, uint32_t kv_last_page_len,
@@ -234,6 +245,32 @@ size_t quest_peer_staging_bytes(uint32_t rows, uint32_t row_bytes, uint32_t worl
 int quest_peer_allgather(const void* src, uint32_t rows, uint32_t row_bytes, void* const* peer_staging,
                          void* const* peer_flags, void* state, void* dst, uint32_t world, uint32_t rank,
                          uint32_t timeout_ms, void* stream);
+
+/* ---- device-side failures ------------------------------------------------------------------------------
+ * The tcgen05 prefill kernels and the peer exchange wait on hardware barriers / remote flags with a wall-time
+ * bound (seconds) instead of hanging the GPU.  A kernel whose wait ran out raises a sticky bit in host-mapped
+ * memory; quest_device_error() returns the bits raised so far (a plain host read: no synchronisation, so a
+ * failure becomes visible once the failing kernel has run).  While a class's bit is set the entry points of that
+ * class (quest_prefill; quest_peer_allgather) return QUEST_ERR_DEVICE.  The reference has no counterpart: its
+ * kernels cannot time out (they use no asynchronous barriers), and CUDA launch failures surface as TORCH_CHECK
+ * errors (quest/ops/csrc/page.cu:91-93). */
+#define QUEST_DEVERR_PREFILL 1u
+#define QUEST_DEVERR_PEER 2u
+#define QUEST_DEVERR_COUNT 2
+uint32_t quest_device_error(void);
+void quest_device_error_clear(void);
+
+/* ---- explicit test / A-B switches (process-wide; nothing in the library reads the environment) -----------
+ * quest_debug_set_option(option, value) returns the previous value; all options default to 0 = product path. */
+#define QUEST_DBG_PDL_OFF 0          /* 1: launch without programmatic dependent launch                       */
+#define QUEST_DBG_EST_ROWS 1         /* 1: generic estimate kernel on shapes the tile kernel takes             */
+#define QUEST_DBG_PREFILL_IMPL 2     /* 0: by shape; 1: SIMT; 2: cp.async + tcgen05; 3: TMA + tcgen05 only     */
+#define QUEST_DBG_PREFILL_P_SMEM 3   /* 1: TMA prefill hands P to the PV MMA through shared memory             */
+#define QUEST_DBG_TOPK_NO_CLUSTER 4  /* 1: one CTA per top-k row for every length                              */
+#define QUEST_DBG_TOPK_GENERIC 5     /* 1: shared-memory-key top-k kernel for every length                     */
+#define QUEST_DBG_STEP_UNFUSED 6     /* 1: layer step as the stand-alone estimate / top-k / decode kernels     */
+#define QUEST_DBG_COUNT 8
+int quest_debug_set_option(int option, int value);
 
 /* Counters for bench/tests: number of kernels this library has launched since load / last reset. */
 uint64_t quest_launch_count(void);

@@ -1,39 +1,106 @@
-// Library-level entry points: identification, launch counter, and the fused layer step that chains
-// estimate -> top-k -> sparse decode with programmatic dependent launch (one call per layer per token;
-// reference call sites quest/models/QuestAttention.py:135-158).
+// Library-level entry points: identification, launch counter, device-error words, test switches, and the layer step
+// that chains estimate -> (page selection inside) sparse decode with programmatic dependent launch (one call per
+// layer per token; reference call sites quest/models/QuestAttention.py:135-158).
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
+#include "select.cuh"
 
 namespace quest {
 unsigned long long g_launch_count = 0;
-int launch_fused_step(const void* q, void* o, const void* kv_data, const int32_t* kv_indices, uint32_t len,
-                      uint32_t last_page_idx, uint32_t last_page_len, const void* meta_data,
-                      const int32_t* meta_indices, void* scores, int32_t* topk_idx, uint32_t k, uint32_t Hq,
-                      uint32_t Hkv, uint32_t D, uint32_t P, void* workspace, size_t workspace_bytes, uint32_t flags,
-                      cudaStream_t stream);  // fused.cu
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
-                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba = BatchArgs{},
-                      uint32_t batch = 1);  // estimate.cu
+                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba, uint32_t batch,
+                      const SelOut& so);  // estimate.cu
 int topk_batch(const void* scores, int32_t* out_idx, uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba,
                uint32_t batch, cudaStream_t s);  // topk.cu
 int decode_batch(const void* q, void* o, const int32_t* indices, uint32_t n_sel, uint32_t Hq, uint32_t Hkv, uint32_t D,
-                 uint32_t P, uint32_t ppc, void* ws, const BatchArgs& ba, uint32_t batch, cudaStream_t s);  // decode.cu
-int pdl_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("QUEST_PDL");
-    v = (e && e[0] == '0') ? 0 : 1;
-  }
-  return v;
+                 uint32_t P, uint32_t ppc, void* ws, const BatchArgs& ba, uint32_t batch, cudaStream_t s,
+                 uint32_t key_stride);  // decode.cu
+int decode_select(const void* q, void* o, const void* kv, int32_t* topk_idx, uint32_t k, const int32_t* kv_indices,
+                  uint32_t len, uint32_t last_page_idx, uint32_t last_page_len, uint32_t Hq, uint32_t Hkv, uint32_t D,
+                  uint32_t P, uint32_t ppc, void* ws, uint32_t key_stride, cudaStream_t s);  // decode.cu
+constexpr uint32_t kDecodeThreads = 128;  // == kDecThreads (decode.cu): the selection's key rows are laid out for it
+
+static int g_debug_options[QUEST_DBG_COUNT] = {};
+int debug_option(int option) { return (option >= 0 && option < QUEST_DBG_COUNT) ? g_debug_options[option] : 0; }
+
+// ---- sticky device-error words: mapped pinned host memory, so the host reads them without touching the device
+static unsigned int* g_err_host = nullptr;
+static unsigned int* g_err_dev = nullptr;
+static std::once_flag g_err_once;
+unsigned int* device_error_word() {
+  std::call_once(g_err_once, [] {
+    void* h = nullptr;
+    if (cudaHostAlloc(&h, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return;
+    }
+    for (int i = 0; i < 16; ++i) reinterpret_cast<volatile unsigned int*>(h)[i] = 0u;
+    void* d = nullptr;
+    if (cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) {
+      (void)cudaGetLastError();
+      cudaFreeHost(h);
+      return;
+    }
+    g_err_host = reinterpret_cast<unsigned int*>(h);
+    g_err_dev = reinterpret_cast<unsigned int*>(d);
+  });
+  return g_err_dev;
 }
+unsigned int device_error_peek() {
+  if (!g_err_host) return 0u;
+  unsigned int bits = 0;
+  for (int i = 0; i < QUEST_DEVERR_COUNT; ++i)
+    if (reinterpret_cast<volatile unsigned int*>(g_err_host)[i]) bits |= 1u << i;
+  return bits;
+}
+}  // namespace quest
+
+extern "C" uint32_t quest_device_error(void) {
+  quest::device_error_word();  // allocates on first use (call once at load time, outside any stream capture)
+  return quest::device_error_peek();
+}
+extern "C" void quest_device_error_clear(void) {
+  if (quest::g_err_host)
+    for (int i = 0; i < QUEST_DEVERR_COUNT; ++i) reinterpret_cast<volatile unsigned int*>(quest::g_err_host)[i] = 0u;
+}
+extern "C" int quest_debug_set_option(int option, int value) {
+  if (option < 0 || option >= QUEST_DBG_COUNT) return QUEST_ERR_BAD_ARG;
+  const int old = quest::g_debug_options[option];
+  quest::g_debug_options[option] = value;
+  return old;
 }
 
 extern "C" const char* quest_version(void) { return "quest_b200 0.1.0 sm_100a"; }
 extern "C" uint64_t quest_launch_count(void) { return quest::g_launch_count; }
 extern "C" void quest_launch_count_reset(void) { quest::g_launch_count = 0; }
 
+namespace quest {
+// estimate (optionally carrying the append) -> decode that selects its own pages.  QUEST_ERR_UNSUPPORTED: nothing was
+// launched and the caller takes the three stand-alone kernels.
+static int fused_step(const void* q, void* o, const void* kv_data, const int32_t* kv_indices, uint32_t len,
+                      uint32_t last_page_idx, uint32_t last_page_len, const void* meta_data, const int32_t* meta_indices,
+                      void* scores, int32_t* topk_idx, uint32_t k, uint32_t Hq, uint32_t Hkv, uint32_t D, uint32_t P,
+                      uint32_t ppc, void* workspace, size_t workspace_bytes, const AppendArgs& ap, cudaStream_t s) {
+  if (k == 0 || len == 0 || len > kSelMaxLen || !workspace || debug_option(QUEST_DBG_STEP_UNFUSED)) return QUEST_ERR_UNSUPPORTED;
+  const uint32_t nchunks = (k + 1 + ppc - 1) / ppc;
+  if (workspace_bytes < quest_step_workspace_bytes(Hq, D, nchunks, len)) return QUEST_ERR_UNSUPPORTED;
+  const uint32_t key_stride = sel_key_stride(len, kDecodeThreads);
+  const SelOut so = {reinterpret_cast<uint8_t*>(workspace), ws_hist_off(Hq), ws_keys_off(Hq, D, nchunks), key_stride};
+  int rc = estimate_dispatch(q, scores, len, meta_data, meta_indices, Hq, Hkv, D, P, QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED,
+                             ap, s, BatchArgs{}, 1, so);
+  if (rc) return rc;
+  return decode_select(q, o, kv_data, topk_idx, k, kv_indices, len, last_page_idx, last_page_len, Hq, Hkv, D, P, ppc, workspace,
+                       key_stride, s);
+}
+}  // namespace quest
+
+// estimate + page selection + sparse decode without the append (the three calls QuestAttention.forward makes after
+// append_kv, quest/models/QuestAttention.py:135-158): two launches when the workspace has room for the selection's
+// key rows (quest_step_workspace_bytes), else the three stand-alone kernels.
 extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_data, const int32_t* kv_indices,
                                         uint32_t len, uint32_t last_page_idx, uint32_t last_page_len,
                                         const void* meta_data, const int32_t* meta_indices, void* scores,
@@ -41,12 +108,12 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
                                         uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
                                         uint32_t pages_per_chunk, void* workspace, size_t workspace_bytes,
                                         void* stream) {
-  if (!kv_indices || !scores || !topk_idx) return QUEST_ERR_BAD_ARG;
+  if (!q || !o || !kv_data || !kv_indices || !meta_data || !meta_indices || !scores || !topk_idx) return QUEST_ERR_BAD_ARG;
+  if (!num_qo_heads || !num_kv_heads || !page_size || !pages_per_chunk || num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
   if (k > len) return QUEST_ERR_BAD_ARG;
-  // one persistent kernel when the shape allows it (fused.cu), else the three stand-alone kernels
-  int rc = quest::launch_fused_step(q, o, kv_data, kv_indices, len, last_page_idx, last_page_len, meta_data, meta_indices,
-                                    scores, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, workspace,
-                                    workspace_bytes, QUEST_EST_META_ORDERED, (cudaStream_t)stream);
+  int rc = quest::fused_step(q, o, kv_data, kv_indices, len, last_page_idx, last_page_len, meta_data, meta_indices, scores,
+                             topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
+                             workspace_bytes, quest::AppendArgs{}, (cudaStream_t)stream);
   if (rc != QUEST_ERR_UNSUPPORTED) return rc;
   rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                           QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, stream);
@@ -59,8 +126,8 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
 }
 
 // One decode step of one layer: append_kv + estimate + top-k + sparse decode (the four calls of
-// quest/models/QuestAttention.py:100-150 in the reference).  The append rides on the estimate kernel's first CTA, so
-// the step is three launches.
+// quest/models/QuestAttention.py:100-150 in the reference).  The append rides on the estimate kernel's last CTA and the
+// page selection runs in the decode kernel's prologue, so the step is two launches.
 extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new, void* o, void* kv_data,
                                        const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_idx,
                                        uint32_t kv_last_page_len, void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
@@ -69,7 +136,7 @@ extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const v
                                        uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
                                        size_t workspace_bytes, void* stream) {
   if (!q || !k_new || !v_new || !o || !kv_data || !kv_indices || !meta_data || !meta_indices) return QUEST_ERR_BAD_ARG;
-  if (!num_kv_pages || !num_meta_pages || !num_qo_heads || !num_kv_heads || !page_size) return QUEST_ERR_BAD_ARG;
+  if (!num_kv_pages || !num_meta_pages || !num_qo_heads || !num_kv_heads || !page_size || !pages_per_chunk) return QUEST_ERR_BAD_ARG;
   if (num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
   if (kv_last_page_len < 1 || kv_last_page_len > page_size || meta_last_page_len < 1 || meta_last_page_len > page_size)
     return QUEST_ERR_BAD_ARG;
@@ -85,8 +152,13 @@ extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const v
     rc = quest_append_decode(k_new, v_new, kv_data, kv_indices, num_kv_pages, kv_last_page_len, meta_data, meta_indices,
                              num_meta_pages, meta_last_page_len, num_kv_heads, head_dim, page_size, stream);
   } else {
+    rc = quest::fused_step(q, o, kv_data, kv_indices, len, kv_last_page_idx, kv_last_page_len, meta_data, meta_indices, scores,
+                           topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
+                           workspace_bytes, ap, (cudaStream_t)stream);
+    if (rc != QUEST_ERR_UNSUPPORTED) return rc;
     rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                  QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream);
+                                  QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream, quest::BatchArgs{}, 1,
+                                  quest::SelOut{});
     if (rc) return rc;
     // payload ids = the sequence's page table, shared by all heads (row stride 0)
     rc = quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
@@ -117,11 +189,25 @@ extern "C" int quest_decode_layer_step_batch(const void* q, const void* k_new, c
   // the append rides on the estimate launch; its pointers and lengths are taken from the records inside the kernel
   quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, nullptr, nullptr, nullptr, 0, 0, 0, 0};
   cudaStream_t s = (cudaStream_t)stream;
+  const uint32_t flags = QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED;
+  // two launches (selection inside the decode kernel) when every sequence's workspace block has room for its key rows
+  if (max_len <= quest::kSelMaxLen && !quest::debug_option(QUEST_DBG_STEP_UNFUSED) &&
+      workspace_seq_bytes >= quest_step_workspace_bytes(num_qo_heads, head_dim, nchunks, max_len)) {
+    const uint32_t key_stride = quest::sel_key_stride(max_len, quest::kDecodeThreads);
+    const quest::SelOut so = {reinterpret_cast<uint8_t*>(workspace), quest::ws_hist_off(num_qo_heads),
+                              quest::ws_keys_off(num_qo_heads, head_dim, nchunks), key_stride};
+    const int rc = quest::estimate_dispatch(q, scores, max_len, nullptr, nullptr, num_qo_heads, num_kv_heads, head_dim, page_size,
+                                            flags, ap, s, ba, batch, so);
+    if (rc == QUEST_OK)
+      return quest::decode_batch(q, o, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
+                                 ba, batch, s, key_stride);
+    if (rc != QUEST_ERR_UNSUPPORTED) return rc;
+  }
   int rc = quest::estimate_dispatch(q, scores, max_len, nullptr, nullptr, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                    QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, s, ba, batch);
+                                    flags, ap, s, ba, batch, quest::SelOut{});
   if (rc) return rc;
   rc = quest::topk_batch(scores, topk_idx, num_qo_heads, max_len, k, ba, batch, s);
   if (rc) return rc;
   return quest::decode_batch(q, o, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
-                             ba, batch, s);
+                             ba, batch, s, 0);
 }

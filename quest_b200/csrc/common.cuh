@@ -24,7 +24,21 @@
 namespace quest {
 
 extern unsigned long long g_launch_count;  // defined in capi.cu
-int pdl_enabled();  // 1 unless QUEST_PDL=0 in the environment (capi.cu); programmatic dependent launch attribute
+int debug_option(int option);  // quest_debug_set_option (capi.cu): explicit test / A-B switches, never the environment
+inline int pdl_enabled() { return debug_option(QUEST_DBG_PDL_OFF) == 0; }  // programmatic dependent launch attribute
+
+// Sticky, host-visible error words in mapped pinned memory (capi.cu).  A kernel that gives up on a bounded wait stores
+// into its class's word; every later quest_* entry point that depends on that class returns QUEST_ERR_DEVICE until
+// quest_device_error_clear(), so corrupt data is never handed back silently.
+unsigned int* device_error_word();  // device-visible pointer to QUEST_DEVERR_COUNT words (UVA: valid on every GPU)
+unsigned int device_error_peek();   // OR of the QUEST_DEVERR_* bits raised so far; a host read, no synchronisation
+#ifdef __CUDACC__
+__device__ __forceinline__ void device_error_raise(unsigned int* words, unsigned int bit) {
+  if (words == nullptr) return;
+  *reinterpret_cast<volatile unsigned int*>(words + (31 - __clz(bit))) = 1u;
+  __threadfence_system();
+}
+#endif
 
 // 16-byte vector of 8 halves: the reference's vec_t<half, 8> (vec_size = max(16/sizeof(half), D/32)).
 struct alignas(16) H8 {
@@ -166,20 +180,26 @@ struct BatchArgs {
 constexpr float kLog2e = 1.44269504088896340736f;
 
 // Decode workspace layout (caller-owned bytes, zero-filled once when allocated):
-//   [0, 4096)              sync words of the fused layer-step kernel (self-resetting)
-//   [4096, 4096 + 4*Hq)    one merge ticket per q head (self-resetting)
-//   ws_md_off(Hq)          fp32 (m, d) pairs [Hq][nchunks]
-//   ws_o_off(Hq, nchunks)  fp32 partial outputs [Hq][nchunks][D]
+//   [0, 4096)                   reserved (zero)
+//   [4096, 4096 + 4*Hq)         one merge ticket per q head (self-resetting)
+//   ws_hist_off(Hq)             bin totals of the in-decode page selection, 4 KB per q head (select.cuh; self-resetting)
+//   ws_md_off(Hq)               fp32 (m, d) pairs [Hq][nchunks]
+//   ws_o_off(Hq, nchunks)       fp32 partial outputs [Hq][nchunks][D]
+//   ws_keys_off(Hq, D, nchunks) = quest_decode_workspace_bytes: the layer step's 16-bit score keys [Hq][key_stride]
+//                               follow (quest_step_workspace_bytes)
 // The zero-state words sit at fixed offsets so that launches with different chunk counts can share a workspace.
 constexpr size_t kWsSyncBytes = 4096;
+constexpr size_t kWsHistBytesPerHead = 4096;  // == kSelHistBytes (select.cuh)
 __host__ __device__ inline size_t ws_ticket_off() { return kWsSyncBytes; }
-__host__ __device__ inline size_t ws_md_off(uint32_t Hq) { return (kWsSyncBytes + (size_t)Hq * 4 + 255) & ~(size_t)255; }
+__host__ __device__ inline size_t ws_hist_off(uint32_t Hq) { return (kWsSyncBytes + (size_t)Hq * 4 + 255) & ~(size_t)255; }
+__host__ __device__ inline size_t ws_md_off(uint32_t Hq) { return ws_hist_off(Hq) + (size_t)Hq * kWsHistBytesPerHead; }
 __host__ __device__ inline size_t ws_o_off(uint32_t Hq, uint32_t nchunks) {
   return (ws_md_off(Hq) + (size_t)Hq * nchunks * 2 * sizeof(float) + 255) & ~(size_t)255;
 }
-__host__ __device__ inline size_t ws_bytes(uint32_t Hq, uint32_t D, uint32_t nchunks) {
-  return ws_o_off(Hq, nchunks) + (size_t)Hq * nchunks * D * sizeof(float);
+__host__ __device__ inline size_t ws_keys_off(uint32_t Hq, uint32_t D, uint32_t nchunks) {
+  return (ws_o_off(Hq, nchunks) + (size_t)Hq * nchunks * D * sizeof(float) + 255) & ~(size_t)255;
 }
+__host__ __device__ inline size_t ws_bytes(uint32_t Hq, uint32_t D, uint32_t nchunks) { return ws_keys_off(Hq, D, nchunks); }
 
 }  // namespace quest
 

@@ -8,7 +8,6 @@
 //                        cp.async (double buffered), S = Q K^T and O += P V run as tcgen05.mma with the
 //                        accumulators in TMEM, the online softmax reads S with tcgen05.ld, one row per thread.
 //   prefill_simt_kernel  CUDA cores, 16 queries per CTA: short query chunks (qo_len <= 16) and the A/B baseline.
-#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -146,7 +145,8 @@ template <int D>
 __global__ void __launch_bounds__(kUmThreads, 2)
 prefill_umma_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32_t qo_len,
                     const __half* __restrict__ kv, const int32_t* __restrict__ kv_indices, uint32_t kv_len,
-                    int causal, uint32_t Hq, uint32_t Hkv, uint32_t P, float sm_scale_log2) {
+                    int causal, uint32_t Hq, uint32_t Hkv, uint32_t P, float sm_scale_log2,
+                    unsigned int* __restrict__ err_word) {
   using namespace umma;
   using L = UmSmem<D>;
   extern __shared__ __align__(1024) uint8_t um_smem[];
@@ -317,7 +317,10 @@ prefill_umma_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint32
       }
     }
   }
-  if (!ok) atomicOr(&g_pf_timeouts, 1u);
+  if (!ok) {  // a wait ran out: o is not valid.  Sticky, host-visible (quest_device_error)
+    atomicOr(&g_pf_timeouts, 1u);
+    device_error_raise(err_word, QUEST_DEVERR_PREFILL);
+  }
   fence_before_sync();
   __syncthreads();
   if (warp == 0) tmem_free<kUmTmemCols>(tbase);
@@ -329,13 +332,9 @@ int launch_prefill_tma(const __half* q, __half* o, uint32_t qo_len, const __half
                        float sc, cudaStream_t s);
 unsigned int prefill_tma_timeouts();
 
-// QUEST_PF_IMPL (test / A-B hook, read per call): unset = by shape (TMA kernel where it applies, else the cp.async
-// tcgen05 kernel; SIMT for qo_len <= 16), "simt" = 1, "umma" = 2 (cp.async tcgen05 kernel), "tma" = 3 (no fallback)
-static int prefill_impl_override() {
-  const char* e = std::getenv("QUEST_PF_IMPL");
-  if (!e) return 0;
-  return !std::strcmp(e, "simt") ? 1 : !std::strcmp(e, "umma") ? 2 : !std::strcmp(e, "tma") ? 3 : 0;
-}
+// QUEST_DBG_PREFILL_IMPL (quest_debug_set_option; test / A-B hook): 0 = by shape (TMA kernel where it applies, else the
+// cp.async tcgen05 kernel; SIMT for qo_len <= 16), 1 = SIMT, 2 = cp.async tcgen05 kernel, 3 = TMA kernel (no fallback)
+static int prefill_impl_override() { return debug_option(QUEST_DBG_PREFILL_IMPL); }
 
 template <int D>
 static cudaError_t launch_prefill_umma(const __half* q, __half* o, uint32_t qo_len, const __half* kv,
@@ -346,7 +345,7 @@ static cudaError_t launch_prefill_umma(const __half* q, __half* o, uint32_t qo_l
   if (attr != cudaSuccess) return attr;
   dim3 grid((qo_len + kUmBQ - 1) / kUmBQ, Hq);
   prefill_umma_kernel<D><<<grid, kUmThreads, UmSmem<D>::total, s>>>(q, o, qo_len, kv, kv_indices, kv_len, causal, Hq, Hkv,
-                                                                    P, sc);
+                                                                    P, sc, device_error_word());
   return cudaSuccess;
 }
 
@@ -369,6 +368,7 @@ extern "C" int quest_prefill(const void* q, void* o, uint32_t qo_len, const void
   const uint64_t kv_len64 = (uint64_t)(num_kv_pages - 1) * page_size + kv_last_page_len;
   if (qo_len == 0) return QUEST_OK;
   if (qo_len > kv_len64) return QUEST_ERR_BAD_ARG;
+  if (quest::device_error_peek() & QUEST_DEVERR_PREFILL) return QUEST_ERR_DEVICE;  // an earlier prefill gave up on a wait
   const uint32_t kv_len = (uint32_t)kv_len64;
   const float sc = quest::kLog2e / sqrtf((float)head_dim);
   cudaStream_t s = (cudaStream_t)stream;

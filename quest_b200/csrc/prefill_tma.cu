@@ -18,8 +18,6 @@
 //     packed FFMA2 / FADD2 for the scale-subtract and the row sum.
 #include <cuda.h>
 
-#include <cstdlib>
-
 #include "common.cuh"
 #include "umma.cuh"
 
@@ -50,10 +48,12 @@ struct TmSmem {
   static constexpr uint32_t kTile = (D / 64) * kTmBK * 128;
   static constexpr uint32_t kP = kTmBQ * 128;
   static constexpr uint32_t off_q = 0, off_k = kQ, off_v = off_k + 2 * kTile, off_p = off_v + 2 * kTile;
-  static constexpr uint32_t off_bar = off_p + kP, total = off_bar + 128;
+  static constexpr uint32_t off_bar = off_p + kP, total = off_bar + 192;  // 16 barriers, TMEM slot, abort flag
 };
-// barrier slots (8 bytes each) from off_bar
-enum : uint32_t { kBarQ = 0, kBarK = 1, kBarV = 3, kBarS = 5, kBarPV = 7, kBarVFree = 9, kBarSFree = 11, kBarP = 13, kNumBars = 15 };
+// barrier slots (8 bytes each) from off_bar.  kBarPV completes once per tile and may only be waited on by a thread
+// that is at most ONE phase behind it (the parity test cannot tell phase c from phase c+2); kBarDone is the one-shot
+// "every PV has completed" signal the epilogue waits on, whatever the skew.
+enum : uint32_t { kBarQ = 0, kBarK = 1, kBarV = 3, kBarS = 5, kBarPV = 7, kBarVFree = 9, kBarSFree = 11, kBarP = 13, kBarDone = 15, kNumBars = 16 };
 
 // Page id of this lane's box of the 64-token tile at t0 (lane l < boxes per tile = 64 / min(P,64)), or -1 when the
 // tile has no such page.  Loaded one or more iterations before it is used, so the latency is off the issue path.
@@ -86,7 +86,8 @@ template <int D, bool kPTmem>
 __global__ void __launch_bounds__(kTmThreads, 2)
 prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_constant__ CUtensorMap kvmap,
                    __half* __restrict__ o, uint32_t qo_len, const int32_t* __restrict__ kv_indices, uint32_t num_pages,
-                   uint32_t kv_len, int causal, uint32_t Hq, uint32_t Hkv, uint32_t p_shift, float sm_scale_log2) {
+                   uint32_t kv_len, int causal, uint32_t Hq, uint32_t Hkv, uint32_t p_shift, float sm_scale_log2,
+                   unsigned int* __restrict__ err_word) {
   using namespace umma;
   using L = TmSmem<D>;
   extern __shared__ __align__(1024) uint8_t tm_smem[];
@@ -114,7 +115,7 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
 
   if (warp == 4) tmem_alloc<kTmTmemCols>(smem_u32(tmem_slot));
   if (tid == 0) {
-    for (uint32_t i = 0; i < kNumBars; ++i) mbar_init(bar(i), i >= kBarSFree ? 128u : 1u);
+    for (uint32_t i = 0; i < kNumBars; ++i) mbar_init(bar(i), (i >= kBarSFree && i < kBarDone) ? 128u : 1u);
     *abort_flag = (sbase & 1023u) ? 1u : 0u;
     mbar_init_fence();
   }
@@ -148,6 +149,7 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
         mma_commit(bar(kBarVFree + b));  // V loader: the stage is free
         PF_STAMP(j, 5);
       }
+      mma_commit(bar(kBarDone));  // one-shot: O holds every tile
     }
     __syncwarp();
   } else if (warp == 7) {
@@ -324,7 +326,9 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
       if (tid == 0) PF_STAMP(j, 12);
     }
 
-    wait(kBarPV, (ntiles - 1) & 1);
+    // NOT kBarPV: with P in tensor memory this warp may not have waited on it for many tiles, the barrier can be
+    // two phases behind (only PV(ntiles-3) is implied by S(ntiles-1)) and its parity then reads as "done"
+    wait(kBarDone, 0);
     fence_after_sync();
     __syncwarp();
     const float inv = dsum > 0.f ? __fdividef(1.f, dsum) : 0.f;
@@ -350,7 +354,10 @@ prefill_tma_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_consta
   }
   fence_before_sync();
   __syncthreads();
-  if (tid == 0 && *abort_flag) atomicOr(&g_pf_tma_timeouts, 1u);
+  if (tid == 0 && *abort_flag) {  // a wait ran out: o is not valid.  Sticky, host-visible (quest_device_error)
+    atomicOr(&g_pf_tma_timeouts, 1u);
+    device_error_raise(err_word, QUEST_DEVERR_PREFILL);
+  }
   if (warp == 4) tmem_free<kTmTmemCols>(tbase);  // the allocating warp frees
 }
 
@@ -370,10 +377,7 @@ static EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-static bool p_in_tmem() {  // QUEST_PF_PTMEM=0: P through shared memory (A/B hook, read per call)
-  const char* e = std::getenv("QUEST_PF_PTMEM");
-  return !(e && e[0] == '0');
-}
+static bool p_in_tmem() { return debug_option(QUEST_DBG_PREFILL_P_SMEM) == 0; }  // test / A-B hook: P through shared memory
 
 template <int D, bool kPTmem>
 static int launch_tma(const __half* q, __half* o, uint32_t qo_len, const __half* kv, const int32_t* kv_indices,
@@ -409,7 +413,7 @@ static int launch_tma(const __half* q, __half* o, uint32_t qo_len, const __half*
   }
   dim3 grid((qo_len + kTmBQ - 1) / kTmBQ, Hq);
   prefill_tma_kernel<D, kPTmem><<<grid, kTmThreads, TmSmem<D>::total, s>>>(qmap, kvmap, o, qo_len, kv_indices, num_pages, kv_len, causal, Hq,
-                                                                  Hkv, p_shift, sc);
+                                                                  Hkv, p_shift, sc, device_error_word());
   return QUEST_OK;
 }
 

@@ -225,14 +225,7 @@ static bool topk_cluster_fits(uint32_t rows, uint32_t c) {
   return (uint64_t)rows * c <= (uint64_t)3 * sms;
 }
 
-static bool topk_use_cluster() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("QUEST_TOPK_CLUSTER");  // A/B hook: 0 = one CTA per row for every length
-    v = (e && e[0] == '0') ? 0 : 1;
-  }
-  return v != 0;
-}
+static bool topk_use_cluster() { return debug_option(QUEST_DBG_TOPK_NO_CLUSTER) == 0; }  // A/B hook
 
 // descriptor mode (quest_decode_layer_step_batch): max_len bounds every sequence's row; fast variants only
 int topk_batch(const void* scores, int32_t* out_idx, uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba,
@@ -288,7 +281,7 @@ extern "C" int quest_topk(const void* scores, const int32_t* in_idx, uint32_t in
   if (k > len) return QUEST_ERR_BAD_ARG;
   if (len > quest::kTopkMaxLen) return QUEST_ERR_UNSUPPORTED;
   cudaStream_t s = (cudaStream_t)stream;
-  static const bool no_fast = getenv("QUEST_TOPK_GENERIC") != nullptr;  // test hook: force the generic kernels
+  const bool no_fast = quest::debug_option(QUEST_DBG_TOPK_GENERIC) != 0;  // test hook: force the generic kernels
   if (!no_fast && len <= 1024) return quest::launch_topk_fast<8, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 2048) return quest::launch_topk_fast<16, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && quest::topk_use_cluster()) {

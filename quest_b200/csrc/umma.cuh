@@ -109,7 +109,8 @@ __device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier
 // Waits for the phase with the given parity to complete.  The spin is bounded (a lost arrival shows up as a wrong
 // result and a set bit in *timeouts, not as a hung GPU); returns false on timeout.
 __device__ __forceinline__ bool mbar_wait(uint32_t bar_saddr, uint32_t parity) {
-  for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
+  unsigned long long t0 = 0;
+  for (uint32_t spin = 0;; ++spin) {
     uint32_t done;
     asm volatile(
         "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
@@ -117,8 +118,13 @@ __device__ __forceinline__ bool mbar_wait(uint32_t bar_saddr, uint32_t parity) {
         : "r"(bar_saddr), "r"(parity)
         : "memory");
     if (done) return true;
+    if ((spin & 255u) == 255u) {  // bounded by wall time (4 s of %globaltimer), not by a poll count
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000ull) return false;
+    }
   }
-  return false;
 }
 
 // ---- cp.async (16 bytes, L2 only); src_bytes == 0 writes zeros without touching global memory
@@ -139,8 +145,17 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar_saddr) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar_saddr, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar_saddr), "r"(bytes) : "memory");
 }
+// Bounded by wall time (%globaltimer, kWaitTimeoutNs), not by a poll count: under time slicing, MPS or a profiler's
+// replay a legitimate wait can take many polls.
+constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ bool mbar_wait_abortable(uint32_t bar_saddr, uint32_t parity, volatile uint32_t* abort_flag) {
-  for (uint32_t spin = 0; spin < (1u << 20); ++spin) {
+  unsigned long long t0 = 0;
+  for (uint32_t spin = 0;; ++spin) {
     uint32_t done;
     asm volatile(
         "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
@@ -148,7 +163,12 @@ __device__ __forceinline__ bool mbar_wait_abortable(uint32_t bar_saddr, uint32_t
         : "r"(bar_saddr), "r"(parity)
         : "memory");
     if (done) return true;
-    if ((spin & 63u) == 63u && *abort_flag) return true;
+    if ((spin & 63u) == 63u) {
+      if (*abort_flag) return true;
+      const unsigned long long now = global_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > kWaitTimeoutNs) break;
+    }
   }
   *abort_flag = 1u;
   return false;  // this wait is the one that ran out

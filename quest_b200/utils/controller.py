@@ -38,8 +38,8 @@ class InferenceController:
         # device-resident page tables (capacity entries) + how many entries are valid on the device
         self._kv_table = torch.zeros(self.kv_cache.pool.capacity, dtype=torch.int32, device=device)
         self._meta_table = torch.zeros(self.metadata_cache.pool.capacity, dtype=torch.int32, device=device)
-        self._kv_synced = 0
-        self._meta_synced = 0
+        self._kv_synced = (0, 0)    # (valid entries on the device, generation of the host list they mirror)
+        self._meta_synced = (0, 0)
         self._indptr_cache = {}
         self._topk_cache = {}
         self._step = None  # bound arguments of decode_layer_step, valid until the next begin_forward
@@ -69,11 +69,18 @@ class InferenceController:
         appended_new_pages = self.kv_cache.append_seq(seq_len)
         _ = self.metadata_cache.append_seq(appended_new_pages)
 
-    def _sync_table(self, table, ids, synced):
-        n = len(ids)
-        if n > synced:
-            table[synced:n] = torch.tensor(ids[synced:n], dtype=torch.int32)
-        return n
+    def _sync_table(self, table, cache, synced):
+        """Copies the entries the device does not have yet.  The list only grows between two release() calls; a
+        release (directly on the cache or through clean_states) bumps the cache's generation, and a list that is
+        shorter than what was copied can only mean the same, so both resynchronise from entry 0 (the reference
+        rebuilds the tensors on every begin_forward, controller.py:84-95)."""
+        ids = cache.indicies
+        n, (have, gen) = len(ids), synced
+        if gen != cache.generation or n < have:
+            have = 0
+        if n > have:
+            table[have:n] = torch.tensor(ids[have:n], dtype=torch.int32)
+        return (n, cache.generation)
 
     def _indptr(self, n):
         t = self._indptr_cache.get(n)
@@ -88,8 +95,8 @@ class InferenceController:
         """Bring the device page tables up to date with the host lists (one small H2D copy per newly allocated page)
         and refresh the views / host ids derived from them."""
         kv_ids, meta_ids = self.kv_cache.indicies, self.metadata_cache.indicies
-        self._kv_synced = self._sync_table(self._kv_table, kv_ids, self._kv_synced)
-        self._meta_synced = self._sync_table(self._meta_table, meta_ids, self._meta_synced)
+        self._kv_synced = self._sync_table(self._kv_table, self.kv_cache, self._kv_synced)
+        self._meta_synced = self._sync_table(self._meta_table, self.metadata_cache, self._meta_synced)
         self.kv_indptr_for_append = self._indptr(len(kv_ids))
         self.metadata_indptr_for_append = self._indptr(len(meta_ids))
         self.kv_last_page_idx = kv_ids[-1]
@@ -155,5 +162,3 @@ class InferenceController:
     def clean_states(self):
         self.kv_cache.release()
         self.metadata_cache.release()
-        self._kv_synced = 0
-        self._meta_synced = 0

@@ -70,6 +70,7 @@ class KvCache:
                             device=device)
         self._indicies = []
         self._seqlen = 0
+        self.generation = 0  # bumped by release(): device copies of the page table made before it are stale
 
     @property
     def pool(self) -> KvPool:
@@ -109,3 +110,4 @@ class KvCache:
         for idx in self._indicies:
             self._pool.free_block(idx)
         self._indicies.clear()
+        self.generation += 1

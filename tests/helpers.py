@@ -49,3 +49,25 @@ class OracleCache:
     def append(self, k, v):
         self.reserve(k.shape[0])
         orc.append_paged_kv(self.kv_pool, self.kv_indices, self.last_page_len, self.meta_pool, self.meta_indices, k, v)
+
+
+PREFILL_IMPL = {"": 0, "simt": 1, "umma": 2, "tma": 3}
+
+
+class prefill_impl:
+    """``with prefill_impl("tma_smem"): ...`` -- selects a prefill kernel through the library's explicit debug switches
+    (quest_debug_set_option; the library does not read the environment).  "": the library's own choice by shape."""
+
+    def __init__(self, impl):
+        self.impl = impl
+
+    def __enter__(self):
+        import quest_b200._kernels as K
+        self.a = K.debug_option(K.DBG_PREFILL_IMPL, PREFILL_IMPL[self.impl.split("_")[0]])
+        self.b = K.debug_option(K.DBG_PREFILL_P_SMEM, 1 if self.impl == "tma_smem" else 0)
+        self.a.__enter__(), self.b.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        self.b.__exit__(*exc), self.a.__exit__(*exc)
+        return False

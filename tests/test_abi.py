@@ -42,12 +42,29 @@ def test_decode_plan_host_only():
     assert lib.quest_decode_plan(127, 32, 32, 128, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0
     assert ppc.value * nch.value >= 128 and (nch.value - 1) * ppc.value < 128
     assert 32 * nch.value <= 148 * 7  # one resident wave (7 CTAs of 128 threads per SM)
-    # sync words | tickets | (m, d) pairs | fp32 partial outputs, each section 256-byte aligned (csrc/common.cuh)
-    assert lib.quest_decode_workspace_bytes(32, 128, nch.value) == 4096 + 256 + 32 * nch.value * 2 * 4 + 32 * nch.value * 128 * 4
+    # reserved | tickets | selection bin totals (4 KB per head) | (m, d) pairs | fp32 partial outputs, each section
+    # 256-byte aligned (csrc/common.cuh); the layer step adds one row of 16-bit keys per head (csrc/select.cuh)
+    core = 4096 + 256 + 32 * 4096 + 32 * nch.value * 2 * 4 + 32 * nch.value * 128 * 4
+    assert lib.quest_decode_workspace_bytes(32, 128, nch.value) == core
+    assert lib.quest_step_workspace_bytes(32, 128, nch.value, 2047) == core + 32 * 2048 * 2
+    assert lib.quest_step_workspace_bytes(32, 128, nch.value, 2049) == core + 32 * (24 * 128) * 2
     # tiny problems collapse to one chunk; bad dims are refused
     assert lib.quest_decode_plan(0, 32, 32, 128, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0 and nch.value == 1
     assert lib.quest_decode_plan(10, 32, 32, 96, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == -2
     assert lib.quest_topk_max_len() >= 65536
+
+
+def test_debug_options_are_explicit_and_restored():
+    """Test / A-B switches are set through the ABI (the library never reads the environment) and hand back the old value."""
+    lib = K.load_library()
+    assert lib.quest_debug_set_option(K.DBG_PREFILL_IMPL, 3) == 0
+    with K.debug_option(K.DBG_PREFILL_IMPL, 2):
+        assert lib.quest_debug_set_option(K.DBG_PREFILL_IMPL, 2) == 2
+    assert lib.quest_debug_set_option(K.DBG_PREFILL_IMPL, 0) == 3
+    assert lib.quest_debug_set_option(99, 1) == -1
+    src = "".join(open(os.path.join(ROOT, "quest_b200", "csrc", f)).read() for f in os.listdir(os.path.join(ROOT, "quest_b200", "csrc"))
+                  if f.endswith((".cu", ".cuh")))
+    assert "getenv" not in src
 
 
 def test_argument_errors_without_touching_the_gpu():

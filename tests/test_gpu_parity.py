@@ -9,7 +9,7 @@ import torch
 import quest_b200._kernels as K
 import quest_b200.utils as qu
 from oracle import quest_oracle as orc
-from tests.helpers import OracleCache, golden_inputs
+from tests.helpers import OracleCache, golden_inputs, prefill_impl
 
 pytestmark = pytest.mark.gpu
 ATTN_ATOL = 2e-3  # north_star: fp16 attention output max abs error
@@ -307,12 +307,27 @@ def test_decode_layer_step_operator_equals_four_ops(kv_len, budget):
             assert torch.equal(pa[:-1], pb[:-1]) and torch.equal(pa[-1, :, :ca.last_page_len], pb[-1, :, :ca.last_page_len])
 
 
+def step_workspace(lib, Hq, D, nchunks, n_scored, fused):
+    """fused: room for the selection's key rows -> two launches (estimate publishing keys + bin totals, decode selecting
+    its own pages); else the plain decode workspace -> the three stand-alone kernels behind the same entry point."""
+    nbytes = lib.quest_step_workspace_bytes(Hq, D, nchunks, n_scored) if fused else lib.quest_decode_workspace_bytes(Hq, D, nchunks)
+    return torch.zeros(nbytes, dtype=torch.uint8, device=DEV)
+
+
+def assert_workspace_at_rest(lib, ws, Hq, D, nchunks):
+    """Tickets and the selection's bin totals are back to zero after every launch (self-resetting state)."""
+    zero_state = lib.quest_decode_workspace_bytes(Hq, D, nchunks) - Hq * nchunks * (D + 2) * 4 - 512
+    assert int(ws[:4096 + 256 + Hq * 4096].view(torch.int32).abs().sum()) == 0 and zero_state > 0
+
+
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("H,kv_len,budget,P", [(32, 2500, 32, 16), (32, 32768, 128, 16), (32, 20000, 64, 16), (32, 700, 44, 16),
                                                (16, 9000, 100, 16), (8, 4000, 17, 16), (32, 5000, 8, 8), (32, 40, 2, 16),
-                                               (32, 32768 + 16 * 300, 128, 16), (4, 3000, 16, 16), (32, 3000, 16, 32)])
-def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
+                                               (32, 32768 + 16 * 300, 128, 16), (4, 3000, 16, 16), (32, 3000, 16, 32),
+                                               (8, 131072, 256, 16), (2, 16 * 2048 + 16, 2047, 16)])
+def test_layer_step_equals_separate_calls(H, kv_len, budget, P, fused):
     """quest_sparse_decode_step against the three operator calls: scores and selected pages bit-exact, attention within
-    tolerance (the experimental cluster kernel of fused.cu, QUEST_FUSED=1|2, chunks the merge differently)."""
+    tolerance.  fused: the two-launch form (page selection inside the decode kernel, csrc/select.cuh)."""
     D = 128
     oc, gc, k, v, rng = make_pair(kv_len, P, H, D, seed=11 + H + budget)
     q = rng.standard_normal((1, H, D), dtype=np.float32).astype(np.float16)
@@ -329,7 +344,7 @@ def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
     import ctypes
     ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
     assert lib.quest_decode_plan(kk, H, H, D, P, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0
-    ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, max(nch.value, 296 // H)), dtype=torch.uint8, device=DEV)
+    ws = step_workspace(lib, H, D, nch.value, n, fused)
     tq = t(q)
     for _ in range(3):  # repeated launches reuse the self-resetting workspace
         s2, i2 = torch.zeros_like(s1), torch.zeros_like(i1)
@@ -340,7 +355,7 @@ def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
                                           ws.numel(), torch.cuda.current_stream().cuda_stream)
         assert rc == 0
         torch.cuda.synchronize()
-        assert int(ws[:4096].view(torch.int32).abs().sum()) == 0  # sync words reset, error word clear
+        assert_workspace_at_rest(lib, ws, H, D, nch.value)
         assert torch.equal(s1, s2) and torch.equal(i1, i2)
         assert (o1.float() - o2.float()).abs().max().item() <= 1e-3
     if n <= 700:  # the numpy oracle is slow beyond this
@@ -352,10 +367,12 @@ def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
     assert torch.equal(o1, o3)
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("Hq,Hkv,kv_len,budget,P,D", [(32, 32, 2500, 32, 16, 128), (32, 32, 32768, 128, 16, 128), (32, 32, 2049, 16, 16, 128),
                                                       (32, 32, 2065, 16, 16, 128), (32, 8, 3000, 24, 16, 128), (8, 8, 700, 9, 8, 64),
-                                                      (32, 32, 17, 2, 16, 128), (32, 32, 9, 1, 16, 128), (6, 3, 1000, 12, 16, 128)])
-def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P, D):
+                                                      (32, 32, 17, 2, 16, 128), (32, 32, 9, 1, 16, 128), (6, 3, 1000, 12, 16, 128),
+                                                      (32, 8, 131072, 256, 16, 128)])
+def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P, D, fused):
     """quest_decode_layer_step (append carried by the estimate kernel) against append_kv + estimate + top-k + decode on a
     second copy of the cache: pools, scores, selected pages and output all bit-identical; repeated over 3 tokens so that
     page and metadata-page boundaries are crossed (kv_len 2049 starts a page, 2065 continues one)."""
@@ -384,7 +401,7 @@ def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P
         # B: one call
         ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
         assert lib.quest_decode_plan(kk, Hq, Hkv, D, P, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0
-        ws = torch.zeros(lib.quest_decode_workspace_bytes(Hq, D, nch.value), dtype=torch.uint8, device=DEV)
+        ws = step_workspace(lib, Hq, D, nch.value, n, fused)
         s2, i2 = torch.zeros_like(s1), torch.zeros_like(i1)
         o2 = torch.zeros((1, Hq, D), dtype=torch.float16, device=DEV)
         tq, tk, tv = t(q), t(k1), t(v1)
@@ -397,6 +414,7 @@ def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P
         assert torch.equal(ga.kv.view(torch.int16), gb.kv.view(torch.int16)), f"kv pool, step {step}"
         assert torch.equal(ga.meta.view(torch.int16), gb.meta.view(torch.int16)), f"metadata pool, step {step}"
         assert torch.equal(s1, s2) and torch.equal(i1, i2) and torch.equal(o1, o2), f"step {step}"
+        assert_workspace_at_rest(lib, ws, Hq, D, nch.value)
     ga.assert_equal_oracle()
     gb.assert_equal_oracle()
 
@@ -447,30 +465,27 @@ PREFILL_CASES = [(13, 33, 32, 32, 128, 16), (502, 1110, 8, 8, 128, 16), (64, 64,
                  (70, 135, 2, 1, 64, 128)]
 
 
-def _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, causal, impl):
+_PREFILL_WANT = {}
+
+
+def _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, causal, impl, repeats=1):
     if impl.startswith("tma") and (P < 8 or P & (P - 1)):
         pytest.skip("the TMA kernel covers page sizes 2^n >= 8")
     rounds = [kv_len - qo_len, qo_len] if kv_len > qo_len else [qo_len]
     oc, gc, k, v, rng = make_pair(0, P, Hkv, D, seed=qo_len, rounds=[r for r in rounds if r])
     q = rng.standard_normal((qo_len, Hq, D), dtype=np.float32).astype(np.float16)
     kvi, *_ = gc.tables()
-    old = os.environ.get("QUEST_PF_IMPL")
-    if impl:
-        os.environ["QUEST_PF_IMPL"] = impl.split("_")[0]
-    if impl == "tma_smem":  # the TMA kernel with P handed over through shared memory instead of tensor memory
-        os.environ["QUEST_PF_PTMEM"] = "0"
-    try:
-        o = K.prefill_with_paged_kv_cache(t(q), gc.kv, kvi, oc.last_page_len, causal, 0, False, 1.0, 1e4)
-        torch.cuda.synchronize()
-    finally:
-        os.environ.pop("QUEST_PF_PTMEM", None)
-        if old is None:
-            os.environ.pop("QUEST_PF_IMPL", None)
-        else:
-            os.environ["QUEST_PF_IMPL"] = old
-    assert K.load_library().quest_debug_prefill_timeouts() == 0
-    want = orc.dense_attention(q, k, v, causal=causal)
-    assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL
+    key = (qo_len, kv_len, Hq, Hkv, D, P, causal)  # inputs are a function of the shape (seeded): one oracle run per shape
+    if key not in _PREFILL_WANT:
+        _PREFILL_WANT[key] = orc.dense_attention(q, k, v, causal=causal)
+    want = _PREFILL_WANT[key]
+    tq = t(q)
+    with prefill_impl(impl):  # "tma_smem": the TMA kernel with P handed over through shared memory instead of tensor memory
+        for _ in range(repeats):
+            o = K.prefill_with_paged_kv_cache(tq, gc.kv, kvi, oc.last_page_len, causal, 0, False, 1.0, 1e4)
+            torch.cuda.synchronize()
+            assert K.load_library().quest_debug_prefill_timeouts() == 0 and K.load_library().quest_device_error() == 0
+            assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL
 
 
 @pytest.mark.parametrize("impl", ["", "tma", "tma_smem", "umma", "simt"])  # "": the library's own choice by shape
@@ -488,6 +503,41 @@ def test_prefill_matches_dense_noncausal(qo_len, kv_len, Hq, Hkv, D, P, impl):
     _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, False, impl)
 
 
+@pytest.mark.parametrize("impl", ["", "tma", "tma_smem", "umma"])
+@pytest.mark.parametrize("qo_len,kv_len,Hq,Hkv,D,P", [(2048, 2048, 32, 32, 128, 16), (4096, 4096, 32, 8, 128, 16), (1500, 3100, 48, 12, 64, 32)])
+def test_prefill_multi_wave_matches_dense(qo_len, kv_len, Hq, Hkv, D, P, impl):
+    """More CTAs than the GPU holds at once (512 / 1024 / 576 against ~296 resident): CTAs of different lengths succeed
+    one another on an SM and co-resident CTAs drift apart, so a softmax warp can run tiles ahead of the PV MMAs -- the
+    case in which the final wait of the TMA kernel used to alias two phases of its per-tile barrier (round-1 verdict).
+    Five launches each."""
+    _prefill_case(qo_len, kv_len, Hq, Hkv, D, P, True, impl, repeats=5)
+
+
+@pytest.mark.parametrize("impl", ["tma", "tma_smem"])
+def test_prefill_under_a_competing_stream(impl):
+    """The TMA kernel while another stream keeps the SMs and the memory system busy (its CTAs are then scheduled in
+    ragged waves and the warps of a CTA see very different latencies): 20 launches, every one against the oracle."""
+    qo_len = kv_len = 3072
+    Hq, Hkv, D, P = 16, 16, 128, 16
+    oc, gc, k, v, rng = make_pair(0, P, Hkv, D, seed=77, rounds=[kv_len])
+    q = rng.standard_normal((qo_len, Hq, D), dtype=np.float32).astype(np.float16)
+    want = orc.dense_attention(q, k, v, causal=True)
+    kvi, *_ = gc.tables()
+    tq = t(q)
+    side = torch.cuda.Stream()
+    junk = torch.randn(64 * 1024 * 1024, device=DEV)
+    lib = K.load_library()
+    with prefill_impl(impl):
+        for it in range(20):
+            with torch.cuda.stream(side):
+                for _ in range(4):
+                    junk.mul_(1.0001).add_(0.5)
+            o = K.prefill_with_paged_kv_cache(tq, gc.kv, kvi, oc.last_page_len, True, 0, False, 1.0, 1e4)
+            torch.cuda.synchronize()
+            assert lib.quest_debug_prefill_timeouts() == 0 and lib.quest_device_error() == 0
+            assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL, f"launch {it}"
+
+
 @pytest.mark.parametrize("impl", ["tma", "umma"])
 def test_prefill_large_logits_lazy_rescale(impl):
     """Rows whose running maximum keeps growing by large steps (keys scaled up along the sequence): exercises the
@@ -503,12 +553,9 @@ def test_prefill_large_logits_lazy_rescale(impl):
     oc.append(k, v)
     gc.append(k, v)
     kvi, *_ = gc.tables()
-    os.environ["QUEST_PF_IMPL"] = impl
-    try:
+    with prefill_impl(impl):
         o = K.prefill_with_paged_kv_cache(t(q), gc.kv, kvi, oc.last_page_len, True, 0, False, 1.0, 1e4)
         torch.cuda.synchronize()
-    finally:
-        os.environ.pop("QUEST_PF_IMPL", None)
     assert K.load_library().quest_debug_prefill_timeouts() == 0
     want = orc.dense_attention(q, k, v, causal=True)
     assert np.abs(o.float().cpu().numpy() - want).max() <= ATTN_ATOL

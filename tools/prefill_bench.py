@@ -67,7 +67,7 @@ def main():
         reps = max(2, min(50, int(2e13 / flops)))
 
         def ours(impl):
-            os.environ["QUEST_PF_IMPL"] = impl
+            lib.quest_debug_set_option(K.DBG_PREFILL_IMPL, {"simt": 1, "umma": 2, "tma": 3}[impl])
             rc = lib.quest_prefill(q.data_ptr(), o[impl].data_ptr(), n, pool.data_ptr(), table.data_ptr(), n_pages, P, 1, H, H, D, P, st)
             assert rc == 0, rc
 
@@ -84,7 +84,8 @@ def main():
             line += f"{t_s:8.2f} {flops / t_s / 1e9:8.1f} | "
         else:
             line += f"{'-':>8s} {'-':>8s} | "
-        os.environ.pop("QUEST_PF_IMPL", None)
+        lib.quest_debug_set_option(K.DBG_PREFILL_IMPL, 0)
+        assert lib.quest_debug_prefill_timeouts() == 0 and lib.quest_device_error() == 0
         if ref is not None:
             qo_indptr = torch.tensor([0, n], dtype=torch.int32, device=DEV)
             kv_indptr = torch.tensor([0, n_pages], dtype=torch.int32, device=DEV)
@@ -97,6 +98,11 @@ def main():
             torch.cuda.synchronize()
             err = (o["ref"].float() - o["tma"].float()).abs().max().item()
             line += f"{t_r:8.3f} {flops / t_r / 1e9:8.1f} | {t_r / t_u:8.2f} {err:9.1e}"
+            # a throughput number only counts with parity: every timed size is checked against the reference kernel
+            assert err <= 2e-3, f"n={n}: tma kernel differs from the reference prefill kernel by {err}"
+            if not only:
+                err_c = (o["ref"].float() - o["umma"].float()).abs().max().item()
+                assert err_c <= 2e-3, f"n={n}: cp.async tcgen05 kernel differs from the reference prefill kernel by {err_c}"
         else:
             line += f"{'n/a':>8s} {'n/a':>8s} | {'n/a':>8s} {'n/a':>9s}"
         print(line, flush=True)
