@@ -168,11 +168,7 @@ class Workload:
             ppc.value = int(os.environ["BENCH_PPC"])
             nch.value = (K_SEL + 1 + ppc.value - 1) // ppc.value
         self.plan = (ppc.value, nch.value)
-        # room for the selection's key rows: the layer step runs as two launches (estimate publishing keys and bin totals,
-        # decode selecting its own pages); BENCH_UNFUSED=1 sizes it for the three stand-alone kernels instead (A/B)
-        unfused = os.environ.get("BENCH_UNFUSED", "0") == "1"
-        self.ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, nch.value) if unfused else
-                              lib.quest_step_workspace_bytes(H, D, nch.value, N_SCORED), dtype=torch.uint8, device=self.dev)
+        self.ws = torch.zeros(lib.quest_decode_workspace_bytes(H, D, nch.value), dtype=torch.uint8, device=self.dev)
         kvi, mi = ic.kv_indices_with_last, ic.metadata_indices
         n_meta = mi.numel()
         kv_last_len, meta_last_len = ic.kv_cache.last_page_len, ic.metadata_cache.last_page_len

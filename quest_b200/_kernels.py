@@ -30,7 +30,6 @@ SIGNATURES = {
     "quest_topk": (_c.c_int, [_vp, _i32p, _u32, _vp, _i32p, _u32, _u32, _u32, _vp]),
     "quest_decode_plan": (_c.c_int, [_u32, _u32, _u32, _u32, _u32, _u32, _c.POINTER(_u32), _c.POINTER(_u32)]),
     "quest_decode_workspace_bytes": (_sz, [_u32, _u32, _u32]),
-    "quest_step_workspace_bytes": (_sz, [_u32, _u32, _u32, _u32]),
     "quest_decode_run": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_sparse_decode_step": (_c.c_int, [_vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_decode_layer_step": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32,
@@ -71,7 +70,7 @@ def load_library():
 
 
 # include/quest_b200.h QUEST_DBG_*: explicit test / A-B switches (the library never reads the environment)
-DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC, DBG_STEP_UNFUSED = range(7)
+DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC, DBG_STEP_UNFUSED, DBG_TAIL_GIVE_UP = range(8)
 DEVERR_PREFILL, DEVERR_PEER = 1, 2
 
 
@@ -306,19 +305,14 @@ class BatchDecodeWithPagedKVCachePyTorchWrapper:
     def end_forward(self):
         self._plan = None  # the workspace tensor is kept for the next begin_forward (tickets are self-resetting)
 
-    def _planned(self, n_sel, Hq, Hkv, D, P, device, scored_pages=0):
-        """``scored_pages`` > 0: size the workspace for the two-launch layer step (room for the selection's key rows,
-        quest_step_workspace_bytes), in steps of 4096 pages so that a growing sequence rarely reallocates."""
-        scored_cap = (int(scored_pages) + 4095) // 4096 * 4096
-        key = (n_sel, Hq, Hkv, D, P, scored_cap)
+    def _planned(self, n_sel, Hq, Hkv, D, P, device):
+        key = (n_sel, Hq, Hkv, D, P)
         if key not in self._chunks:
             lib = load_library()
             ppc, nch = _c.c_uint32(0), _c.c_uint32(0)
             _rc(lib.quest_decode_plan(n_sel, Hq, Hkv, D, P, _num_sms(device), _c.byref(ppc), _c.byref(nch)),
                 "BatchDecodeWithPagedKVCache plan")
-            nbytes = (lib.quest_step_workspace_bytes(Hq, D, nch.value, scored_cap) if scored_cap else
-                      lib.quest_decode_workspace_bytes(Hq, D, nch.value))
-            self._chunks[key] = (ppc.value, nch.value, nbytes)
+            self._chunks[key] = (ppc.value, nch.value, lib.quest_decode_workspace_bytes(Hq, D, nch.value))
         ppc, nch, nbytes = self._chunks[key]
         if self._ws is None or self._ws.numel() < nbytes or self._ws.device != device:
             self._ws = torch.zeros(nbytes, dtype=torch.uint8, device=device)
@@ -366,7 +360,7 @@ class BatchDecodeWithPagedKVCachePyTorchWrapper:
         _check(tuple(scores.shape) == (Hq, n_pages - 1), "scores must be [num_qo_heads, num_kv_pages - 1]")
         _check(tuple(topk_indices.shape) == (Hq, n_sel), "topk_indices must be [num_qo_heads, planned num_pages]")
         _check_half(q, "decode_layer_step")
-        ppc, _ = self._planned(n_sel, Hq, Hkv, D, P, q.device, scored_pages=n_pages - 1)
+        ppc, _ = self._planned(n_sel, Hq, Hkv, D, P, q.device)
         return (q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), kv_data.data_ptr(), kv_indices.data_ptr(), n_pages,
                 int(kv_last_page_idx), int(kv_last_page_len), metadata_data.data_ptr(), metadata_indices.data_ptr(),
                 metadata_indices.size(0), int(metadata_last_page_len), scores.data_ptr(), topk_indices.data_ptr(), n_sel,
@@ -374,6 +368,6 @@ class BatchDecodeWithPagedKVCachePyTorchWrapper:
 
     def layer_step(self, *tensors_and_ints):
         """append_kv_cache_decode + estimate_attn_score + topk_filtering + forward in one C call
-        (quest_decode_layer_step: the append rides on the estimate kernel, the page selection on the decode kernel).  Same tensors as those four ops take
+        (quest_decode_layer_step: the append and the page selection ride on the estimate launch).  Same tensors as those four ops take
         (see layer_step_args); begin_forward must have planned num_pages = topk_indices.size(1)."""
         _rc(load_library().quest_decode_layer_step(*self.layer_step_args(*tensors_and_ints), _stream()), "decode_layer_step")

@@ -49,8 +49,7 @@ class BatchDecodeStep:
         _kernels._rc(self.lib.quest_decode_plan(self.k, self.Hq * self.B, self.Hkv * self.B, self.D, self.P, sms,
                                                 ctypes.byref(ppc), ctypes.byref(nch)), "quest_decode_plan")
         self.ppc = ppc.value
-        # room for the selection's key rows: the step is two launches per layer (estimate, decode that selects its pages)
-        self.ws_seq = (self.lib.quest_step_workspace_bytes(self.Hq, self.D, nch.value, self.max_kv_pages - 1) + 15) // 16 * 16
+        self.ws_seq = (self.lib.quest_decode_workspace_bytes(self.Hq, self.D, nch.value) + 15) // 16 * 16
         self.ws = torch.zeros(self.B, self.ws_seq, dtype=torch.uint8, device=self.dev)
         self.score_stride = self.Hq * (self.max_kv_pages - 1)
         self.scores = torch.empty(self.B, self.score_stride, dtype=torch.float16, device=self.dev)

@@ -42,12 +42,8 @@ def test_decode_plan_host_only():
     assert lib.quest_decode_plan(127, 32, 32, 128, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0
     assert ppc.value * nch.value >= 128 and (nch.value - 1) * ppc.value < 128
     assert 32 * nch.value <= 148 * 7  # one resident wave (7 CTAs of 128 threads per SM)
-    # reserved | tickets | selection bin totals (4 KB per head) | (m, d) pairs | fp32 partial outputs, each section
-    # 256-byte aligned (csrc/common.cuh); the layer step adds one row of 16-bit keys per head (csrc/select.cuh)
-    core = 4096 + 256 + 32 * 4096 + 32 * nch.value * 2 * 4 + 32 * nch.value * 128 * 4
-    assert lib.quest_decode_workspace_bytes(32, 128, nch.value) == core
-    assert lib.quest_step_workspace_bytes(32, 128, nch.value, 2047) == core + 32 * 2048 * 2
-    assert lib.quest_step_workspace_bytes(32, 128, nch.value, 2049) == core + 32 * (24 * 128) * 2
+    # sync words | tickets | (m, d) pairs | fp32 partial outputs, each section 256-byte aligned (csrc/common.cuh)
+    assert lib.quest_decode_workspace_bytes(32, 128, nch.value) == 4096 + 256 + 32 * nch.value * 2 * 4 + 32 * nch.value * 128 * 4
     # tiny problems collapse to one chunk; bad dims are refused
     assert lib.quest_decode_plan(0, 32, 32, 128, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0 and nch.value == 1
     assert lib.quest_decode_plan(10, 32, 32, 96, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == -2
