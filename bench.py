@@ -285,8 +285,6 @@ def main():
 
     import quest_b200._kernels as K
     lib = K.load_library()  # fails loudly if the CUDA library is missing
-    if os.environ.get("BENCH_UNFUSED", "0") == "1":  # A/B: the three stand-alone kernels behind the same entry points
-        lib.quest_debug_set_option(K.DBG_STEP_UNFUSED, 1)
     wl = Workload(dev, 1234 + rank)
 
     step, launches_per_step = wl.make_raw_step()

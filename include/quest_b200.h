@@ -134,8 +134,7 @@ int quest_decode_run(const void* q, void* o, float* lse,
 
 /* ---- fused layer step: estimate -> top-k -> sparse decode ---------------------------------------
  * The three calls QuestAttention.forward makes per layer per token (quest/models/QuestAttention.py:
- * 135-158) behind one entry; kernels are chained with programmatic dependent launch, and for rows of up to
- * 8192 pages the top-k runs in the tail of the estimate launch (2 launches instead of 3).  scores
+ * 135-158) behind one entry; kernels are chained with programmatic dependent launch.  scores
  * ([num_qo_heads, len] fp16) and topk_idx ([num_qo_heads, k] int32) are caller-provided
  * intermediates and hold the same values the separate calls would produce.
  * kv_indices: the sequence's page table (device, first `len` entries are the scored pages);
@@ -156,8 +155,7 @@ int quest_sparse_decode_step(const void* q, void* o,
  * and lengths already count it (as for quest_append_decode); kv_last_page_idx = kv_indices[num_kv_pages-1]
  * as a host value (the reference passes it the same way, controller.py:86-87).  k pages are selected among
  * the num_kv_pages-1 full pages (k = 0: attend to the last page only); scores [num_qo_heads, num_kv_pages-1]
- * fp16 and topk_idx [num_qo_heads, k] are outputs.  The append rides on one extra CTA of the estimate launch and the
- * page selection on that launch's tail: 2 launches (3 for rows longer than 8192 pages). */
+ * fp16 and topk_idx [num_qo_heads, k] are outputs.  The append rides on the estimate kernel (3 launches). */
 int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new, void* o,
                             void* kv_data, const int32_t* kv_indices, uint32_t num_kv_pages,
                             uint32_t kv_last_page_idx, uint32_t kv_last_page_len,
@@ -261,8 +259,6 @@ void quest_device_error_clear(void);
 #define QUEST_DBG_PREFILL_P_SMEM 3   /* 1: TMA prefill hands P to the PV MMA through shared memory             */
 #define QUEST_DBG_TOPK_NO_CLUSTER 4  /* 1: one CTA per top-k row for every length                              */
 #define QUEST_DBG_TOPK_GENERIC 5     /* 1: shared-memory-key top-k kernel for every length                     */
-#define QUEST_DBG_STEP_UNFUSED 6     /* 1: layer step as the stand-alone estimate / top-k / decode kernels     */
-#define QUEST_DBG_TAIL_GIVE_UP 7     /* 1: the estimate launch's selectors give up at once (decode-side fallback) */
 #define QUEST_DBG_COUNT 8
 int quest_debug_set_option(int option, int value);
 

@@ -70,7 +70,7 @@ def load_library():
 
 
 # include/quest_b200.h QUEST_DBG_*: explicit test / A-B switches (the library never reads the environment)
-DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC, DBG_STEP_UNFUSED, DBG_TAIL_GIVE_UP = range(8)
+DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC = range(6)
 DEVERR_PREFILL, DEVERR_PEER = 1, 2
 
 
@@ -368,6 +368,6 @@ class BatchDecodeWithPagedKVCachePyTorchWrapper:
 
     def layer_step(self, *tensors_and_ints):
         """append_kv_cache_decode + estimate_attn_score + topk_filtering + forward in one C call
-        (quest_decode_layer_step: the append and the page selection ride on the estimate launch).  Same tensors as those four ops take
+        (quest_decode_layer_step: the append rides on the estimate kernel).  Same tensors as those four ops take
         (see layer_step_args); begin_forward must have planned num_pages = topk_indices.size(1)."""
         _rc(load_library().quest_decode_layer_step(*self.layer_step_args(*tensors_and_ints), _stream()), "decode_layer_step")

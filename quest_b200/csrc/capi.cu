@@ -1,6 +1,6 @@
 // Library-level entry points: identification, launch counter, device-error words, test switches, and the layer step
-// that chains estimate -> (page selection inside) sparse decode with programmatic dependent launch (one call per
-// layer per token; reference call sites quest/models/QuestAttention.py:135-158).
+// that chains estimate -> top-k -> sparse decode with programmatic dependent launch (one call per layer per token;
+// reference call sites quest/models/QuestAttention.py:135-158).
 #include <stdlib.h>
 
 #include <mutex>
@@ -11,16 +11,12 @@ namespace quest {
 unsigned long long g_launch_count = 0;
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
-                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba, uint32_t batch,
-                      const TailSel& ts);  // estimate.cu
+                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba = BatchArgs{},
+                      uint32_t batch = 1);  // estimate.cu
 int topk_batch(const void* scores, int32_t* out_idx, uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba,
                uint32_t batch, cudaStream_t s);  // topk.cu
 int decode_batch(const void* q, void* o, const int32_t* indices, uint32_t n_sel, uint32_t Hq, uint32_t Hkv, uint32_t D,
-                 uint32_t P, uint32_t ppc, void* ws, const BatchArgs& ba, uint32_t batch, cudaStream_t s, uint32_t max_len,
-                 const void* sel_scores);  // decode.cu
-int decode_select(const void* q, void* o, const void* kv, int32_t* topk_idx, uint32_t k, const int32_t* kv_indices,
-                  uint32_t len, const void* scores, uint32_t last_page_idx, uint32_t last_page_len, uint32_t Hq, uint32_t Hkv,
-                  uint32_t D, uint32_t P, uint32_t ppc, void* ws, cudaStream_t s);  // decode.cu
+                 uint32_t P, uint32_t ppc, void* ws, const BatchArgs& ba, uint32_t batch, cudaStream_t s);  // decode.cu
 
 static int g_debug_options[QUEST_DBG_COUNT] = {};
 int debug_option(int option) { return (option >= 0 && option < QUEST_DBG_COUNT) ? g_debug_options[option] : 0; }
@@ -76,28 +72,8 @@ extern "C" const char* quest_version(void) { return "quest_b200 0.1.0 sm_100a"; 
 extern "C" uint64_t quest_launch_count(void) { return quest::g_launch_count; }
 extern "C" void quest_launch_count_reset(void) { quest::g_launch_count = 0; }
 
-namespace quest {
-// estimate (optionally carrying the append) with the page selection in its tail -> decode.  QUEST_ERR_UNSUPPORTED: nothing
-// was launched and the caller takes the three stand-alone kernels.
-static int fused_step(const void* q, void* o, const void* kv_data, const int32_t* kv_indices, uint32_t len,
-                      uint32_t last_page_idx, uint32_t last_page_len, const void* meta_data, const int32_t* meta_indices,
-                      void* scores, int32_t* topk_idx, uint32_t k, uint32_t Hq, uint32_t Hkv, uint32_t D, uint32_t P,
-                      uint32_t ppc, void* workspace, size_t workspace_bytes, const AppendArgs& ap, cudaStream_t s) {
-  if (k == 0 || len == 0 || !workspace || debug_option(QUEST_DBG_STEP_UNFUSED)) return QUEST_ERR_UNSUPPORTED;
-  const uint32_t nchunks = (k + 1 + ppc - 1) / ppc;
-  if (workspace_bytes < ws_bytes(Hq, D, nchunks)) return QUEST_ERR_WORKSPACE;
-  const TailSel ts = {reinterpret_cast<uint8_t*>(workspace), topk_idx, kv_indices, k, (uint32_t)debug_option(QUEST_DBG_TAIL_GIVE_UP)};
-  int rc = estimate_dispatch(q, scores, len, meta_data, meta_indices, Hq, Hkv, D, P, QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED,
-                             ap, s, BatchArgs{}, 1, ts);
-  if (rc) return rc;
-  return decode_select(q, o, kv_data, topk_idx, k, kv_indices, len, scores, last_page_idx, last_page_len, Hq, Hkv, D, P, ppc,
-                       workspace, s);
-}
-}  // namespace quest
-
-// estimate + page selection + sparse decode without the append (the three calls QuestAttention.forward makes after
-// append_kv, quest/models/QuestAttention.py:135-158): two launches (the selection runs in the estimate launch's tail) for
-// rows of up to 8192 pages, else the three stand-alone kernels.
+// estimate + top-k + sparse decode without the append (the three calls QuestAttention.forward makes after append_kv,
+// quest/models/QuestAttention.py:135-158), chained with programmatic dependent launch.
 extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_data, const int32_t* kv_indices,
                                         uint32_t len, uint32_t last_page_idx, uint32_t last_page_len,
                                         const void* meta_data, const int32_t* meta_indices, void* scores,
@@ -108,11 +84,7 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
   if (!q || !o || !kv_data || !kv_indices || !meta_data || !meta_indices || !scores || !topk_idx) return QUEST_ERR_BAD_ARG;
   if (!num_qo_heads || !num_kv_heads || !page_size || !pages_per_chunk || num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
   if (k > len) return QUEST_ERR_BAD_ARG;
-  int rc = quest::fused_step(q, o, kv_data, kv_indices, len, last_page_idx, last_page_len, meta_data, meta_indices, scores,
-                             topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
-                             workspace_bytes, quest::AppendArgs{}, (cudaStream_t)stream);
-  if (rc != QUEST_ERR_UNSUPPORTED) return rc;
-  rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+  int rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                           QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, stream);
   if (rc) return rc;
   // payload ids = the sequence's page table, shared by all heads (row stride 0)
@@ -123,8 +95,8 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
 }
 
 // One decode step of one layer: append_kv + estimate + top-k + sparse decode (the four calls of
-// quest/models/QuestAttention.py:100-150 in the reference).  The append rides on one extra CTA of the estimate launch and the
-// page selection runs in that launch's tail, so the step is two launches.
+// quest/models/QuestAttention.py:100-150 in the reference).  The append rides on one extra CTA of the estimate launch, so the
+// step is three launches.
 extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new, void* o, void* kv_data,
                                        const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_idx,
                                        uint32_t kv_last_page_len, void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
@@ -149,13 +121,8 @@ extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const v
     rc = quest_append_decode(k_new, v_new, kv_data, kv_indices, num_kv_pages, kv_last_page_len, meta_data, meta_indices,
                              num_meta_pages, meta_last_page_len, num_kv_heads, head_dim, page_size, stream);
   } else {
-    rc = quest::fused_step(q, o, kv_data, kv_indices, len, kv_last_page_idx, kv_last_page_len, meta_data, meta_indices, scores,
-                           topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
-                           workspace_bytes, ap, (cudaStream_t)stream);
-    if (rc != QUEST_ERR_UNSUPPORTED) return rc;
     rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                  QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream, quest::BatchArgs{}, 1,
-                                  quest::TailSel{});
+                                  QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream);
     if (rc) return rc;
     // payload ids = the sequence's page table, shared by all heads (row stride 0)
     rc = quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
@@ -187,22 +154,11 @@ extern "C" int quest_decode_layer_step_batch(const void* q, const void* k_new, c
   quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, nullptr, nullptr, nullptr, 0, 0, 0, 0};
   cudaStream_t s = (cudaStream_t)stream;
   const uint32_t flags = QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED;
-  // two launches: the selection runs in the tail of the estimate launch (rows of up to 8192 pages)
-  if (!quest::debug_option(QUEST_DBG_STEP_UNFUSED)) {
-    const quest::TailSel ts = {reinterpret_cast<uint8_t*>(workspace), topk_idx, nullptr, k,
-                               (uint32_t)quest::debug_option(QUEST_DBG_TAIL_GIVE_UP)};
-    const int rc = quest::estimate_dispatch(q, scores, max_len, nullptr, nullptr, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                            flags, ap, s, ba, batch, ts);
-    if (rc == QUEST_OK)
-      return quest::decode_batch(q, o, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
-                                 ba, batch, s, max_len, scores);
-    if (rc != QUEST_ERR_UNSUPPORTED) return rc;
-  }
   int rc = quest::estimate_dispatch(q, scores, max_len, nullptr, nullptr, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                    flags, ap, s, ba, batch, quest::TailSel{});
+                                    flags, ap, s, ba, batch);
   if (rc) return rc;
   rc = quest::topk_batch(scores, topk_idx, num_qo_heads, max_len, k, ba, batch, s);
   if (rc) return rc;
   return quest::decode_batch(q, o, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
-                             ba, batch, s, 0, nullptr);
+                             ba, batch, s);
 }

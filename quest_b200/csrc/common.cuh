@@ -180,16 +180,12 @@ struct BatchArgs {
 constexpr float kLog2e = 1.44269504088896340736f;
 
 // Decode workspace layout (caller-owned bytes, zero-filled once when allocated):
-//   [0, 4)                      arrival counter of the estimate kernel's scanning CTAs (layer step; reset by the decode kernel)
-//   [256, 256 + 4*Hq)           per q head: 1 = the head's page ids were selected in the estimate launch's tail (reset by the
-//                               decode kernel's last CTA for the head)
+//   [0, 4096)                   reserved (zero)
 //   [4096, 4096 + 4*Hq)         one merge ticket per q head (self-resetting)
 //   ws_md_off(Hq)               fp32 (m, d) pairs [Hq][nchunks]
 //   ws_o_off(Hq, nchunks)       fp32 partial outputs [Hq][nchunks][D]
 // The zero-state words sit at fixed offsets so that launches with different chunk counts can share a workspace.
 constexpr size_t kWsSyncBytes = 4096;
-constexpr size_t kWsFlagsOff = 256;
-constexpr uint32_t kWsMaxFlagHeads = (kWsSyncBytes - kWsFlagsOff) / 4;
 __host__ __device__ inline size_t ws_ticket_off() { return kWsSyncBytes; }
 __host__ __device__ inline size_t ws_md_off(uint32_t Hq) { return (kWsSyncBytes + (size_t)Hq * 4 + 255) & ~(size_t)255; }
 __host__ __device__ inline size_t ws_o_off(uint32_t Hq, uint32_t nchunks) {
@@ -198,16 +194,6 @@ __host__ __device__ inline size_t ws_o_off(uint32_t Hq, uint32_t nchunks) {
 __host__ __device__ inline size_t ws_bytes(uint32_t Hq, uint32_t D, uint32_t nchunks) {
   return ws_o_off(Hq, nchunks) + (size_t)Hq * nchunks * D * sizeof(float);
 }
-
-// Page selection in the tail of the estimate launch (layer step; estimate.cu): the first scanning CTAs to finish wait
-// for the rest and run the per-head top-k themselves, so the step has no top-k launch.  ws == nullptr: off.
-struct TailSel {
-  uint8_t* ws;                // the step's workspace (batch: one block per sequence, BatchArgs::ws_stride apart)
-  int32_t* out_idx;           // [Hq][k] selected page ids (batch: [batch][Hq][k])
-  const int32_t* page_table;  // payload ids (batch: from the records)
-  uint32_t k;
-  uint32_t give_up;           // test hook (QUEST_DBG_TAIL_GIVE_UP): selectors leave at once, the decode kernel selects
-};
 
 }  // namespace quest
 

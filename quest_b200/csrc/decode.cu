@@ -9,7 +9,7 @@
 // ticket) merges them -- no separate merge launch.
 #include <stdlib.h>
 
-#include "topk.cuh"
+#include "common.cuh"
 
 namespace quest {
 
@@ -45,17 +45,13 @@ __device__ __forceinline__ uint32_t div_p(uint32_t t, uint32_t p_magic) { return
 // 2 warp-wide K loads + 2 V loads (a lane group of D/8 lanes owns one 16-byte-per-lane token row), with
 // the next item's loads issued before the current item is consumed: 8 independent 128-bit loads per lane
 // stay in flight, ~128 KB per SM at 8 CTAs/SM, and the softmax arithmetic hides under them.
-// kSel (layer step): `indices_` was filled by the selectors in the tail of the estimate launch (estimate.cu); a head
-// whose flag is down (its selector gave up waiting) is selected here instead, by every chunk CTA of the head from the
-// head's scores (`sel_scores`, sel_len of them; payload sel_table) with the same deterministic rule.
-template <int D, int kThreads, int kMinBlocks, bool kSel>
+template <int D, int kThreads, int kMinBlocks>
 __global__ void __launch_bounds__(kThreads, kMinBlocks)
 decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __restrict__ lse_,
               const __half* __restrict__ kv_, const int32_t* __restrict__ indices_, uint32_t idx_stride,
               uint32_t n_sel, uint32_t last_page_idx_, uint32_t last_page_len_, uint32_t Hkv, uint32_t G,
               uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws_,
-              const BatchArgs ba, uint32_t sel_len_, const int32_t* __restrict__ sel_table_,
-              const uint16_t* __restrict__ sel_scores_) {
+              const BatchArgs ba) {
   const __half* __restrict__ q = q_;
   __half* __restrict__ o = o_;
   float* __restrict__ lse = lse_;
@@ -63,9 +59,6 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
   const int32_t* __restrict__ indices = indices_;
   uint32_t last_page_idx = last_page_idx_, last_page_len = last_page_len_;
   uint8_t* __restrict__ ws = ws_;
-  uint32_t sel_len = sel_len_;
-  const int32_t* __restrict__ sel_table = sel_table_;
-  const uint16_t* __restrict__ sel_scores = sel_scores_;
   if (ba.descs != nullptr) {  // descriptor mode: blockIdx.z = sequence (its record is constant during the step)
     const SeqDesc* d = ba.descs + blockIdx.z;
     const size_t b = blockIdx.z, Hq_ = gridDim.y;
@@ -77,20 +70,16 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
     last_page_len = d->kv_last_page_len;
     last_page_idx = (uint32_t)d->kv_indices[d->num_kv_pages - 1];
     ws += b * ba.ws_stride;
-    sel_len = d->num_kv_pages - 1;
-    sel_table = d->kv_indices;
-    if (kSel) sel_scores += b * ba.score_stride;
   }
   constexpr int kWarps = kThreads / 32;
   constexpr int LPR = D / 8;
   constexpr int TPL = 32 / LPR;           // token rows per warp-wide load
   constexpr int IT = 2 * TPL;             // tokens per item
   constexpr int NG = kWarps * TPL;     // lane groups per CTA
-  extern __shared__ int32_t s_pages[];    // [pages of this chunk], then (kSel) the fallback selection's keys
+  extern __shared__ int32_t s_pages[];    // [pages of this chunk]
   __shared__ float s_o[NG][D];
   __shared__ float s_md[NG][2];
   __shared__ uint32_t s_last;
-  __shared__ TopkScratch<kThreads / 32> s_sel;  // kSel fallback only
   const uint32_t chunk = blockIdx.x, nchunks = gridDim.x, h = blockIdx.y, Hq = gridDim.y;
   const uint32_t kvh = h / G;
   const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -105,38 +94,10 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
   D_STAMP(0);
   const int32_t* idx_row = indices + (size_t)h * idx_stride;
   float qv[8];
-  pdl_wait();  // q, the page ids (top-k kernel / the estimate launch's selectors) and the last page's new row (append) come from earlier kernels
+  pdl_wait();  // q, the page ids (top-k kernel) and the last page's new row (append) come from earlier kernels
   D_STAMP(1);
-  if constexpr (kSel) {
-    uint32_t* flags = reinterpret_cast<uint32_t*>(ws + kWsFlagsOff);
-    if (chunk == 0 && h == 0 && tid == 0) *reinterpret_cast<uint32_t*>(ws) = 0u;  // the estimate CTAs' arrival counter
-    if (__ldcg(flags + h) == 0u) {
-      // the head's selector gave up (estimate.cu): select here.  Every chunk CTA of the head writes the same ids.
-      int32_t* row = const_cast<int32_t*>(idx_row);
-      uint32_t k = n_sel;
-      if (k > sel_len) {
-        for (uint32_t i = sel_len + tid; i < k; i += kThreads) row[i] = -1;
-        k = sel_len;
-      }
-      if (k > 0) {
-        uint16_t* keys = reinterpret_cast<uint16_t*>(s_pages + ((min(ppc, total_pages) + 3) & ~3u));
-        const uint16_t* sc = sel_scores + (size_t)h * sel_len;
-        const uint32_t len8 = (sel_len + 7) & ~7u;
-        for (uint32_t i = tid; i < len8; i += kThreads) keys[i] = i < sel_len ? key_of(sc[i]) : (uint16_t)0;
-        __syncthreads();
-        topk_select<kThreads / 32, 8>(keys, sel_len, k, tid, 1, &s_sel, sel_table, row, nullptr);
-      }
-      __syncthreads();  // the ids this CTA wrote are visible to its own threads below
-      for (uint32_t i = tid; i < npg; i += kThreads)
-        s_pages[i] = pg0 + i < n_sel ? __ldcg(idx_row + pg0 + i) : (int32_t)last_page_idx;
-    } else {
-      for (uint32_t i = tid; i < npg; i += kThreads)
-        s_pages[i] = pg0 + i < n_sel ? __ldg(idx_row + pg0 + i) : (int32_t)last_page_idx;
-    }
-  } else {
-    for (uint32_t i = tid; i < npg; i += kThreads)
-      s_pages[i] = pg0 + i < n_sel ? __ldg(idx_row + pg0 + i) : (int32_t)last_page_idx;
-  }
+  for (uint32_t i = tid; i < npg; i += kThreads)
+    s_pages[i] = pg0 + i < n_sel ? __ldg(idx_row + pg0 + i) : (int32_t)last_page_idx;
   {
     const H8 qh = ld_plain(q + (size_t)h * D + lir * 8);
     h8_to_float(qh, qv);
@@ -272,7 +233,6 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
       if (col < D) o[(size_t)h * D + col] = __float2half_rn(dsum > 0.f ? __fdividef(osum[c], dsum) : 0.f);
     }
     if (lse && tid == 0) lse[h] = dsum > 0.f ? M + lg2(dsum) : -INFINITY;
-    if (kSel && tid == 0) reinterpret_cast<uint32_t*>(ws + kWsFlagsOff)[h] = 0u;  // the head's only reader is done with it
     return;
   }
   float* ws_o = reinterpret_cast<float*>(ws + ws_o_off(Hq, nchunks));
@@ -367,25 +327,18 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
     if (lse) lse[h] = df > 0.f ? Mf + lg2(df) : -INFINITY;
     ticket[h] = 0;  // ready for the next launch
   }
-  // every chunk CTA of the head read the head's selection flag before it took its ticket
-  if (kSel && tid == 0) reinterpret_cast<uint32_t*>(ws + kWsFlagsOff)[h] = 0u;
   D_STAMP(5);  // head merged
 }
 
-// sel_scores != nullptr: layer step with the selection in the estimate launch's tail -- `indices` is the topk_idx the
-// selectors filled; sel_len / sel_table / sel_scores serve the per-head fallback
 template <int D>
 static int launch_decode(const void* q, void* o, float* lse, const void* kv, const int32_t* indices,
                          uint32_t idx_stride, uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len,
                          uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t ppc, void* ws, cudaStream_t stream,
-                         const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, uint32_t sel_len = 0,
-                         const int32_t* sel_table = nullptr, const void* sel_scores = nullptr) {
+                         const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
   const uint32_t nchunks = (n_sel + 1 + ppc - 1) / ppc;
   const uint32_t npg_max = ppc < n_sel + 1 ? ppc : n_sel + 1;
-  size_t smem = (size_t)npg_max * sizeof(int32_t);
+  const size_t smem = (size_t)npg_max * sizeof(int32_t);
   if (smem > 32 * 1024) return QUEST_ERR_UNSUPPORTED;
-  if (sel_scores)  // keys of the fallback selection; sel_len bounds every sequence's row
-    smem = ((npg_max + 3) & ~3u) * sizeof(int32_t) + (((size_t)sel_len + 7) & ~(size_t)7) * sizeof(uint16_t);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(nchunks, Hq, batch);
   cfg.blockDim = dim3(kDecThreads);
@@ -397,37 +350,21 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const float sm_scale_log2 = kLog2e / sqrtf((float)D);
-  auto kern = sel_scores ? decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS, true> : decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS, false>;
+  auto kern = decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS>;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, lse,
                                      (const __half*)kv, indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv,
-                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba, sel_len, sel_table,
-                                     (const uint16_t*)sel_scores);
+                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
 
-// descriptor mode (quest_decode_layer_step_batch); sel_scores != nullptr: the ids come from the estimate launch's selectors
-// (max_len bounds the sequences' rows for the fallback's shared memory)
+// descriptor mode (quest_decode_layer_step_batch)
 int decode_batch(const void* q, void* o, const int32_t* indices, uint32_t n_sel, uint32_t Hq, uint32_t Hkv, uint32_t D,
-                 uint32_t P, uint32_t ppc, void* ws, const BatchArgs& ba, uint32_t batch, cudaStream_t s, uint32_t max_len,
-                 const void* sel_scores) {
-  const uint32_t sl = sel_scores ? max_len : 0u;
+                 uint32_t P, uint32_t ppc, void* ws, const BatchArgs& ba, uint32_t batch, cudaStream_t s) {
   switch (D) {
-    case 64: return launch_decode<64>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch, sl, nullptr, sel_scores);
-    case 128: return launch_decode<128>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch, sl, nullptr, sel_scores);
-    case 256: return launch_decode<256>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch, sl, nullptr, sel_scores);
-    default: return QUEST_ERR_UNSUPPORTED;
-  }
-}
-
-// the layer step's decode: ids from the estimate launch's selectors, per-head fallback from the scores
-int decode_select(const void* q, void* o, const void* kv, int32_t* topk_idx, uint32_t k, const int32_t* kv_indices,
-                  uint32_t len, const void* scores, uint32_t last_page_idx, uint32_t last_page_len, uint32_t Hq, uint32_t Hkv,
-                  uint32_t D, uint32_t P, uint32_t ppc, void* ws, cudaStream_t s) {
-  switch (D) {
-    case 64: return launch_decode<64>(q, o, nullptr, kv, topk_idx, k, k, last_page_idx, last_page_len, Hq, Hkv, P, ppc, ws, s, BatchArgs{}, 1, len, kv_indices, scores);
-    case 128: return launch_decode<128>(q, o, nullptr, kv, topk_idx, k, k, last_page_idx, last_page_len, Hq, Hkv, P, ppc, ws, s, BatchArgs{}, 1, len, kv_indices, scores);
-    case 256: return launch_decode<256>(q, o, nullptr, kv, topk_idx, k, k, last_page_idx, last_page_len, Hq, Hkv, P, ppc, ws, s, BatchArgs{}, 1, len, kv_indices, scores);
+    case 64: return launch_decode<64>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch);
+    case 128: return launch_decode<128>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch);
+    case 256: return launch_decode<256>(q, o, nullptr, nullptr, indices, n_sel, n_sel, 0, 0, Hq, Hkv, P, ppc, ws, s, ba, batch);
     default: return QUEST_ERR_UNSUPPORTED;
   }
 }

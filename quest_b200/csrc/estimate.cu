@@ -23,7 +23,6 @@
 #include <stdlib.h>
 
 #include "common.cuh"
-#include "topk.cuh"
 
 namespace quest {
 
@@ -165,111 +164,25 @@ __device__ __forceinline__ float reduce4_transposed(const float a[4], uint32_t l
 // kG = 0: any group size, one lane row per kv head looping over its q heads, q/mask in smem.
 // -DQUEST_EST_CLOCKS: every CTA stamps %globaltimer at its phase boundaries (tools/step_timeline.py)
 #ifdef QUEST_EST_CLOCKS
-__device__ unsigned long long g_est_clk[1024 * 8];
+__device__ unsigned long long g_est_clk[1024 * 4];
 #define E_STAMP(i)                                                                 \
   do {                                                                             \
     if (threadIdx.x == 0) {                                                        \
       unsigned long long t_;                                                       \
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                       \
-      g_est_clk[(blockIdx.x & 1023) * 8 + (i)] = t_;                               \
+      g_est_clk[(blockIdx.x & 1023) * 4 + (i)] = t_;                               \
     }                                                                              \
   } while (0)
 #else
 #define E_STAMP(i) do { } while (0)
 #endif
 
-// ---- page selection in the launch's tail (kTail) ------------------------------------------------------------------
-// The layer step needs the k best pages of every head before its decode kernel can touch the cache.  As a launch of its
-// own (topk.cu) the selection costs its ~2 us body plus a launch boundary on either side (4.4 us from the last score to
-// the decode kernel's first CTA, tools/step_timeline.py).  Here the FIRST scanning CTAs to finish become the selectors: a
-// CTA that takes arrival ticket t < rows waits until every scanning CTA of the sequence has arrived (they are all resident:
-// the grid is one wave) and selects row t, t + n_scan, ... with the register radix select of topk.cuh (same kernel code,
-// same deterministic tie rule), then raises the row's flag.  The wait is bounded: a selector that gives up leaves the flag
-// down and the decode kernel selects for that head itself (decode.cu), so a grid that is not co-resident (another
-// stream's kernel holding SMs) costs time, never correctness.  Rows of up to 8192 pages; longer ones keep the launch.
-constexpr uint32_t kTailMaxLen = 8192;
-constexpr unsigned long long kTailWaitNs = 500000ull;  // a legitimate wait is the spread of the CTAs' finish times: ~1 us
-
-template <int G>
-__device__ __forceinline__ void tail_select_row(const uint16_t* __restrict__ s, uint32_t len, uint32_t k,
-                                                const int32_t* __restrict__ page_table, int32_t* __restrict__ out_row,
-                                                uint16_t* keys, void* scratch) {
-  constexpr int W = kTileWarps, NK = 4 * G;
-  constexpr uint32_t T = 32 * W;
-  const uint32_t tid = threadIdx.x;
-  // scores written by other CTAs of this grid: read past L1 (ld.global.cg); the whole key array is written
-  // (0xffff -> key 0 past the row's end), rows of an odd length are only 2-byte aligned: scalar loads, all independent
-  uint16_t v[NK];
-#pragma unroll
-  for (int j = 0; j < NK; ++j) v[j] = tid + j * T < len ? __ldcg(s + tid + j * T) : (uint16_t)0xffffu;
-#pragma unroll
-  for (int j = 0; j < NK; ++j) keys[tid + j * T] = key_of(v[j]);
-  __syncthreads();
-  topk_select_fast<W, TopkNoHook, G>(keys, len, k, tid, 1, reinterpret_cast<TopkFastScratch<W, G>*>(scratch), page_table,
-                                     out_row, nullptr);
-  __syncthreads();  // keys / scratch are reused by the next row
-}
-
-// Called by every thread of a scanning CTA once its scores are written.  n_scan: scanning CTAs of this sequence.
-__device__ __forceinline__ void tail_select(uint8_t* ws, const __half* __restrict__ scores, uint32_t len, uint32_t k,
-                                            uint32_t rows, uint32_t n_scan, const int32_t* __restrict__ page_table,
-                                            int32_t* __restrict__ out_idx, uint32_t k_stride, uint32_t give_up) {
-  __shared__ __align__(16) uint16_t keys[16 * kTileWarps * 32];
-  __shared__ __align__(16) uint8_t scratch[sizeof(TopkFastScratch<kTileWarps, 4>)];
-  static_assert(sizeof(TopkFastScratch<kTileWarps, 4>) >= sizeof(TopkFastScratch<kTileWarps, 1>), "scratch is shared by both variants");
-  __shared__ uint32_t s_ticket;
-  uint32_t* ctr = reinterpret_cast<uint32_t*>(ws);
-  uint32_t* flags = reinterpret_cast<uint32_t*>(ws + kWsFlagsOff);
-  const uint32_t tid = threadIdx.x;
-  __threadfence();  // this thread's scores are visible device-wide before the CTA's arrival is
-  __syncthreads();
-  if (tid == 0) {
-    uint32_t t;
-    asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(t) : "l"(ctr) : "memory");
-    if (t < rows) {  // a selector: wait for the other scanning CTAs (bounded)
-      unsigned long long t0 = 0;
-      uint32_t seen = t + 1;
-      while (seen < n_scan && !give_up) {
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(ctr) : "memory");
-        unsigned long long now;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-        if (t0 == 0) t0 = now;
-        else if (now - t0 > kTailWaitNs) break;
-      }
-      if (seen < n_scan || give_up) t = 0xffffffffu;  // gave up: the rows stay unflagged
-    }
-    s_ticket = t;
-  }
-  __syncthreads();
-  const uint32_t ticket = s_ticket;
-  if (ticket >= rows) return;
-  E_STAMP(4);  // selector: every scanning CTA has arrived
-  if (k > len) {  // descriptor mode: a sequence with fewer scored pages than k selects all of them, the rest is -1
-    for (uint32_t row = ticket; row < rows; row += n_scan)
-      for (uint32_t i = len + tid; i < k; i += kTileWarps * 32) out_idx[(size_t)row * k_stride + i] = -1;
-    k = len;
-  }
-  for (uint32_t row = ticket; row < rows; row += n_scan) {
-    const uint16_t* s = reinterpret_cast<const uint16_t*>(scores) + (size_t)row * len;
-    if (k > 0) {
-      if (len <= 4u * kTileWarps * 32)
-        tail_select_row<1>(s, len, k, page_table, out_idx + (size_t)row * k_stride, keys, scratch);
-      else
-        tail_select_row<4>(s, len, k, page_table, out_idx + (size_t)row * k_stride, keys, scratch);
-    }
-    __threadfence();  // every thread's ids before the flag (the decode kernel also waits for this grid to complete)
-    __syncthreads();
-    if (tid == 0) flags[row] = 1u;
-  }
-  E_STAMP(5);  // selector: rows selected
-}
-
-template <int D, int kOrdered, int kG, int kTail>
+template <int D, int kOrdered, int kG>
 __global__ void __launch_bounds__(kTileWarps * 32, 2)
 estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uint32_t len_,
                      const __half* __restrict__ meta_, const int32_t* __restrict__ meta_indices_,
                      uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_magic /* ceil(2^32/P), 0 for P=1 */,
-                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap_, const BatchArgs ba, const TailSel ts_) {
+                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap_, const BatchArgs ba) {
   // descriptor mode: blockIdx.y = sequence; lengths, page tables and pools come from its device record
   const __half* __restrict__ q = q_;
   __half* __restrict__ o = o_;
@@ -277,7 +190,6 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   const __half* __restrict__ meta = meta_;
   const int32_t* __restrict__ meta_indices = meta_indices_;
   AppendArgs ap = ap_;
-  TailSel ts = ts_;
   if (ba.descs != nullptr) {
     const SeqDesc* d = ba.descs + blockIdx.y;
     const uint32_t npg = d->num_kv_pages;
@@ -286,11 +198,6 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
     meta_indices = d->meta_indices;
     q += (size_t)blockIdx.y * Hq * (D);
     o += (size_t)blockIdx.y * ba.score_stride;
-    if (kTail) {
-      ts.ws += (size_t)blockIdx.y * ba.ws_stride;
-      ts.out_idx += (size_t)blockIdx.y * Hq * ts.k;
-      ts.page_table = d->kv_indices;
-    }
     if (ap.k != nullptr) {
       ap.k += (size_t)blockIdx.y * Hkv * (D);
       ap.v += (size_t)blockIdx.y * Hkv * (D);
@@ -464,14 +371,12 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
     p += kDepth * PPP;
   }
   E_STAMP(3);  // this CTA's pages are scored
-  if constexpr (kTail != 0) tail_select(ts.ws, o, len, ts.k, Hq, n_scan, ts.page_table, ts.out_idx, ts.k, ts.give_up);
 }
 
 template <int D>
 static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void* meta, const int32_t* meta_indices,
                                 uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t flags, const AppendArgs& ap,
-                                cudaStream_t stream, const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1,
-                                const TailSel& ts = TailSel{}) {
+                                cudaStream_t stream, const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
   // descriptor mode (ba.descs): `len` is an upper bound over the batch (sizes the grid and the page-table staging)
   constexpr uint32_t T_r = kTileWarps * (32 / (D / 8));
   static int num_sms = 0;
@@ -497,12 +402,8 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   if (!per_q) smem += (size_t)Hq * D * 6;
   if (smem > 100 * 1024) return QUEST_ERR_UNSUPPORTED;
   const bool ord = flags & QUEST_EST_META_ORDERED;
-  const bool tail = ts.ws != nullptr;
-  if (tail && (len > kTailMaxLen || Hq > kWsMaxFlagHeads)) return QUEST_ERR_UNSUPPORTED;
-  auto kern = tail ? (per_q ? (ord ? estimate_tile_kernel<D, 1, 1, 1> : estimate_tile_kernel<D, 0, 1, 1>)
-                            : (ord ? estimate_tile_kernel<D, 1, 0, 1> : estimate_tile_kernel<D, 0, 0, 1>))
-                   : (per_q ? (ord ? estimate_tile_kernel<D, 1, 1, 0> : estimate_tile_kernel<D, 0, 1, 0>)
-                            : (ord ? estimate_tile_kernel<D, 1, 0, 0> : estimate_tile_kernel<D, 0, 0, 0>));
+  auto kern = per_q ? (ord ? estimate_tile_kernel<D, 1, 1> : estimate_tile_kernel<D, 0, 1>)
+                    : (ord ? estimate_tile_kernel<D, 1, 0> : estimate_tile_kernel<D, 0, 0>);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -519,7 +420,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   cfg.numAttrs = 1;
   const uint32_t p_magic = P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P);
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta, meta_indices,
-                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap, ba, ts);
+                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap, ba);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -574,21 +475,20 @@ namespace quest {
 // estimate, optionally carrying the step's append_kv (ap.k != nullptr) on the tile kernel's first CTA
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
-                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba, uint32_t batch,
-                      const TailSel& ts) {
+                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba, uint32_t batch) {
   if ((size_t)num_qo_heads * head_dim * 6 > 160 * 1024) return QUEST_ERR_UNSUPPORTED;
   {  // product path: the tile kernel, whenever the kv heads divide its row tile
     const uint32_t T_r = kTileWarps * (32 / (head_dim / 8));
     const bool force_rows = debug_option(QUEST_DBG_EST_ROWS) != 0;  // test hook: the generic kernel on tile-kernel shapes
     if (!force_rows && len && T_r % num_kv_heads == 0 && (head_dim == 64 || head_dim == 128 || head_dim == 256)) {
       switch (head_dim) {
-        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, ts);
-        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, ts);
-        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, ts);
+        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
+        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
+        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
       }
     }
   }
-  if (ba.descs != nullptr || ts.ws != nullptr) return QUEST_ERR_UNSUPPORTED;  // descriptor mode / tail selection: tile kernel only
+  if (ba.descs != nullptr) return QUEST_ERR_UNSUPPORTED;  // descriptor mode exists for the tile kernel only
   if (ap.k != nullptr) {  // generic path: append as its own launch
     const int rc = quest_append_decode(ap.k, ap.v, ap.kv, ap.kv_indices, ap.num_kv_pages, ap.kv_last_len, ap.meta,
                                        meta_indices, ap.num_meta_pages, ap.meta_last_len, num_kv_heads, head_dim,
@@ -608,7 +508,7 @@ int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_dat
 
 #ifdef QUEST_EST_CLOCKS
 extern "C" int quest_debug_estimate_clocks(unsigned long long* host_out, uint32_t n_ctas) {
-  return (int)cudaMemcpyFromSymbol(host_out, quest::g_est_clk, (size_t)n_ctas * 8 * 8);
+  return (int)cudaMemcpyFromSymbol(host_out, quest::g_est_clk, (size_t)n_ctas * 4 * 8);
 }
 #endif
 
@@ -621,5 +521,5 @@ extern "C" int quest_estimate(const void* q, void* o, uint32_t len, const void* 
   if (len == 0) return QUEST_OK;
   quest::AppendArgs none = {};
   return quest::estimate_dispatch(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                  flags, none, (cudaStream_t)stream, quest::BatchArgs{}, 1, quest::TailSel{});
+                                  flags, none, (cudaStream_t)stream, quest::BatchArgs{}, 1);
 }

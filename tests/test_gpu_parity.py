@@ -307,39 +307,18 @@ def test_decode_layer_step_operator_equals_four_ops(kv_len, budget):
             assert torch.equal(pa[:-1], pb[:-1]) and torch.equal(pa[-1, :, :ca.last_page_len], pb[-1, :, :ca.last_page_len])
 
 
-class step_mode:
-    """fused: the layer step as two launches (page selection in the tail of the estimate launch, the library's default for
-    rows of up to 8192 pages); else the three stand-alone kernels behind the same entry point (explicit library switch)."""
-
-    def __init__(self, fused):
-        # "fallback": the selectors give up at once, so every head is selected by the decode kernel's own CTAs
-        self.opts = [K.debug_option(K.DBG_STEP_UNFUSED, 0 if fused else 1),
-                     K.debug_option(K.DBG_TAIL_GIVE_UP, 1 if fused == "fallback" else 0)]
-
-    def __enter__(self):
-        for o in self.opts:
-            o.__enter__()
-        return self
-
-    def __exit__(self, *exc):
-        for o in reversed(self.opts):
-            o.__exit__(*exc)
-        return False
-
-
 def assert_workspace_at_rest(ws):
-    """Arrival counter, selection flags and merge tickets are back to zero after every step (self-resetting state)."""
+    """Reserved words and merge tickets are zero after every step (the tickets reset themselves)."""
     assert int(ws[:4096 + 256].view(torch.int32).abs().sum()) == 0
 
 
-@pytest.mark.parametrize("fused", [True, "fallback", False])
 @pytest.mark.parametrize("H,kv_len,budget,P", [(32, 2500, 32, 16), (32, 32768, 128, 16), (32, 20000, 64, 16), (32, 700, 44, 16),
                                                (16, 9000, 100, 16), (8, 4000, 17, 16), (32, 5000, 8, 8), (32, 40, 2, 16),
                                                (32, 32768 + 16 * 300, 128, 16), (4, 3000, 16, 16), (32, 3000, 16, 32),
                                                (8, 131072, 256, 16), (2, 16 * 2048 + 16, 2047, 16)])
-def test_layer_step_equals_separate_calls(H, kv_len, budget, P, fused):
+def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
     """quest_sparse_decode_step against the three operator calls: scores and selected pages bit-exact, attention within
-    tolerance.  fused: the two-launch form (page selection in the tail of the estimate launch, csrc/estimate.cu)."""
+    tolerance."""
     D = 128
     oc, gc, k, v, rng = make_pair(kv_len, P, H, D, seed=11 + H + budget)
     q = rng.standard_normal((1, H, D), dtype=np.float32).astype(np.float16)
@@ -361,13 +340,11 @@ def test_layer_step_equals_separate_calls(H, kv_len, budget, P, fused):
     for _ in range(3):  # repeated launches reuse the self-resetting workspace
         s2, i2 = torch.zeros_like(s1), torch.zeros_like(i1)
         o2 = torch.zeros((1, H, D), dtype=torch.float16, device=DEV)
-        with step_mode(fused):
-            lib.quest_launch_count_reset()
-            rc = lib.quest_sparse_decode_step(tq.data_ptr(), o2.data_ptr(), gc.kv.data_ptr(), kvi.data_ptr(), n,
-                                              oc.kv_indices[-1], oc.last_page_len, gc.meta.data_ptr(), mi.data_ptr(),
-                                              s2.data_ptr(), i2.data_ptr(), kk, H, H, D, P, ppc.value, ws.data_ptr(),
-                                              ws.numel(), torch.cuda.current_stream().cuda_stream)
-            assert rc == 0 and lib.quest_launch_count() == (2 if fused and n <= 8192 and nch.value > 0 else 3)
+        rc = lib.quest_sparse_decode_step(tq.data_ptr(), o2.data_ptr(), gc.kv.data_ptr(), kvi.data_ptr(), n,
+                                          oc.kv_indices[-1], oc.last_page_len, gc.meta.data_ptr(), mi.data_ptr(),
+                                          s2.data_ptr(), i2.data_ptr(), kk, H, H, D, P, ppc.value, ws.data_ptr(),
+                                          ws.numel(), torch.cuda.current_stream().cuda_stream)
+        assert rc == 0
         torch.cuda.synchronize()
         assert_workspace_at_rest(ws)
         assert torch.equal(s1, s2) and torch.equal(i1, i2)
@@ -381,12 +358,11 @@ def test_layer_step_equals_separate_calls(H, kv_len, budget, P, fused):
     assert torch.equal(o1, o3)
 
 
-@pytest.mark.parametrize("fused", [True, "fallback", False])
 @pytest.mark.parametrize("Hq,Hkv,kv_len,budget,P,D", [(32, 32, 2500, 32, 16, 128), (32, 32, 32768, 128, 16, 128), (32, 32, 2049, 16, 16, 128),
                                                       (32, 32, 2065, 16, 16, 128), (32, 8, 3000, 24, 16, 128), (8, 8, 700, 9, 8, 64),
                                                       (32, 32, 17, 2, 16, 128), (32, 32, 9, 1, 16, 128), (6, 3, 1000, 12, 16, 128),
                                                       (32, 8, 131072, 256, 16, 128)])
-def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P, D, fused):
+def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P, D):
     """quest_decode_layer_step (append carried by the estimate kernel) against append_kv + estimate + top-k + decode on a
     second copy of the cache: pools, scores, selected pages and output all bit-identical; repeated over 3 tokens so that
     page and metadata-page boundaries are crossed (kv_len 2049 starts a page, 2065 continues one)."""
@@ -419,11 +395,10 @@ def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P
         s2, i2 = torch.zeros_like(s1), torch.zeros_like(i1)
         o2 = torch.zeros((1, Hq, D), dtype=torch.float16, device=DEV)
         tq, tk, tv = t(q), t(k1), t(v1)
-        with step_mode(fused):
-            rc = lib.quest_decode_layer_step(tq.data_ptr(), tk.data_ptr(), tv.data_ptr(), o2.data_ptr(), gb.kv.data_ptr(), kvi.data_ptr(),
-                                             n_pages, oc.kv_indices[-1], oc.last_page_len, gb.meta.data_ptr(), mi.data_ptr(),
-                                             len(oc.meta_indices), oc.meta_last_page_len, s2.data_ptr(), i2.data_ptr(), kk, Hq, Hkv,
-                                             D, P, ppc.value, ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream)
+        rc = lib.quest_decode_layer_step(tq.data_ptr(), tk.data_ptr(), tv.data_ptr(), o2.data_ptr(), gb.kv.data_ptr(), kvi.data_ptr(),
+                                         n_pages, oc.kv_indices[-1], oc.last_page_len, gb.meta.data_ptr(), mi.data_ptr(),
+                                         len(oc.meta_indices), oc.meta_last_page_len, s2.data_ptr(), i2.data_ptr(), kk, Hq, Hkv,
+                                         D, P, ppc.value, ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream)
         assert rc == 0
         torch.cuda.synchronize()
         assert torch.equal(ga.kv.view(torch.int16), gb.kv.view(torch.int16)), f"kv pool, step {step}"

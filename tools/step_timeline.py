@@ -1,4 +1,4 @@
-"""Per-CTA phase timeline of one layer step (estimate -> decode with its page selection) inside the bench graph:
+"""Per-CTA phase timeline of one layer step (estimate -> top-k -> decode) inside the bench graph:
   QUEST_EXTRA_FLAGS="-DQUEST_DEC_CLOCKS -DQUEST_EST_CLOCKS" QUEST_LIB_SUFFIX=_dbg bash quest_b200/csrc/build.sh   (here)
   QUEST_B200_LIB=quest_b200/libquest_b200_dbg.so python tools/step_timeline.py                                     (GPU box)
 Replays the bench workload's 32-layer graph and reads the %globaltimer stamps of the LAST layer's launches (the stamps of
@@ -15,7 +15,7 @@ sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 import quest_b200._kernels as K  # noqa: E402
 
-EST = ["est: cta start", "est: first ring issued", "est: launch wait done", "est: pages scored", "est: selector go", "est: selector done"]
+EST = ["est: cta start", "est: first ring issued", "est: launch wait done", "est: pages scored"]
 DEC = ["dec: cta start", "dec: launch wait done", "dec: ids + q in", "dec: warp 0 rows consumed", "dec: partial out, ticket",
        "dec: head merged"]
 
@@ -23,8 +23,6 @@ DEC = ["dec: cta start", "dec: launch wait done", "dec: ids + q in", "dec: warp 
 def main():
     lib = K.load_library()
     dev = torch.device("cuda", 0)
-    if os.environ.get("BENCH_UNFUSED", "0") == "1":
-        lib.quest_debug_set_option(K.DBG_STEP_UNFUSED, 1)
     wl = bench.Workload(dev, 1234)
     step, _ = wl.make_raw_step(parts=tuple(os.environ.get("PARTS", "layer").split(",")))
     step()
@@ -34,13 +32,13 @@ def main():
         g.replay()
     torch.cuda.synchronize()
     ne, nd = 297, 1024
-    be, bd = (ctypes.c_ulonglong * (ne * 8))(), (ctypes.c_ulonglong * (nd * 8))()
+    be, bd = (ctypes.c_ulonglong * (ne * 4))(), (ctypes.c_ulonglong * (nd * 8))()
     lib.quest_debug_estimate_clocks.restype = lib.quest_debug_decode_clocks.restype = ctypes.c_int
     assert lib.quest_debug_estimate_clocks(be, ne) == 0 and lib.quest_debug_decode_clocks(bd, nd) == 0
-    te = np.frombuffer(be, dtype=np.uint64).reshape(ne, 8).astype(np.int64)[:296]
+    te = np.frombuffer(be, dtype=np.uint64).reshape(ne, 4).astype(np.int64)[:296]
     td = np.frombuffer(bd, dtype=np.uint64).reshape(nd, 8).astype(np.int64)
     t0 = np.median(te[:, 0])
-    print(f"layer step timeline (last layer of the graph), us relative to the median estimate CTA start; unfused={os.environ.get('BENCH_UNFUSED', '0')}")
+    print(f"layer step timeline (last layer of the graph), us relative to the median estimate CTA start")
     print(f"{'event':30s} {'n':>5s} {'min':>8s} {'p10':>8s} {'p50':>8s} {'p90':>8s} {'max':>8s}")
     for names, t in ((EST, te), (DEC, td)):
         order = range(len(names))
