@@ -259,6 +259,7 @@ void quest_device_error_clear(void);
 #define QUEST_DBG_PREFILL_P_SMEM 3   /* 1: TMA prefill hands P to the PV MMA through shared memory             */
 #define QUEST_DBG_TOPK_NO_CLUSTER 4  /* 1: one CTA per top-k row for every length                              */
 #define QUEST_DBG_TOPK_GENERIC 5     /* 1: shared-memory-key top-k kernel for every length                     */
+#define QUEST_DBG_TOPK_NO_HIST 6     /* 1: layer step selects with the stand-alone top-k kernels (no bin totals) */
 #define QUEST_DBG_COUNT 8
 int quest_debug_set_option(int option, int value);
 

@@ -70,7 +70,7 @@ def load_library():
 
 
 # include/quest_b200.h QUEST_DBG_*: explicit test / A-B switches (the library never reads the environment)
-DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC = range(6)
+DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC, DBG_TOPK_NO_HIST = range(7)
 DEVERR_PREFILL, DEVERR_PEER = 1, 2
 
 

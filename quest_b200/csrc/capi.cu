@@ -12,7 +12,15 @@ unsigned long long g_launch_count = 0;
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
                       uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba = BatchArgs{},
-                      uint32_t batch = 1);  // estimate.cu
+                      uint32_t batch = 1, uint32_t* hist = nullptr);  // estimate.cu
+bool topk_hist_covers(uint32_t max_len);  // topk.cu
+int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
+                   uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s);  // topk.cu
+// the layer step's bin totals live in its decode workspace (common.cuh); nullptr: the workspace has no room for them
+static uint32_t* step_hist(void* workspace, size_t workspace_bytes, uint32_t Hq, uint32_t max_len) {
+  if (!workspace || workspace_bytes < ws_md_off(Hq) || !topk_hist_covers(max_len)) return nullptr;
+  return reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(workspace) + ws_hist_off(Hq));
+}
 int topk_batch(const void* scores, int32_t* out_idx, uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba,
                uint32_t batch, cudaStream_t s);  // topk.cu
 int decode_batch(const void* q, void* o, const int32_t* indices, uint32_t n_sel, uint32_t Hq, uint32_t Hkv, uint32_t D,
@@ -84,11 +92,23 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
   if (!q || !o || !kv_data || !kv_indices || !meta_data || !meta_indices || !scores || !topk_idx) return QUEST_ERR_BAD_ARG;
   if (!num_qo_heads || !num_kv_heads || !page_size || !pages_per_chunk || num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
   if (k > len) return QUEST_ERR_BAD_ARG;
-  int rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                          QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, stream);
+  if (k == 0 || len == 0)
+    return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, last_page_idx, last_page_len, num_qo_heads, num_kv_heads,
+                            head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
+  // the estimate kernel counts the scores into per-head bin totals, from which the top-k kernel selects in one pass
+  uint32_t* hist = quest::step_hist(workspace, workspace_bytes, num_qo_heads, len);
+  int rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+                                    QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, quest::AppendArgs{}, (cudaStream_t)stream,
+                                    quest::BatchArgs{}, 1, hist);
+  if (rc == QUEST_ERR_UNSUPPORTED && hist) {  // shapes only the generic estimate kernel takes
+    hist = nullptr;
+    rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+                        QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, stream);
+  }
   if (rc) return rc;
   // payload ids = the sequence's page table, shared by all heads (row stride 0)
-  rc = quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
+  rc = hist ? quest::topk_from_hist(scores, hist, kv_indices, 0, topk_idx, num_qo_heads, len, k, quest::BatchArgs{}, 1, (cudaStream_t)stream)
+            : quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
   if (rc) return rc;
   return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, last_page_idx, last_page_len, num_qo_heads,
                           num_kv_heads, head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
@@ -121,11 +141,19 @@ extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const v
     rc = quest_append_decode(k_new, v_new, kv_data, kv_indices, num_kv_pages, kv_last_page_len, meta_data, meta_indices,
                              num_meta_pages, meta_last_page_len, num_kv_heads, head_dim, page_size, stream);
   } else {
+    // the estimate kernel counts the scores into per-head bin totals, from which the top-k kernel selects in one pass
+    uint32_t* hist = quest::step_hist(workspace, workspace_bytes, num_qo_heads, len);
     rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                  QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream);
+                                  QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream, quest::BatchArgs{}, 1, hist);
+    if (rc == QUEST_ERR_UNSUPPORTED && hist) {  // shapes only the generic estimate kernel takes (it launches the append itself)
+      hist = nullptr;
+      rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+                                    QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream);
+    }
     if (rc) return rc;
     // payload ids = the sequence's page table, shared by all heads (row stride 0)
-    rc = quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
+    rc = hist ? quest::topk_from_hist(scores, hist, kv_indices, 0, topk_idx, num_qo_heads, len, k, quest::BatchArgs{}, 1, (cudaStream_t)stream)
+              : quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
   }
   if (rc) return rc;
   return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, kv_last_page_idx, kv_last_page_len, num_qo_heads, num_kv_heads,
@@ -154,10 +182,12 @@ extern "C" int quest_decode_layer_step_batch(const void* q, const void* k_new, c
   quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, nullptr, nullptr, nullptr, 0, 0, 0, 0};
   cudaStream_t s = (cudaStream_t)stream;
   const uint32_t flags = QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED;
+  uint32_t* hist = quest::step_hist(workspace, workspace_seq_bytes, num_qo_heads, max_len);
   int rc = quest::estimate_dispatch(q, scores, max_len, nullptr, nullptr, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                    flags, ap, s, ba, batch);
+                                    flags, ap, s, ba, batch, hist);
   if (rc) return rc;
-  rc = quest::topk_batch(scores, topk_idx, num_qo_heads, max_len, k, ba, batch, s);
+  rc = hist ? quest::topk_from_hist(scores, hist, nullptr, 0, topk_idx, num_qo_heads, max_len, k, ba, batch, s)
+            : quest::topk_batch(scores, topk_idx, num_qo_heads, max_len, k, ba, batch, s);
   if (rc) return rc;
   return quest::decode_batch(q, o, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
                              ba, batch, s);

@@ -179,15 +179,29 @@ struct BatchArgs {
 
 constexpr float kLog2e = 1.44269504088896340736f;
 
+// fp16 bits -> order-preserving 16-bit key (raft select_radix.cuh:82-90 twiddle_in)
+__device__ __forceinline__ uint16_t score_key(uint16_t h) { return (h & 0x8000u) ? (uint16_t)~h : (uint16_t)(h | 0x8000u); }
+// estimate epilogue of the layer step: count one score of head h in the head's bin totals (fire-and-forget reduction at L2)
+__device__ __forceinline__ void hist_count(uint32_t* __restrict__ hist, uint32_t h, __half score) {
+  const uint32_t bin = (uint32_t)score_key(__half_as_ushort(score)) >> 5;
+  asm volatile("red.global.add.u32 [%0], %1;" ::"l"(hist + (size_t)h * 1024 + (bin >> 1)), "r"(1u << ((bin & 1u) * 16)) : "memory");
+}
+
 // Decode workspace layout (caller-owned bytes, zero-filled once when allocated):
 //   [0, 4096)                   reserved (zero)
 //   [4096, 4096 + 4*Hq)         one merge ticket per q head (self-resetting)
+//   ws_hist_off(Hq)             layer step: per q head, how many of its scores fall in each of 2048 key bins (16-bit counts,
+//                               4 KB per head); added to by the estimate kernel, read and zeroed by the top-k kernel
 //   ws_md_off(Hq)               fp32 (m, d) pairs [Hq][nchunks]
 //   ws_o_off(Hq, nchunks)       fp32 partial outputs [Hq][nchunks][D]
 // The zero-state words sit at fixed offsets so that launches with different chunk counts can share a workspace.
 constexpr size_t kWsSyncBytes = 4096;
 __host__ __device__ inline size_t ws_ticket_off() { return kWsSyncBytes; }
-__host__ __device__ inline size_t ws_md_off(uint32_t Hq) { return (kWsSyncBytes + (size_t)Hq * 4 + 255) & ~(size_t)255; }
+constexpr uint32_t kHistBinShift = 5;                               // bin = 16-bit key >> 5
+constexpr uint32_t kHistBins = 1u << (16 - kHistBinShift);          // 2048
+constexpr size_t kHistBytesPerHead = kHistBins * 2;                 // 16-bit counts: rows of up to 65535 scores
+__host__ __device__ inline size_t ws_hist_off(uint32_t Hq) { return (kWsSyncBytes + (size_t)Hq * 4 + 255) & ~(size_t)255; }
+__host__ __device__ inline size_t ws_md_off(uint32_t Hq) { return ws_hist_off(Hq) + (size_t)Hq * kHistBytesPerHead; }
 __host__ __device__ inline size_t ws_o_off(uint32_t Hq, uint32_t nchunks) {
   return (ws_md_off(Hq) + (size_t)Hq * nchunks * 2 * sizeof(float) + 255) & ~(size_t)255;
 }

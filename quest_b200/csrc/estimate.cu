@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(kTileWarps * 32, 2)
 estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uint32_t len_,
                      const __half* __restrict__ meta_, const int32_t* __restrict__ meta_indices_,
                      uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_magic /* ceil(2^32/P), 0 for P=1 */,
-                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap_, const BatchArgs ba) {
+                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap_, const BatchArgs ba, uint32_t* __restrict__ hist_) {
   // descriptor mode: blockIdx.y = sequence; lengths, page tables and pools come from its device record
   const __half* __restrict__ q = q_;
   __half* __restrict__ o = o_;
@@ -190,6 +190,10 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   const __half* __restrict__ meta = meta_;
   const int32_t* __restrict__ meta_indices = meta_indices_;
   AppendArgs ap = ap_;
+  // layer step: every score is also counted in its head's bin totals, from which the top-k kernel finds the threshold
+  // without a histogram pass of its own (topk.cu, topk_hist_kernel); one workspace block per sequence
+  uint32_t* __restrict__ hist = hist_;
+  if (hist != nullptr && ba.descs != nullptr) hist += (size_t)blockIdx.y * (ba.ws_stride / 4);
   if (ba.descs != nullptr) {
     const SeqDesc* d = ba.descs + blockIdx.y;
     const uint32_t npg = d->num_kv_pages;
@@ -339,7 +343,11 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
         sa[s] = sacc;
       }
       const float v = reduce4_transposed<LPR>(sa, lir);
-      if (st) o[(size_t)kvh * len + pp] = __float2half_rn(v);
+      if (st) {
+        const __half sv = __float2half_rn(v);
+        o[(size_t)kvh * len + pp] = sv;
+        if (hist != nullptr) hist_count(hist, kvh, sv);
+      }
     } else {
       for (uint32_t g = 0; g < G; ++g) {
         const uint32_t h = kvh * G + g;
@@ -363,7 +371,11 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
           sa[s] = sacc;
         }
         const float v = reduce4_transposed<LPR>(sa, lir);
-        if (st) o[(size_t)h * len + pp] = __float2half_rn(v);
+        if (st) {
+          const __half sv = __float2half_rn(v);
+          o[(size_t)h * len + pp] = sv;
+          if (hist != nullptr) hist_count(hist, h, sv);
+        }
       }
 #pragma unroll
       for (int s = 0; s < kDepth; ++s) issue(s);
@@ -376,7 +388,8 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
 template <int D>
 static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void* meta, const int32_t* meta_indices,
                                 uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t flags, const AppendArgs& ap,
-                                cudaStream_t stream, const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
+                                cudaStream_t stream, const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1,
+                                uint32_t* hist = nullptr) {
   // descriptor mode (ba.descs): `len` is an upper bound over the batch (sizes the grid and the page-table staging)
   constexpr uint32_t T_r = kTileWarps * (32 / (D / 8));
   static int num_sms = 0;
@@ -420,7 +433,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   cfg.numAttrs = 1;
   const uint32_t p_magic = P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P);
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta, meta_indices,
-                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap, ba);
+                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap, ba, hist);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -475,20 +488,21 @@ namespace quest {
 // estimate, optionally carrying the step's append_kv (ap.k != nullptr) on the tile kernel's first CTA
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
-                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba, uint32_t batch) {
+                      uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba, uint32_t batch,
+                      uint32_t* hist) {
   if ((size_t)num_qo_heads * head_dim * 6 > 160 * 1024) return QUEST_ERR_UNSUPPORTED;
   {  // product path: the tile kernel, whenever the kv heads divide its row tile
     const uint32_t T_r = kTileWarps * (32 / (head_dim / 8));
     const bool force_rows = debug_option(QUEST_DBG_EST_ROWS) != 0;  // test hook: the generic kernel on tile-kernel shapes
     if (!force_rows && len && T_r % num_kv_heads == 0 && (head_dim == 64 || head_dim == 128 || head_dim == 256)) {
       switch (head_dim) {
-        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
-        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
-        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch);
+        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist);
+        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist);
+        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist);
       }
     }
   }
-  if (ba.descs != nullptr) return QUEST_ERR_UNSUPPORTED;  // descriptor mode exists for the tile kernel only
+  if (ba.descs != nullptr || hist != nullptr) return QUEST_ERR_UNSUPPORTED;  // descriptor mode / bin totals: tile kernel only
   if (ap.k != nullptr) {  // generic path: append as its own launch
     const int rc = quest_append_decode(ap.k, ap.v, ap.kv, ap.kv_indices, ap.num_kv_pages, ap.kv_last_len, ap.meta,
                                        meta_indices, ap.num_meta_pages, ap.meta_last_len, num_kv_heads, head_dim,
@@ -521,5 +535,5 @@ extern "C" int quest_estimate(const void* q, void* o, uint32_t len, const void* 
   if (len == 0) return QUEST_OK;
   quest::AppendArgs none = {};
   return quest::estimate_dispatch(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                  flags, none, (cudaStream_t)stream, quest::BatchArgs{}, 1);
+                                  flags, none, (cudaStream_t)stream, quest::BatchArgs{}, 1, nullptr);
 }

@@ -212,6 +212,180 @@ static int launch_topk_cluster(const void* scores, const int32_t* in_idx, uint32
   QUEST_RETURN_LAUNCH();
 }
 
+// ---- selection from published bin totals (layer step) -------------------------------------------------------------
+// In the layer step the estimate kernel counts every score into its head's 2048 bin totals (key >> 5; common.cuh
+// hist_count) while it writes it, so the selection does not have to histogram the row: the threshold BIN is one block
+// scan over the totals (raft spends a histogram pass over the data per 8 key bits, select_radix.cuh:930-1090; the
+// register radix select above four 4-bit passes), the low 5 key bits are resolved among the few keys of that bin, and
+// the ranks are one more block scan.  Same selection rule and output order as topk_select_fast.  Every thread owns
+// 4*G consecutive positions (blocked, so ranks follow positions) and 2048/512 = 4 bins, which it zeroes again once
+// read: the totals are back at rest when the kernel ends.  Rows of up to 4*G*512 pages (G = 4: 8192).
+constexpr int kHistThreads = 512;
+
+template <int G>
+__global__ void __launch_bounds__(kHistThreads)
+topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ hist_, const int32_t* __restrict__ in_idx_,
+                 uint32_t in_stride_, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_, const BatchArgs ba) {
+  constexpr int NK = 4 * G, W = kHistThreads / 32;
+  constexpr uint32_t BPT = kHistBins / kHistThreads;  // 4 bins = two packed words per thread
+  static_assert(BPT == 4, "one 8-byte load of bin totals per thread");
+  __shared__ uint32_t s_wtot[W], s_wtot2[W], s_sub[32], s_bstar, s_need1;
+  const uint32_t head = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int32_t* __restrict__ in_idx = in_idx_;
+  int32_t* __restrict__ out_idx = out_idx_;
+  uint32_t* __restrict__ hist = hist_;
+  uint32_t in_stride = in_stride_, len = len_, k = k_;
+#if QUEST_TRIG_TOPK
+  pdl_trigger();
+#endif
+  if (t < 32) s_sub[t] = 0;
+  pdl_wait();  // scores and bin totals come from the estimate kernel
+  if (ba.descs != nullptr) {  // descriptor mode, as in topk_fast_kernel
+    const SeqDesc* d = ba.descs + blockIdx.y;
+    len = d->num_kv_pages - 1;
+    in_idx = d->kv_indices;
+    in_stride = 0;
+    scores += (size_t)blockIdx.y * ba.score_stride;
+    out_idx += (size_t)blockIdx.y * gridDim.x * k_;
+    hist += (size_t)blockIdx.y * (ba.ws_stride / 4);
+    if (len > (uint32_t)(NK * kHistThreads)) len = NK * kHistThreads;  // never: the host sizes the variant by its bound
+  }
+  // this thread's bins [2048 - 4(t+1), 2048 - 4t): read, and put back to zero for the next step
+  uint2* hp = reinterpret_cast<uint2*>(hist + (size_t)head * (kHistBins / 2) + (kHistBins - BPT * (t + 1)) / 2);
+  const uint2 hv = *hp;
+  *hp = make_uint2(0u, 0u);
+  if (k > len) {
+    for (uint32_t i = len + t; i < k_; i += kHistThreads) out_idx[(size_t)head * k_ + i] = -1;
+    k = len;
+  }
+  if (k == 0) return;
+  const uint16_t* s = scores + (size_t)head * len;
+  const uint32_t p0 = t * NK;
+  // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent
+  uint32_t key[NK];
+  int32_t pay[NK];
+#pragma unroll
+  for (int j = 0; j < NK; ++j) key[j] = p0 + j < len ? (uint32_t)score_key(s[p0 + j]) : 0u;
+  const int32_t* pt = in_idx ? in_idx + (size_t)head * in_stride : nullptr;
+#pragma unroll
+  for (int j = 0; j < NK; ++j) pay[j] = p0 + j < len ? (pt ? __ldg(pt + p0 + j) : (int32_t)(p0 + j)) : 0;
+  const uint32_t nvalid = len > p0 ? min(len - p0, (uint32_t)NK) : 0u;
+
+  uint32_t tau = 0, need2 = 0;
+  const bool all = k >= len;  // every page of the row
+  if (!all) {
+    // ---- threshold bin: the inclusive scan over threads counts the keys in a thread's bins and all higher ones
+    const uint32_t c[BPT] = {hv.x & 0xffffu, hv.x >> 16, hv.y & 0xffffu, hv.y >> 16};  // ascending bins
+    const uint32_t mine = c[0] + c[1] + c[2] + c[3];
+    uint32_t incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t a = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= (uint32_t)off) incl += a;
+    }
+    if (lane == 31) s_wtot[warp] = incl;
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < W; ++w)
+      if ((uint32_t)w < warp) incl += s_wtot[w];
+    uint32_t above = incl - mine;
+    if (above < k && k <= incl) {  // exactly one thread: the k-th largest key lies in one of its bins
+      uint32_t b = 0, n1 = 0;
+#pragma unroll
+      for (int x = (int)BPT - 1; x >= 0; --x) {
+        const bool hit = above < k && k <= above + c[x];
+        b = hit ? (uint32_t)x : b;
+        n1 = hit ? k - above : n1;
+        above += c[x];
+      }
+      s_bstar = kHistBins - BPT * (t + 1) + b;
+      s_need1 = n1;
+    }
+    __syncthreads();
+    const uint32_t bstar = s_bstar, need1 = s_need1;
+    // ---- the low key bits among the keys of the threshold bin
+#pragma unroll
+    for (int j = 0; j < NK; ++j)
+      if ((uint32_t)j < nvalid && (key[j] >> kHistBinShift) == bstar) atomicAdd(&s_sub[key[j] & 31u], 1u);
+    __syncthreads();
+    {  // every warp resolves the sub-bin by itself: lane i looks at sub-bin 31 - i
+      const uint32_t cs = s_sub[31 - lane];
+      uint32_t inc = cs;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, inc, off);
+        if (lane >= (uint32_t)off) inc += a;
+      }
+      const uint32_t ab = inc - cs;
+      const uint32_t hit = __ballot_sync(0xffffffffu, ab < need1 && need1 <= inc);
+      const uint32_t l = (__ffs(hit) - 1) & 31u;
+      tau = (bstar << kHistBinShift) | (31 - l);
+      need2 = need1 - __shfl_sync(0xffffffffu, ab, l);
+    }
+  }
+  // ---- ranks: (greater, equal) counts of the positions before this thread's, as one packed block scan
+  const uint32_t bump = all ? 1u : 0u;  // all: tau = 0 and every in-row key counts as greater
+  uint32_t ngt = 0, neq = 0;
+#pragma unroll
+  for (int j = 0; j < NK; ++j) {
+    const bool in = (uint32_t)j < nvalid;
+    ngt += in && key[j] + bump > tau;
+    neq += in && key[j] + bump == tau;
+  }
+  const uint32_t pk = (ngt << 16) | neq;
+  uint32_t spk = pk;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const uint32_t a = __shfl_up_sync(0xffffffffu, spk, off);
+    if (lane >= (uint32_t)off) spk += a;
+  }
+  if (lane == 31) s_wtot2[warp] = spk;
+  __syncthreads();
+  uint32_t before = spk - pk;
+#pragma unroll
+  for (int w = 0; w < W; ++w)
+    if ((uint32_t)w < warp) before += s_wtot2[w];
+  uint32_t gt_before = before >> 16, eq_before = before & 0xffffu;
+  int32_t* out = out_idx + (size_t)head * k_;
+#pragma unroll
+  for (int j = 0; j < NK; ++j) {
+    const bool in = (uint32_t)j < nvalid;
+    const bool gt = in && key[j] + bump > tau, eq = in && key[j] + bump == tau;
+    const uint32_t pos = gt_before + min(eq_before, need2);
+    if ((gt || (eq && eq_before < need2)) && pos < k) out[pos] = pay[j];  // pos < k always, unless the totals were not at rest
+    gt_before += gt;
+    eq_before += eq;
+  }
+}
+
+template <int G>
+static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
+                            uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream,
+                            const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(num_heads, batch);
+  cfg.blockDim = dim3(kHistThreads);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba);
+  if (e != cudaSuccess) return (int)e;
+  QUEST_RETURN_LAUNCH();
+}
+
+// Layer step: rows whose bin totals the estimate kernel has published in `hist` (max_len bounds every row).
+bool topk_hist_covers(uint32_t max_len) { return max_len <= 16u * kHistThreads && debug_option(QUEST_DBG_TOPK_NO_HIST) == 0; }
+int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
+                   uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s) {
+  if (max_len <= 4u * kHistThreads) return launch_topk_hist<1>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch);
+  if (max_len <= 8u * kHistThreads) return launch_topk_hist<2>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch);
+  if (max_len <= 16u * kHistThreads) return launch_topk_hist<4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch);
+  return QUEST_ERR_UNSUPPORTED;
+}
+
 // A cluster pays off while all its CTAs (512 threads at 40 registers: 3 per SM) run in one wave; beyond that the single-CTA rows
 // (1024 threads, 2 per SM) finish sooner (configs[3] on one GPU: 8 x 32 rows).
 static bool topk_cluster_fits(uint32_t rows, uint32_t c) {
@@ -271,6 +445,24 @@ static int launch_topk(const void* scores, const int32_t* in_idx, uint32_t in_st
 }
 
 }  // namespace quest
+
+namespace quest {
+// test helper: the bin totals the estimate kernel would have published for these scores
+__global__ void hist_build_kernel(const __half* __restrict__ scores, uint32_t* __restrict__ hist, uint32_t len) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x)
+    hist_count(hist, blockIdx.y, scores[(size_t)blockIdx.y * len + i]);
+}
+}  // namespace quest
+
+// Test hook (not part of the operator surface): topk_hist_kernel on arbitrary scores.  hist: num_heads x 4 KB, zero on
+// entry and zero again when the kernel has run.
+extern "C" int quest_debug_topk_hist(const void* scores, const int32_t* in_idx, uint32_t in_idx_row_stride, int32_t* out_idx,
+                                     uint32_t num_heads, uint32_t len, uint32_t k, void* hist, void* stream) {
+  if (!scores || !out_idx || !hist || !num_heads || k > len || !quest::topk_hist_covers(len)) return QUEST_ERR_BAD_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  quest::hist_build_kernel<<<dim3(8, num_heads), 256, 0, s>>>((const __half*)scores, (uint32_t*)hist, len);
+  return quest::topk_from_hist(scores, (uint32_t*)hist, in_idx, in_idx_row_stride, out_idx, num_heads, len, k, quest::BatchArgs{}, 1, s);
+}
 
 extern "C" uint32_t quest_topk_max_len(void) { return quest::kTopkMaxLen; }
 

@@ -42,8 +42,9 @@ def test_decode_plan_host_only():
     assert lib.quest_decode_plan(127, 32, 32, 128, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0
     assert ppc.value * nch.value >= 128 and (nch.value - 1) * ppc.value < 128
     assert 32 * nch.value <= 148 * 7  # one resident wave (7 CTAs of 128 threads per SM)
-    # sync words | tickets | (m, d) pairs | fp32 partial outputs, each section 256-byte aligned (csrc/common.cuh)
-    assert lib.quest_decode_workspace_bytes(32, 128, nch.value) == 4096 + 256 + 32 * nch.value * 2 * 4 + 32 * nch.value * 128 * 4
+    # reserved | tickets | layer step's bin totals (4 KB per head) | (m, d) pairs | fp32 partial outputs, each section
+    # 256-byte aligned (csrc/common.cuh)
+    assert lib.quest_decode_workspace_bytes(32, 128, nch.value) == 4096 + 256 + 32 * 4096 + 32 * nch.value * 2 * 4 + 32 * nch.value * 128 * 4
     # tiny problems collapse to one chunk; bad dims are refused
     assert lib.quest_decode_plan(0, 32, 32, 128, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0 and nch.value == 1
     assert lib.quest_decode_plan(10, 32, 32, 96, 16, 148, ctypes.byref(ppc), ctypes.byref(nch)) == -2

@@ -179,6 +179,41 @@ def test_topk_exact(n, k, dist):
     np.testing.assert_array_equal(iout2, iout)
 
 
+@pytest.mark.parametrize("n,k", [(13, 2), (24, 24), (77, 19), (311, 69), (1024, 1024), (1025, 7), (2047, 127), (2047, 1), (2048, 2048), (2049, 511),
+                                 (3001, 640), (4096, 1), (4097, 333), (8191, 255), (8192, 4095), (8192, 8191)])
+@pytest.mark.parametrize("dist", ["normal", "narrow", "ties", "const"])
+def test_topk_from_bin_totals_exact(n, k, dist):
+    """The layer step's top-k (topk_hist_kernel: threshold from the bin totals the estimate kernel publishes) on crafted
+    rows: same positions and order as the oracle, bin totals back at zero afterwards.  "narrow": every score in one or two
+    bins, so the low key bits decide; "ties"/"const": the tie quota decides."""
+    H = 32
+    rng = np.random.default_rng(n * 11 + k)
+    if dist == "normal":
+        s = (rng.standard_normal((H, n)) * 30 + 100).astype(np.float16)
+    elif dist == "narrow":
+        s = (rng.random((H, n)) * 3.9 + 128).astype(np.float16)
+    elif dist == "ties":
+        s = rng.choice(np.array([-2.0, -0.0, 0.0, 0.5, 1.0, 1.5, 96.0], dtype=np.float16), size=(H, n))
+    else:
+        s = np.full((H, n), 3.25, dtype=np.float16)
+    perm = rng.permutation(n).astype(np.int32)
+    payload, ts = t(perm), t(s)
+    iout = torch.full((H, k), -1, dtype=torch.int32, device=DEV)
+    hist = torch.zeros(H * 1024, dtype=torch.int32, device=DEV)
+    lib = K.load_library()
+    import ctypes as C
+    lib.quest_debug_topk_hist.restype = C.c_int
+    lib.quest_debug_topk_hist.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
+                                          C.c_void_p]
+    for _ in range(2):  # the second launch finds the totals the first one put back to zero
+        assert lib.quest_debug_topk_hist(ts.data_ptr(), payload.data_ptr(), 0, iout.data_ptr(), H, n, k, hist.data_ptr(),
+                                         torch.cuda.current_stream().cuda_stream) == 0
+        torch.cuda.synchronize()
+        want_pos = orc.topk_select(s, k)
+        np.testing.assert_array_equal(iout.cpu().numpy(), perm[want_pos])
+        assert int(hist.abs().sum()) == 0
+
+
 def test_topk_reference_test_criterion():
     """quest/tests/test_topk.py:22-64: sum of selected values == torch.topk(...).values.sum()."""
     torch.manual_seed(0)
@@ -307,16 +342,31 @@ def test_decode_layer_step_operator_equals_four_ops(kv_len, budget):
             assert torch.equal(pa[:-1], pb[:-1]) and torch.equal(pa[-1, :, :ca.last_page_len], pb[-1, :, :ca.last_page_len])
 
 
-def assert_workspace_at_rest(ws):
-    """Reserved words and merge tickets are zero after every step (the tickets reset themselves)."""
-    assert int(ws[:4096 + 256].view(torch.int32).abs().sum()) == 0
+def assert_workspace_at_rest(ws, Hq):
+    """Reserved words, merge tickets and the selection's bin totals are zero after every step (they reset themselves)."""
+    assert int(ws[:4096 + 256 + Hq * 4096].view(torch.int32).abs().sum()) == 0
+
+
+class topk_mode:
+    """hist: the layer step's top-k selects from the bin totals the estimate kernel publishes (the default for rows of
+    up to 8192 pages); else the stand-alone register radix select (explicit library switch)."""
+
+    def __init__(self, hist):
+        self.opt = K.debug_option(K.DBG_TOPK_NO_HIST, 0 if hist else 1)
+
+    def __enter__(self):
+        return self.opt.__enter__()
+
+    def __exit__(self, *exc):
+        return self.opt.__exit__(*exc)
 
 
 @pytest.mark.parametrize("H,kv_len,budget,P", [(32, 2500, 32, 16), (32, 32768, 128, 16), (32, 20000, 64, 16), (32, 700, 44, 16),
                                                (16, 9000, 100, 16), (8, 4000, 17, 16), (32, 5000, 8, 8), (32, 40, 2, 16),
                                                (32, 32768 + 16 * 300, 128, 16), (4, 3000, 16, 16), (32, 3000, 16, 32),
                                                (8, 131072, 256, 16), (2, 16 * 2048 + 16, 2047, 16)])
-def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
+@pytest.mark.parametrize("hist", [True, False])
+def test_layer_step_equals_separate_calls(H, kv_len, budget, P, hist):
     """quest_sparse_decode_step against the three operator calls: scores and selected pages bit-exact, attention within
     tolerance."""
     D = 128
@@ -340,13 +390,14 @@ def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
     for _ in range(3):  # repeated launches reuse the self-resetting workspace
         s2, i2 = torch.zeros_like(s1), torch.zeros_like(i1)
         o2 = torch.zeros((1, H, D), dtype=torch.float16, device=DEV)
-        rc = lib.quest_sparse_decode_step(tq.data_ptr(), o2.data_ptr(), gc.kv.data_ptr(), kvi.data_ptr(), n,
-                                          oc.kv_indices[-1], oc.last_page_len, gc.meta.data_ptr(), mi.data_ptr(),
-                                          s2.data_ptr(), i2.data_ptr(), kk, H, H, D, P, ppc.value, ws.data_ptr(),
-                                          ws.numel(), torch.cuda.current_stream().cuda_stream)
+        with topk_mode(hist):
+            rc = lib.quest_sparse_decode_step(tq.data_ptr(), o2.data_ptr(), gc.kv.data_ptr(), kvi.data_ptr(), n,
+                                              oc.kv_indices[-1], oc.last_page_len, gc.meta.data_ptr(), mi.data_ptr(),
+                                              s2.data_ptr(), i2.data_ptr(), kk, H, H, D, P, ppc.value, ws.data_ptr(),
+                                              ws.numel(), torch.cuda.current_stream().cuda_stream)
         assert rc == 0
         torch.cuda.synchronize()
-        assert_workspace_at_rest(ws)
+        assert_workspace_at_rest(ws, H)
         assert torch.equal(s1, s2) and torch.equal(i1, i2)
         assert (o1.float() - o2.float()).abs().max().item() <= 1e-3
     if n <= 700:  # the numpy oracle is slow beyond this
@@ -362,7 +413,8 @@ def test_layer_step_equals_separate_calls(H, kv_len, budget, P):
                                                       (32, 32, 2065, 16, 16, 128), (32, 8, 3000, 24, 16, 128), (8, 8, 700, 9, 8, 64),
                                                       (32, 32, 17, 2, 16, 128), (32, 32, 9, 1, 16, 128), (6, 3, 1000, 12, 16, 128),
                                                       (32, 8, 131072, 256, 16, 128)])
-def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P, D):
+@pytest.mark.parametrize("hist", [True, False])
+def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P, D, hist):
     """quest_decode_layer_step (append carried by the estimate kernel) against append_kv + estimate + top-k + decode on a
     second copy of the cache: pools, scores, selected pages and output all bit-identical; repeated over 3 tokens so that
     page and metadata-page boundaries are crossed (kv_len 2049 starts a page, 2065 continues one)."""
@@ -395,16 +447,17 @@ def test_decode_layer_step_equals_four_operator_calls(Hq, Hkv, kv_len, budget, P
         s2, i2 = torch.zeros_like(s1), torch.zeros_like(i1)
         o2 = torch.zeros((1, Hq, D), dtype=torch.float16, device=DEV)
         tq, tk, tv = t(q), t(k1), t(v1)
-        rc = lib.quest_decode_layer_step(tq.data_ptr(), tk.data_ptr(), tv.data_ptr(), o2.data_ptr(), gb.kv.data_ptr(), kvi.data_ptr(),
-                                         n_pages, oc.kv_indices[-1], oc.last_page_len, gb.meta.data_ptr(), mi.data_ptr(),
-                                         len(oc.meta_indices), oc.meta_last_page_len, s2.data_ptr(), i2.data_ptr(), kk, Hq, Hkv,
-                                         D, P, ppc.value, ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream)
+        with topk_mode(hist):
+            rc = lib.quest_decode_layer_step(tq.data_ptr(), tk.data_ptr(), tv.data_ptr(), o2.data_ptr(), gb.kv.data_ptr(), kvi.data_ptr(),
+                                             n_pages, oc.kv_indices[-1], oc.last_page_len, gb.meta.data_ptr(), mi.data_ptr(),
+                                             len(oc.meta_indices), oc.meta_last_page_len, s2.data_ptr(), i2.data_ptr(), kk, Hq, Hkv,
+                                             D, P, ppc.value, ws.data_ptr(), ws.numel(), torch.cuda.current_stream().cuda_stream)
         assert rc == 0
         torch.cuda.synchronize()
         assert torch.equal(ga.kv.view(torch.int16), gb.kv.view(torch.int16)), f"kv pool, step {step}"
         assert torch.equal(ga.meta.view(torch.int16), gb.meta.view(torch.int16)), f"metadata pool, step {step}"
         assert torch.equal(s1, s2) and torch.equal(i1, i2) and torch.equal(o1, o2), f"step {step}"
-        assert_workspace_at_rest(ws)
+        assert_workspace_at_rest(ws, Hq)
     ga.assert_equal_oracle()
     gb.assert_equal_oracle()
 
