@@ -38,6 +38,22 @@ METRIC, UNIT = "sparse_decode_attn_hbm_GBps", "GB/s"
 WORKLOAD = "LongChat-7B-v1.5-32K shape (32 layers x 32 heads x 128, fp16), 32K ctx, page 16, budget 2048, batch 1/GPU"
 
 
+def recorded_traffic(kernel):
+    """DRAM read+write bytes per launch of `kernel` from the tracked ncu --set full capture (profiles/traffic.json), valid
+    only while the kernel's source is the one that was profiled (sha256 recorded beside it); else None."""
+    import hashlib
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            rec = json.load(f)[kernel]
+        with open(os.path.join(ROOT, rec["source"]), "rb") as f:
+            sha = hashlib.sha256(f.read()).hexdigest()
+        if sha != rec["source_sha256"]:
+            return None, f"stale: {rec['source']} changed since {rec['capture']}"
+        return int(rec["dram_bytes_per_launch"]), rec["capture"]
+    except Exception as e:  # no capture on record
+        return None, f"no capture on record ({type(e).__name__})"
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -262,6 +278,88 @@ def graph_of(step, warm=3):
     return g
 
 
+N1_CACHE = "/tmp/quest_b200_bench_n1.json"  # the scaling run's N=1 values, for efficiency_vs_n1 at N > 1 on the same box
+
+
+def extra_configs(rank, world, dev, dist_on):
+    """BASELINE.json configs[3] (GQA 32q/8kv, 128K, budget 4096, batch 8, kv-head sharded: strong scaling) and configs[4]'s
+    per-GPU shape (8192 pages per GPU, budget 8192, sequence sharded: weak scaling; exchanges through peer memory and through
+    NCCL), plus -- on one GPU -- the end-to-end decode tok/s of the reference's scripts/bench_textgen.py protocol.  Every
+    rank takes part; values are complete on rank 0.  A failure is reported in the block, never raised: the headline line
+    must not depend on it."""
+    import argparse as _ap
+    from tools import bench_configs as bc
+    out = {"configs": {}}
+    if not dist_on:  # the sequence-sharded step keeps its exchange buffers in symmetric memory: a world of one needs a group too
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29591")
+        torch.distributed.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    n1 = {}
+    if world > 1:
+        try:
+            with open(N1_CACHE) as f:
+                n1 = json.load(f)
+        except Exception:
+            n1 = {}
+
+    def keep(name, r, keys):
+        d = {k: r[k] for k in keys if k in r}
+        base = n1.get(name, {}).get("us_per_layer")
+        if r.get("scaling") == "strong":
+            d["efficiency_vs_n1"] = (base / (r["us_per_layer"] * world)) if base else (1.0 if world == 1 else None)
+        elif r.get("scaling") == "weak":
+            d["efficiency_vs_n1"] = (base / r["us_per_layer"]) if base else (1.0 if world == 1 else None)
+        out["configs"][name] = d
+
+    try:
+        if 8 % world == 0:
+            r = bc.measure(4, rank, world, dev, layers=2, streams=0, batched=1, steps=20, warmup=5)
+            keep("configs[3]", r, ("workload", "parallelism", "scaling", "n_gpus", "us_per_layer", "eager_us_per_layer",
+                                   "graph_us_per_layer", "frac_of_hbm_peak_per_gpu", "GBps_all_ranks",
+                                   "algorithmic_bytes_per_layer_all_ranks", "selection"))
+            torch.cuda.empty_cache()
+        else:
+            out["configs"]["configs[3]"] = {"skipped": f"8 kv heads do not split over {world} ranks"}
+    except Exception as e:
+        out["configs"]["configs[3]"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    for ex in ("peer", "nccl"):
+        name = f"configs[4]/{ex}"
+        try:
+            r = bc.measure(5, rank, world, dev, layers=2, exchange=ex, steps=20, warmup=5)
+            keep(name, r, ("workload", "parallelism", "scaling", "n_gpus", "us_per_layer", "eager_us_per_layer", "graph_us_per_layer",
+                           "compute_only_eager_us_per_layer", "compute_only_graph_us_per_layer", "exchange_us_per_layer",
+                           "frac_of_hbm_peak_per_gpu", "exchange_bytes_per_rank"))
+            torch.cuda.empty_cache()
+        except Exception as e:
+            out["configs"][name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    if world == 1 and rank == 0:
+        try:
+            with open(N1_CACHE, "w") as f:
+                json.dump(out["configs"], f)
+        except Exception:
+            pass
+        # end-to-end decode throughput, LongChat-7B shape, 32K context: token budget 2048 against the full cache
+        try:
+            from tools import e2e_textgen as tg
+            tok = {}
+            for budget in (2048, 0):
+                a = _ap.Namespace(context_len=CTX, decode_len=48, token_budget=budget, layers=L, prefill_chunk=8192, graph=True)
+                r = tg.run(a, dev)
+                tok["budget_2048" if budget else "full_cache"] = {"tok_per_s": r["value"], "ms_per_token": r["ms_per_token"],
+                                                                  "graph_device_ms_per_token": r.get("graph_device_ms_per_token"),
+                                                                  "prefill_s": r["prefill_s"]}
+                torch.cuda.empty_cache()
+            tok["speedup_vs_full_cache"] = tok["budget_2048"]["tok_per_s"] / tok["full_cache"]["tok_per_s"]
+            tok["protocol"] = ("reference scripts/bench_textgen.py:79-95 (32K random-embedding prefill, then 48 decode steps fed random "
+                               "embeddings, mean latency incl. host work); LongChat-7B-v1.5-32K shape, random-init fp16, batch 1; "
+                               "projections / MLP are torch matmuls, the attention path is this library; one CUDA graph replayed per token")
+            out["e2e_tok_s"] = tok["budget_2048"]["tok_per_s"]
+            out["e2e_textgen"] = tok
+        except Exception as e:
+            out["e2e_textgen"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -269,6 +367,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the configs[3]/configs[4] block and the e2e tok/s run")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -308,16 +407,35 @@ def main():
         t = timed(gk.replay, args.steps, 3, dist_on) / (args.steps * n)
         kern[name] = {"us": t * 1e6, "GBps": nbytes / t / 1e9}
     peak, peak_kind = peaks()
-    # DRAM read+write bytes per launch from the ncu --set full capture of this command (profiles/r01_c_layer_step.md)
-    ncu_traffic = {"estimate": 33598976, "decode": 33626112}
     dom = max(("estimate", "decode"), key=lambda k_: kern[k_]["us"])
     dom_bytes = {"estimate": BYTES_ESTIMATE, "decode": BYTES_DECODE}[dom]
     dom_name = {"estimate": "estimate_tile_kernel", "decode": "decode_kernel"}[dom]
+    traffic, traffic_src = recorded_traffic(dom_name)
 
     sec_e2e = timed(wl.e2e_step, max(3, args.steps // 5), 3, dist_on) / max(3, args.steps // 5)
+    plan = wl.plan
+    n_e2e_bytes = (wl.h_qkv.numel() * 2, wl.h_out.numel() * 2)
+    del wl, g, step, st, gk  # every closure over the 18.5 GB workload
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+
+    # BASELINE.json's multi-GPU splits, measured in the same run on the same ranks
+    extras = {}
+    if not args.no_extras:
+        # NCCL announces itself on stdout when a communicator is created: keep stdout for the ONE JSON line
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            extras = extra_configs(rank, world, dev, dist_on)
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
 
     if rank != 0:
-        if dist_on:
+        if torch.distributed.is_initialized():
             torch.distributed.destroy_process_group()
         return
     ms_step = sec / args.steps * 1e3
@@ -331,21 +449,24 @@ def main():
                    "decode position 32768 repeated", "l2": "inputs larger than L2: 32 layer pools (17.4 GB) rotated every launch",
                    "launch": f"CUDA graph of {launches_per_step} quest_decode_layer_step calls = {kernels_per_step} kernels (estimate carrying the "
                              "append, top-k, decode per layer), chained with programmatic dependent launch", "parallelism": f"batch-sharded x{world}, no collective",
-                   "algorithmic_bytes_per_layer": BYTES_STEP, "decode_plan_pages_per_chunk": wl.plan[0]},
+                   "algorithmic_bytes_per_layer": BYTES_STEP, "decode_plan_pages_per_chunk": plan[0],
+                   "cpu_arm_note": "the reference arm / cpu_baseline time ONE layer-step per step (1/32 of this step); the metric "
+                                   "(algorithmic GB/s) is per-layer on both arms"},
         "frac_of_hbm_peak": BYTES_STEP / (us_layer * 1e-6) / 1e9 / peak,
         "eager_us_per_layer": sec_eager / args.steps * 1e6 / L,
         "kernels": kern,
         "roofline": {"bound": "hbm", "kernel": dom_name, "achieved": kern[dom]["GBps"], "peak": peak, "peak_kind": peak_kind,
-                     "unit": "GB/s", "frac": kern[dom]["GBps"] / peak, "traffic": ncu_traffic[dom],
-                     "traffic_source": "profiles/r01_c_layer_step.md (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)",
+                     "unit": "GB/s", "frac": kern[dom]["GBps"] / peak, "traffic": traffic,
+                     "traffic_source": f"profiles/traffic.json: {traffic_src} (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)",
                      "algorithmic_bytes_per_launch": dom_bytes},
         "e2e": {"value": world * BYTES_STEP * L / sec_e2e / 1e9, "unit": UNIT, "ms_per_step": sec_e2e * 1e3,
-                "h2d_bytes_per_step": wl.h_qkv.numel() * 2, "d2h_bytes_per_step": wl.h_out.numel() * 2,
+                "h2d_bytes_per_step": n_e2e_bytes[0], "d2h_bytes_per_step": n_e2e_bytes[1],
                 "path": "quest_b200.utils operator surface (controller + " + ("4 ops/layer" if E2E_FOUR_OPS else "decode_layer_step/layer")
                         + "), pinned host q/k/v in, o out"},
         "gpu_launches": gpu_launches,
         "clocks": clocks,
     }
+    out.update(extras)
     if not args.no_cpu_baseline:
         ts = run_cpu_port(3, 1)
         s_cpu = sum(ts) / len(ts)
@@ -353,7 +474,7 @@ def main():
                                "sample": "3 layer-steps (after 1 warm-up) of the reference's torch CPU decode path at the same "
                                          "shape in fp32 (oracle/torch_path.py); a full step is 32 of these", "sec_per_layer": s_cpu}
     print(json.dumps(out))
-    if dist_on:
+    if torch.distributed.is_initialized():
         torch.distributed.destroy_process_group()
 
 

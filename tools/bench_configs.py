@@ -212,30 +212,15 @@ def config5(args, rank, world, dev):
         "exchange": args.exchange, "scaling": "weak"}, extra
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, required=True, choices=[4, 5])
-    ap.add_argument("--layers", type=int, default=2)
-    ap.add_argument("--streams", type=int, default=8, help="config 4: concurrent sequences per layer (0 = one stream)")
-    ap.add_argument("--batched", type=int, default=0, help="config 4: N groups of sequences, one batched launch chain each")
-    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"], help="config 5: how the two all-gathers are done")
-    ap.add_argument("--graph-collectives", action="store_true", help="config 5, N > 1: also capture the NCCL step in a CUDA graph")
-    ap.add_argument("--steps", type=int, default=30)
-    ap.add_argument("--warmup", type=int, default=5)
-    args = ap.parse_args()
-    rank, local, world = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("LOCAL_RANK", "0"), ("WORLD_SIZE", "1")))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist_on = world > 1
-    if dist_on:
-        dist.init_process_group("nccl", device_id=dev)
-    elif args.config == 5:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("MASTER_PORT", "29577")
-        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
-        dist_on = True
+def measure(config, rank, world, dev, layers=2, streams=8, batched=0, exchange="nccl", steps=30, warmup=5,
+            graph_collectives=False):
+    """One workload on the ranks of an initialised process group (world > 1; config 5 needs one for world 1 as well).
+    Returns the result dict (complete on rank 0)."""
+    args = argparse.Namespace(config=config, layers=layers, streams=streams, batched=batched, exchange=exchange, steps=steps,
+                              warmup=warmup, graph_collectives=graph_collectives)
+    dist_on = dist.is_initialized()
     extra = {}
-    if args.config == 4:
+    if config == 4:
         step, L, by_rank, cfg = config4(args, rank, world, dev)
     else:
         step, L, by_rank, cfg, extra = config5(args, rank, world, dev)
@@ -276,12 +261,38 @@ def main():
     if args.config == 5:
         shard_obj = extra.pop("shard")
         shard_obj.check_peer()
+        co_best = min(v for k, v in res.items() if k.startswith("compute_only"))
+        res["exchange_us_per_layer"] = max(best - co_best, 0.0)
+    gbps = total_bytes / (best * 1e-6) / 1e9
+    return {"config": args.config, "n_gpus": world, "us_per_layer": best, "algorithmic_bytes_per_layer_all_ranks": total_bytes,
+            "GBps_all_ranks": gbps, "frac_of_hbm_peak_per_gpu": gbps / world / peak(), "layers_rotated": L, **res, **cfg, **extra}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", type=int, required=True, choices=[4, 5])
+    ap.add_argument("--layers", type=int, default=2)
+    ap.add_argument("--streams", type=int, default=8, help="config 4: concurrent sequences per layer (0 = one stream)")
+    ap.add_argument("--batched", type=int, default=0, help="config 4: N groups of sequences, one batched launch chain each")
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "peer"], help="config 5: how the two all-gathers are done")
+    ap.add_argument("--graph-collectives", action="store_true", help="config 5, N > 1: also capture the NCCL step in a CUDA graph")
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    args = ap.parse_args()
+    rank, local, world = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("LOCAL_RANK", "0"), ("WORLD_SIZE", "1")))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    elif args.config == 5:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29577")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    out = measure(args.config, rank, world, dev, args.layers, args.streams, args.batched, args.exchange, args.steps, args.warmup,
+                  args.graph_collectives)
     if rank == 0:
-        gbps = total_bytes / (best * 1e-6) / 1e9
-        print(json.dumps({"config": args.config, "n_gpus": world, "us_per_layer": best, "algorithmic_bytes_per_layer_all_ranks":
-                          total_bytes, "GBps_all_ranks": gbps, "frac_of_hbm_peak_per_gpu": gbps / world / peak(),
-                          "layers_rotated": L, **res, **cfg, **extra}))
-    if dist_on:
+        print(json.dumps(out))
+    if dist.is_initialized():
         dist.destroy_process_group()
 
 

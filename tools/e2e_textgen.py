@@ -96,7 +96,6 @@ class Decoder:
         return last @ self.lm_head
 
 
-@torch.inference_mode()
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--context_len", type=int, default=32768)
@@ -107,8 +106,15 @@ def main():
     ap.add_argument("--graph", action="store_true", help="decode through ONE captured CUDA graph replayed per token "
                     "(descriptor-driven step, quest_decode_layer_step_batch) instead of eager operator calls")
     a = ap.parse_args()
-    dev = torch.device("cuda", 0)
-    torch.cuda.set_device(dev)
+    print(json.dumps(run(a)))
+
+
+@torch.inference_mode()
+def run(a, dev=None):
+    """a: namespace with context_len, decode_len, token_budget, layers, prefill_chunk, graph.  Returns the result dict."""
+    if dev is None:
+        dev = torch.device("cuda", 0)
+        torch.cuda.set_device(dev)
     max_seq = a.context_len + a.decode_len + 512
     max_pages = (max_seq + P - 1) // P
     budget_pages = max_pages if a.token_budget == 0 else a.token_budget // P
@@ -148,11 +154,11 @@ def main():
         torch.cuda.synchronize()
         attn_ms.append(sum(e0.elapsed_time(e1) for e0, e1 in model.attn_events))
     attn = sorted(attn_ms)[len(attn_ms) // 2]
-    print(json.dumps({"metric": "e2e_decode_tok_per_s", "value": 1e3 / ms, "ms_per_token": ms, "prefill_s": prefill_s,
+    return ({"metric": "e2e_decode_tok_per_s", "value": 1e3 / ms, "ms_per_token": ms, "prefill_s": prefill_s,
                       "context_len": a.context_len, "decode_len": a.decode_len, "token_budget": a.token_budget or "full",
                       "page_size": P, "layers": a.layers, "attention_path_ms_per_token": attn, "attention_share": attn / ms,
                       "model": "LongChat-7B-v1.5-32K shape, random init fp16, batch 1; torch matmuls + quest_b200 operators, eager",
-                      "protocol": "reference scripts/bench_textgen.py (random embeddings in, mean decode latency)"}))
+                      "protocol": "reference scripts/bench_textgen.py (random embeddings in, mean decode latency)"})
 
 
 def graph_decode(a, model, ic, budget_pages, max_pages, prefill_s, dev):
@@ -196,12 +202,12 @@ def graph_decode(a, model, ic, budget_pages, max_pages, prefill_s, dev):
     assert torch.isfinite(logits.float()).all()
     warm = lat[8:] if len(lat) > 16 else lat
     ms = sum(warm) / len(warm) * 1e3
-    print(json.dumps({"metric": "e2e_decode_tok_per_s", "value": 1e3 / ms, "ms_per_token": ms, "prefill_s": prefill_s,
+    return ({"metric": "e2e_decode_tok_per_s", "value": 1e3 / ms, "ms_per_token": ms, "prefill_s": prefill_s,
                       "graph_device_ms_per_token": sorted(dev_ms)[len(dev_ms) // 2],
                       "context_len": a.context_len, "decode_len": a.decode_len, "token_budget": a.token_budget or "full",
                       "page_size": P, "layers": a.layers, "mode": "one CUDA graph replayed per token (records refreshed by the host)",
                       "model": "LongChat-7B-v1.5-32K shape, random init fp16, batch 1; torch matmuls + quest_b200 operators",
-                      "protocol": "reference scripts/bench_textgen.py (random embeddings in, mean decode latency, host work included)"}))
+                      "protocol": "reference scripts/bench_textgen.py (random embeddings in, mean decode latency, host work included)"})
 
 
 if __name__ == "__main__":
