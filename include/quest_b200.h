@@ -132,6 +132,16 @@ int quest_decode_run(const void* q, void* o, float* lse,
                      uint32_t page_size, uint32_t pages_per_chunk,
                      void* workspace, size_t workspace_bytes, void* stream);
 
+/* Same, for one shard of a sequence-sharded step: the normalised partial output stays fp32 ([num_qo_heads, head_dim]) and
+ * lse is required, so that the cross-GPU merge (quest_merge_states, flashinfer state.cuh:53-62) sees what the
+ * single-GPU merge sees -- one rounding to fp16, at the very end. */
+int quest_decode_run_partial(const void* q, float* o_partial, float* lse,
+                             const void* kv_data, const int32_t* indices, uint32_t idx_row_stride,
+                             uint32_t num_sel_pages, uint32_t last_page_idx, uint32_t last_page_len,
+                             uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                             uint32_t page_size, uint32_t pages_per_chunk,
+                             void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- fused layer step: estimate -> top-k -> sparse decode ---------------------------------------
  * The three calls QuestAttention.forward makes per layer per token (quest/models/QuestAttention.py:
  * 135-158) behind one entry; kernels are chained with programmatic dependent launch.  scores

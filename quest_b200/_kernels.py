@@ -31,6 +31,7 @@ SIGNATURES = {
     "quest_decode_plan": (_c.c_int, [_u32, _u32, _u32, _u32, _u32, _u32, _c.POINTER(_u32), _c.POINTER(_u32)]),
     "quest_decode_workspace_bytes": (_sz, [_u32, _u32, _u32]),
     "quest_decode_run": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
+    "quest_decode_run_partial": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_sparse_decode_step": (_c.c_int, [_vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_decode_layer_step": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32,
                                            _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),

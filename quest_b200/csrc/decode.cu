@@ -51,7 +51,7 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
               const __half* __restrict__ kv_, const int32_t* __restrict__ indices_, uint32_t idx_stride,
               uint32_t n_sel, uint32_t last_page_idx_, uint32_t last_page_len_, uint32_t Hkv, uint32_t G,
               uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws_,
-              const BatchArgs ba) {
+              const BatchArgs ba, float* __restrict__ o32) {
   const __half* __restrict__ q = q_;
   __half* __restrict__ o = o_;
   float* __restrict__ lse = lse_;
@@ -230,7 +230,11 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
       const uint32_t col = tid + c * kThreads;
-      if (col < D) o[(size_t)h * D + col] = __float2half_rn(dsum > 0.f ? __fdividef(osum[c], dsum) : 0.f);
+      if (col < D) {
+        const float val = dsum > 0.f ? __fdividef(osum[c], dsum) : 0.f;
+        if (o32 != nullptr) o32[(size_t)h * D + col] = val;  // a shard's partial for the cross-GPU merge: not rounded to fp16
+        else o[(size_t)h * D + col] = __float2half_rn(val);
+      }
     }
     if (lse && tid == 0) lse[h] = dsum > 0.f ? M + lg2(dsum) : -INFINITY;
     return;
@@ -321,7 +325,11 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
     const uint32_t col = tid + c * kThreads;
-    if (col < D) o[(size_t)h * D + col] = __float2half_rn(df > 0.f ? __fdividef(of[c], df) : 0.f);
+    if (col < D) {
+      const float val = df > 0.f ? __fdividef(of[c], df) : 0.f;
+      if (o32 != nullptr) o32[(size_t)h * D + col] = val;
+      else o[(size_t)h * D + col] = __float2half_rn(val);
+    }
   }
   if (tid == 0) {
     if (lse) lse[h] = df > 0.f ? Mf + lg2(df) : -INFINITY;
@@ -334,7 +342,7 @@ template <int D>
 static int launch_decode(const void* q, void* o, float* lse, const void* kv, const int32_t* indices,
                          uint32_t idx_stride, uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len,
                          uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t ppc, void* ws, cudaStream_t stream,
-                         const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
+                         const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, float* o32 = nullptr) {
   const uint32_t nchunks = (n_sel + 1 + ppc - 1) / ppc;
   const uint32_t npg_max = ppc < n_sel + 1 ? ppc : n_sel + 1;
   const size_t smem = (size_t)npg_max * sizeof(int32_t);
@@ -353,7 +361,7 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
   auto kern = decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS>;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, lse,
                                      (const __half*)kv, indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv,
-                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba);
+                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba, o32);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -395,12 +403,11 @@ extern "C" size_t quest_decode_workspace_bytes(uint32_t num_qo_heads, uint32_t h
   return quest::ws_bytes(num_qo_heads, head_dim, num_chunks);
 }
 
-extern "C" int quest_decode_run(const void* q, void* o, float* lse, const void* kv_data, const int32_t* indices,
-                                uint32_t idx_row_stride, uint32_t num_sel_pages, uint32_t last_page_idx,
-                                uint32_t last_page_len, uint32_t num_qo_heads, uint32_t num_kv_heads,
-                                uint32_t head_dim, uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
-                                size_t workspace_bytes, void* stream) {
-  if (!q || !o || !kv_data || !num_qo_heads || !num_kv_heads || !page_size || !pages_per_chunk)
+static int decode_run_checked(const void* q, void* o, float* o32, float* lse, const void* kv_data, const int32_t* indices,
+                              uint32_t idx_row_stride, uint32_t num_sel_pages, uint32_t last_page_idx, uint32_t last_page_len,
+                              uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                              uint32_t pages_per_chunk, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!q || (!o && !o32) || !kv_data || !num_qo_heads || !num_kv_heads || !page_size || !pages_per_chunk)
     return QUEST_ERR_BAD_ARG;
   if (num_sel_pages && !indices) return QUEST_ERR_BAD_ARG;
   if (num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
@@ -414,7 +421,7 @@ extern "C" int quest_decode_run(const void* q, void* o, float* lse, const void* 
 #define QUEST_DEC(DD)                                                                                         \
   return quest::launch_decode<DD>(q, o, lse, kv_data, indices, idx_row_stride, num_sel_pages, last_page_idx, \
                                   last_page_len, num_qo_heads, num_kv_heads, page_size, pages_per_chunk,     \
-                                  workspace, s)
+                                  workspace, s, quest::BatchArgs{}, 1, o32)
   switch (head_dim) {
     case 64: QUEST_DEC(64);
     case 128: QUEST_DEC(128);
@@ -422,6 +429,27 @@ extern "C" int quest_decode_run(const void* q, void* o, float* lse, const void* 
     default: return QUEST_ERR_UNSUPPORTED;
   }
 #undef QUEST_DEC
+}
+
+extern "C" int quest_decode_run(const void* q, void* o, float* lse, const void* kv_data, const int32_t* indices,
+                                uint32_t idx_row_stride, uint32_t num_sel_pages, uint32_t last_page_idx,
+                                uint32_t last_page_len, uint32_t num_qo_heads, uint32_t num_kv_heads,
+                                uint32_t head_dim, uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+  if (!o) return QUEST_ERR_BAD_ARG;
+  return decode_run_checked(q, o, nullptr, lse, kv_data, indices, idx_row_stride, num_sel_pages, last_page_idx, last_page_len,
+                            num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
+}
+
+extern "C" int quest_decode_run_partial(const void* q, float* o_partial, float* lse, const void* kv_data, const int32_t* indices,
+                                        uint32_t idx_row_stride, uint32_t num_sel_pages, uint32_t last_page_idx,
+                                        uint32_t last_page_len, uint32_t num_qo_heads, uint32_t num_kv_heads,
+                                        uint32_t head_dim, uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
+  if (!o_partial || !lse) return QUEST_ERR_BAD_ARG;
+  return decode_run_checked(q, nullptr, o_partial, lse, kv_data, indices, idx_row_stride, num_sel_pages, last_page_idx,
+                            last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
+                            workspace_bytes, stream);
 }
 
 #ifdef QUEST_DEC_CLOCKS

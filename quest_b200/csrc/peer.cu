@@ -46,13 +46,14 @@ __device__ __forceinline__ unsigned long long global_ns() {
 __global__ void __launch_bounds__(kPeerThreads)
 peer_allgather_kernel(const uint4* __restrict__ src, uint32_t rows, uint32_t row_vecs, const PeerTable tbl,
                       uint32_t* __restrict__ state, uint4* __restrict__ dst, uint32_t world, uint32_t rank,
-                      unsigned long long timeout_ns) {
-  __shared__ uint32_t s_epoch;
+                      unsigned long long timeout_ns, unsigned int* __restrict__ err_word) {
+  __shared__ uint32_t s_epoch, s_lost;
   const uint32_t tid = threadIdx.x, p = blockIdx.x;
   pdl_wait();  // the message comes from the kernel before this one
   if (tid == 0) {
     s_epoch = state[1 + p] + 1;
     state[1 + p] = s_epoch;
+    s_lost = 0;
   }
   __syncthreads();
   const uint32_t epoch = s_epoch, par = epoch & 1u;
@@ -71,7 +72,11 @@ peer_allgather_kernel(const uint4* __restrict__ src, uint32_t rows, uint32_t row
     uint32_t spins = 0;
     while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
       if ((++spins & 1023u) == 0 && global_ns() - t0 > timeout_ns) {
+        // rank p never showed up: count it, raise the sticky host-visible error (quest_device_error) and poison p's
+        // slot below, so the consumer gets NaNs instead of whatever the staging area held
         atomicAdd(state, 1u);
+        device_error_raise(err_word, QUEST_DEVERR_PEER);
+        s_lost = 1;
         break;
       }
     }
@@ -79,9 +84,11 @@ peer_allgather_kernel(const uint4* __restrict__ src, uint32_t rows, uint32_t row
   __syncthreads();
   // unpack rank p's slot of my staging area: dst[row][p][vec] = staging[par][p][row][vec]
   const uint4* mine = tbl.staging[rank] + ((size_t)par * world + p) * msg_vecs;
+  const bool lost = s_lost != 0;
   for (uint32_t j = tid; j < msg_vecs; j += kPeerThreads) {
     const uint32_t row = j / row_vecs, vec = j - row * row_vecs;
-    dst[((size_t)row * world + p) * row_vecs + vec] = __ldcg(mine + j);  // written by another GPU: read at L2, never a stale L1 line
+    // written by another GPU: read at L2, never a stale L1 line.  All-ones is a NaN as fp16 and as fp32.
+    dst[((size_t)row * world + p) * row_vecs + vec] = lost ? make_uint4(~0u, ~0u, ~0u, ~0u) : __ldcg(mine + j);
   }
 }
 
@@ -93,6 +100,7 @@ extern "C" int quest_peer_allgather(const void* src, uint32_t rows, uint32_t row
   if (!src || !peer_staging || !peer_flags || !state || !dst || !rows || !row_bytes) return QUEST_ERR_BAD_ARG;
   if (world < 1 || world > quest::kPeerMax || rank >= world) return QUEST_ERR_UNSUPPORTED;
   if (row_bytes % 16 || ((uintptr_t)src & 15) || ((uintptr_t)dst & 15)) return QUEST_ERR_BAD_ARG;
+  if (quest::device_error_peek() & QUEST_DEVERR_PEER) return QUEST_ERR_DEVICE;  // an earlier exchange lost a rank
   quest::PeerTable tbl = {};
   for (uint32_t p = 0; p < world; ++p) {
     if (!peer_staging[p] || !peer_flags[p] || ((uintptr_t)peer_staging[p] & 15)) return QUEST_ERR_BAD_ARG;
@@ -110,7 +118,7 @@ extern "C" int quest_peer_allgather(const void* src, uint32_t rows, uint32_t row
   cfg.numAttrs = 1;
   const unsigned long long timeout_ns = (unsigned long long)(timeout_ms ? timeout_ms : 2000u) * 1000000ull;
   cudaError_t e = cudaLaunchKernelEx(&cfg, quest::peer_allgather_kernel, (const uint4*)src, rows, row_bytes / 16, tbl,
-                                     (uint32_t*)state, (uint4*)dst, world, rank, timeout_ns);
+                                     (uint32_t*)state, (uint4*)dst, world, rank, timeout_ns, quest::device_error_word());
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }

@@ -147,7 +147,6 @@ class SeqShardedDecode:
         self.ws = torch.zeros(self.lib.quest_decode_workspace_bytes(self.Hq, self.D, nch.value), dtype=torch.uint8,
                               device=self.dev)
         self.sel = torch.full((self.Hq, max(self.k, 1)), -1, dtype=torch.int32, device=self.dev)
-        self.o16 = torch.empty(self.Hq, self.D, dtype=torch.float16, device=self.dev)
         self.rec = torch.zeros(self.Hq * self.D + self.Hq, dtype=torch.float32, device=self.dev)
         self.rec_all = torch.empty(self.R, self.Hq * self.D + self.Hq, dtype=torch.float32, device=self.dev)
         self.out = torch.empty(1, self.Hq, self.D, dtype=torch.float16, device=self.dev)
@@ -205,6 +204,14 @@ class SeqShardedDecode:
             n = int(self.peer_state[:, 0].sum().item())
             if n:
                 raise RuntimeError(f"quest_peer_allgather: {n} waits timed out (a rank did not take part)")
+
+    def _peer_alive(self):
+        """Host-side read of the library's sticky error words (no synchronisation): a peer exchange that lost a rank
+        poisons its output with NaNs and raises QUEST_DEVERR_PEER, so a step after it fails here instead of returning
+        garbage (the exchange itself is also refused with QUEST_ERR_DEVICE from then on)."""
+        if self.lib.quest_device_error() & self._K.DEVERR_PEER:
+            raise RuntimeError("sequence-sharded decode: an earlier quest_peer_allgather timed out waiting for a rank; "
+                               "its outputs were poisoned (quest_device_error_clear() after the group has been repaired)")
 
     # -- per-layout buffers (the layout changes only when a rank gains a page)
     def begin_step(self, scored_pages_per_rank: Sequence[int]):
@@ -282,11 +289,11 @@ class SeqShardedDecode:
         HD = self.Hq * self.D
         last_idx = ic.kv_last_page_idx if self.has_last else 0
         last_len = ic.kv_cache.last_page_len if self.has_last else 0
-        self._K._rc(self.lib.quest_decode_run(q.data_ptr(), self.o16.data_ptr(), self.rec.data_ptr() + HD * 4,
-                                              ic.kv_cache.buf_layer(layer).data_ptr(), self.sel.data_ptr(), self.k, self.k,
-                                              last_idx, last_len, self.Hq, self.Hkv, self.D, self.P, self.ppc,
-                                              self.ws.data_ptr(), self.ws.numel(), self._st()), "decode")
-        self.rec[:HD].copy_(self.o16.view(-1))
+        # fp32 partial straight into the record: no fp16 rounding before the cross-rank merge, no copy
+        self._K._rc(self.lib.quest_decode_run_partial(q.data_ptr(), self.rec.data_ptr(), self.rec.data_ptr() + HD * 4,
+                                                      ic.kv_cache.buf_layer(layer).data_ptr(), self.sel.data_ptr(), self.k, self.k,
+                                                      last_idx, last_len, self.Hq, self.Hkv, self.D, self.P, self.ppc,
+                                                      self.ws.data_ptr(), self.ws.numel(), self._st()), "decode")
         return self.rec
 
     def merge(self, records: torch.Tensor) -> torch.Tensor:
@@ -301,6 +308,7 @@ class SeqShardedDecode:
         matter on the last rank only.  Returns fp16 [1, Hq, D], identical on every rank."""
         msg = self.candidates(q, k_new, v_new, layer)
         if self.exchange == "peer":
+            self._peer_alive()
             if self.k:
                 self._peer_gather("cand", msg, self.Hq, self.c_max * 2, self.all_s)
             self.select(None)

@@ -4,11 +4,33 @@ from typing import Optional
 
 import torch
 
+import os
+
 import quest_b200._kernels as _kernels
 from quest_b200.utils.utils import TensorLayout
 from quest_b200.utils.kv_cache import KvCache
 from quest_b200.utils.controller import InferenceController
 from quest_b200.utils.decode_wrapper import BatchDecodeWithPagedKVCacheWrapper
+
+class _NoNvtx:
+    @staticmethod
+    def range_push(name):
+        pass
+
+    @staticmethod
+    def range_pop():
+        pass
+
+
+# NVTX ranges with the reference's names (quest/models/QuestAttention.py:87-150) around the decode operators.  Off by
+# default (a push/pop pair costs about a microsecond of host time per range, 8 per layer); QUEST_NVTX=1 or enable_nvtx().
+_nvtx = torch.cuda.nvtx if os.environ.get("QUEST_NVTX", "0") == "1" else _NoNvtx
+
+
+def enable_nvtx(on: bool = True):
+    global _nvtx
+    _nvtx = torch.cuda.nvtx if on else _NoNvtx
+
 
 __all__ = [
     'TensorLayout',
@@ -21,6 +43,7 @@ __all__ = [
     "decode_topk",
     "decode_sparse_attn",
     "decode_layer_step",
+    "enable_nvtx",
     "rms_norm_forward",
     "apply_rope_in_place",
 ]
@@ -165,8 +188,12 @@ def decode_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iContro
     budget to enforce (need_estimate() false) it is append_kv + attention over all pages, as the reference does.
     ``out`` (optional, like q): written instead of a fresh tensor."""
     if not iController.need_estimate():
+        _nvtx.range_push("append_kv")
         append_kv(k, v, iController, layer_idx)
+        _nvtx.range_pop()
+        _nvtx.range_push("full_attn")
         o = decode_sparse_attn(q, iController, layer_idx, iController.kv_indices_without_last)
+        _nvtx.range_pop()
         return o if out is None else out.copy_(o)
     st = iController._step
     if st is None:
@@ -178,8 +205,15 @@ def decode_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iContro
     o = torch.empty_like(q) if out is None else out
     if out is not None and (out.shape != st.qshape or out.dtype != st.dtype or out.device != st.device or not out.is_contiguous()):
         raise RuntimeError("decode_layer_step: out must look like q")
+    # NVTX range names of the reference (quest/models/QuestAttention.py:98-150: append_kv, estimate, topk, approx_attn), nested
+    # because the four operators are one native call here: a timeline of this path lines up with one of the reference
+    _nvtx.range_push("append_kv")
+    _nvtx.range_push("estimate")
+    _nvtx.range_push("topk")
+    _nvtx.range_push("approx_attn")
     rc = st.fn(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), st.kv_ptrs[layer_idx], *st.mid,
                st.meta_ptrs[layer_idx], *st.tail, torch.cuda.current_stream().cuda_stream)
+    _nvtx.range_pop(), _nvtx.range_pop(), _nvtx.range_pop(), _nvtx.range_pop()
     if rc:
         _kernels._rc(rc, "decode_layer_step")
     return o

@@ -170,6 +170,14 @@ def test_peer_allgather_kernel_layout_and_epochs():
                                         R, 0, 50, torch.cuda.current_stream().cuda_stream) == 0
     torch.cuda.synchronize()
     assert state[0].tolist()[0] == 2
+    # ... loudly: the lost ranks' slots are poisoned (all-ones = NaN as fp16 / fp32), the sticky device error is raised and the
+    # next exchange is refused until it is cleared
+    d0 = dst[0].cpu()
+    assert bool((d0[:, 1:] == 255).all()) and torch.equal(d0[:, 0], src[0].cpu())
+    assert lib.quest_device_error() & K.DEVERR_PEER
+    assert lib.quest_peer_allgather(src[0].data_ptr(), rows, row_bytes, ps, pf, state[0].data_ptr(), dst[0].data_ptr(), R, 0, 50, 0) == -4
+    lib.quest_device_error_clear()
+    assert lib.quest_device_error() == 0
     # argument checks
     assert lib.quest_peer_allgather(src[0].data_ptr(), rows, 40, ps, pf, state[0].data_ptr(), dst[0].data_ptr(), R, 0, 50, 0) == -1
     assert lib.quest_peer_allgather(src[0].data_ptr(), rows, row_bytes, ps, pf, state[0].data_ptr(), dst[0].data_ptr(), 9, 0, 50, 0) == -2
