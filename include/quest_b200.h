@@ -32,6 +32,7 @@ extern "C" {
 #define QUEST_ERR_WORKSPACE (-3)    /* caller-provided workspace too small                       */
 #define QUEST_ERR_DEVICE (-4)       /* an earlier kernel of this library gave up on a bounded wait: its
                                        output was not valid (see quest_device_error)             */
+#define QUEST_ERR_SCRATCH_LIMIT (-5) /* quest_decode_run_static: the plan needs more than the built-in scratch array */
 
 /* Library identification: "quest_b200 <version> sm_100a". */
 const char* quest_version(void);
@@ -141,6 +142,25 @@ int quest_decode_run_partial(const void* q, float* o_partial, float* lse,
                              uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
                              uint32_t page_size, uint32_t pages_per_chunk,
                              void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- sparse paged decode without any allocation ----------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same computation and
+ * arguments as quest_decode_run, minus the workspace: the split-KV scratch is a file-scope device array inside the
+ * library (csrc/decode.cu) of quest_decode_static_scratch_bytes() = 4 MiB, which every GPU that loads the library
+ * holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine); it enqueues
+ * one small cudaMemsetAsync (the words that must start at zero) and the kernel.
+ * Limits: a plan whose quest_decode_workspace_bytes(num_qo_heads, head_dim, num_chunks) exceeds the array is refused
+ * with QUEST_ERR_SCRATCH_LIMIT (raise pages_per_chunk, or use quest_decode_run).  ALL calls on a GPU share the one
+ * array, which keeps the last call's contents: calls that overlap on the GPU (two streams, or two processes' worth of
+ * streams in one context) RACE -- serialise them on one stream.  The first call on each device resolves the array's
+ * address (cudaGetSymbolAddress, with that device current); make that first call outside stream capture. */
+size_t quest_decode_static_scratch_bytes(void);
+int quest_decode_run_static(const void* q, void* o, float* lse,
+                            const void* kv_data, const int32_t* indices, uint32_t idx_row_stride,
+                            uint32_t num_sel_pages, uint32_t last_page_idx, uint32_t last_page_len,
+                            uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                            uint32_t page_size, uint32_t pages_per_chunk, void* stream);
 
 /* ---- fused layer step: estimate -> top-k -> sparse decode ---------------------------------------
  * The three calls QuestAttention.forward makes per layer per token (quest/models/QuestAttention.py:

@@ -32,6 +32,8 @@ SIGNATURES = {
     "quest_decode_workspace_bytes": (_sz, [_u32, _u32, _u32]),
     "quest_decode_run": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_decode_run_partial": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
+    "quest_decode_static_scratch_bytes": (_sz, []),
+    "quest_decode_run_static": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp]),
     "quest_sparse_decode_step": (_c.c_int, [_vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_decode_layer_step": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32,
                                            _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
@@ -126,6 +128,10 @@ def _rc(code, op):
             raise RuntimeError(f"{op} refused: an earlier kernel of this library gave up on a bounded wait and its output "
                                f"was not valid (quest_device_error() = {load_library().quest_device_error()}); "
                                "quest_device_error_clear() re-arms the entry point")
+        if code == -5:
+            raise RuntimeError(f"{op} refused: the decode plan needs more scratch than the library's built-in array "
+                               f"({load_library().quest_decode_static_scratch_bytes()} bytes); raise pages_per_chunk or use the "
+                               "workspace-taking entry point")
         raise RuntimeError(f"{op} failed with argument error {code} "
                            "(-1 bad argument, -2 unsupported shape, -3 workspace too small)")
 

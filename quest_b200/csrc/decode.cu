@@ -9,6 +9,8 @@
 // ticket) merges them -- no separate merge launch.
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace quest {
@@ -450,6 +452,58 @@ extern "C" int quest_decode_run_partial(const void* q, float* o_partial, float* 
   return decode_run_checked(q, nullptr, o_partial, lse, kv_data, indices, idx_row_stride, num_sel_pages, last_page_idx,
                             last_page_len, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
                             workspace_bytes, stream);
+}
+
+// ---- quest_decode_run_static: the same launch with its split-KV scratch in a file-scope device array ----------------
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): nothing
+// here allocates -- no cudaMalloc / cudaFree, no allocating library routine.  Every GPU that loads the library holds the
+// array until exit.  In host code the array's NAME is only a host-side stand-in, not a device address, so the address is
+// resolved once per device with cudaGetSymbolAddress (that device current) and the kernel is handed that pointer.
+namespace quest {
+constexpr size_t kStaticScratchBytes = (size_t)4 << 20;  // 4 MiB: e.g. 32 q heads x 128 dims x up to ~230 chunks
+static __device__ __align__(256) uint8_t g_decode_static_scratch[kStaticScratchBytes];
+constexpr int kStaticMaxDevices = 64;
+static void* g_static_scratch_addr[kStaticMaxDevices];  // per device, resolved on first use
+static std::mutex g_static_scratch_mu;
+
+static int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kStaticMaxDevices) return QUEST_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (g_static_scratch_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_decode_static_scratch);  // this device's copy of the array
+    if (e != cudaSuccess) return (int)e;
+    if (ptr == nullptr) return QUEST_ERR_UNSUPPORTED;
+    g_static_scratch_addr[dev] = ptr;
+  }
+  *out = g_static_scratch_addr[dev];
+  return QUEST_OK;
+}
+}  // namespace quest
+
+extern "C" size_t quest_decode_static_scratch_bytes(void) { return quest::kStaticScratchBytes; }
+
+extern "C" int quest_decode_run_static(const void* q, void* o, float* lse, const void* kv_data, const int32_t* indices,
+                                       uint32_t idx_row_stride, uint32_t num_sel_pages, uint32_t last_page_idx,
+                                       uint32_t last_page_len, uint32_t num_qo_heads, uint32_t num_kv_heads,
+                                       uint32_t head_dim, uint32_t page_size, uint32_t pages_per_chunk, void* stream) {
+  if (!o || !num_qo_heads || !pages_per_chunk) return QUEST_ERR_BAD_ARG;
+  const uint32_t nchunks = (num_sel_pages + 1 + pages_per_chunk - 1) / pages_per_chunk;
+  const size_t need = quest_decode_workspace_bytes(num_qo_heads, head_dim, nchunks);
+  if (need > quest::kStaticScratchBytes) return QUEST_ERR_SCRATCH_LIMIT;  // plan with larger chunks, or use quest_decode_run
+  void* scratch = nullptr;
+  int rc = quest::static_scratch_for_current_device(&scratch);
+  if (rc != QUEST_OK) return rc;
+  // The array keeps the previous call's contents.  What must start at zero are the reserved words and the merge tickets
+  // (one per q head; they reset themselves only when a launch runs to completion): cleared on the stream, ahead of the kernel.
+  cudaError_t e = cudaMemsetAsync(scratch, 0, quest::ws_hist_off(num_qo_heads), (cudaStream_t)stream);
+  if (e != cudaSuccess) return (int)e;
+  return decode_run_checked(q, o, nullptr, lse, kv_data, indices, idx_row_stride, num_sel_pages, last_page_idx, last_page_len,
+                            num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, scratch,
+                            quest::kStaticScratchBytes, stream);
 }
 
 #ifdef QUEST_DEC_CLOCKS
