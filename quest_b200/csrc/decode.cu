@@ -33,7 +33,10 @@ __device__ unsigned long long g_dec_clk[4096 * 8];
 #ifndef QUEST_DEC_MINBLOCKS
 #define QUEST_DEC_MINBLOCKS 7  // resident CTAs per SM the kernel is compiled for (72 registers); 8 = 64 registers, A/B in profiles/
 #endif
-constexpr int kDecThreads = 128;
+#ifndef QUEST_DEC_THREADS
+#define QUEST_DEC_THREADS 128  // threads per decode CTA; A/B builds: -DQUEST_DEC_THREADS=256 -DQUEST_DEC_MINBLOCKS=3
+#endif
+constexpr int kDecThreads = QUEST_DEC_THREADS;
 constexpr int kDecWarps = kDecThreads / 32;
 constexpr float kNegBig = -1e30f;
 

@@ -222,6 +222,21 @@ static int launch_topk_cluster(const void* scores, const int32_t* in_idx, uint32
 // read: the totals are back at rest when the kernel ends.  Rows of up to 4*G*512 pages (G = 4: 8192).
 constexpr int kHistThreads = 512;
 
+// -DQUEST_TOPK_HIST_CLOCKS: every CTA stamps %globaltimer at its phase boundaries (tools/step_timeline.py)
+#ifdef QUEST_TOPK_HIST_CLOCKS
+__device__ unsigned long long g_topk_hist_clk[256 * 4];
+#define TH_STAMP(i)                                                                \
+  do {                                                                             \
+    if (threadIdx.x == 0) {                                                        \
+      unsigned long long t_;                                                       \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                       \
+      g_topk_hist_clk[(blockIdx.x & 255) * 4 + (i)] = t_;                          \
+    }                                                                              \
+  } while (0)
+#else
+#define TH_STAMP(i) do { } while (0)
+#endif
+
 template <int G>
 __global__ void __launch_bounds__(kHistThreads)
 topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ hist_, const int32_t* __restrict__ in_idx_,
@@ -239,7 +254,9 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
   pdl_trigger();
 #endif
   if (t < 32) s_sub[t] = 0;
+  TH_STAMP(0);
   pdl_wait();  // scores and bin totals come from the estimate kernel
+  TH_STAMP(1);
   if (ba.descs != nullptr) {  // descriptor mode, as in topk_fast_kernel
     const SeqDesc* d = ba.descs + blockIdx.y;
     len = d->num_kv_pages - 1;
@@ -356,7 +373,14 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
     gt_before += gt;
     eq_before += eq;
   }
+  TH_STAMP(2);
 }
+
+#ifdef QUEST_TOPK_HIST_CLOCKS
+extern "C" int quest_debug_topk_hist_clocks(unsigned long long* host_out, uint32_t n_ctas) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_topk_hist_clk, (size_t)n_ctas * 4 * 8);
+}
+#endif
 
 template <int G>
 static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,

@@ -1,5 +1,5 @@
 """Per-CTA phase timeline of one layer step (estimate -> top-k -> decode) inside the bench graph:
-  QUEST_EXTRA_FLAGS="-DQUEST_DEC_CLOCKS -DQUEST_EST_CLOCKS" QUEST_LIB_SUFFIX=_dbg bash quest_b200/csrc/build.sh   (here)
+  QUEST_EXTRA_FLAGS="-DQUEST_DEC_CLOCKS -DQUEST_EST_CLOCKS -DQUEST_TOPK_HIST_CLOCKS" QUEST_LIB_SUFFIX=_dbg bash quest_b200/csrc/build.sh   (here)
   QUEST_B200_LIB=quest_b200/libquest_b200_dbg.so python tools/step_timeline.py                                     (GPU box)
 Replays the bench workload's 32-layer graph and reads the %globaltimer stamps of the LAST layer's launches (the stamps of
 earlier layers are overwritten), all on one clock: us relative to the median start of the estimate CTAs."""
@@ -37,10 +37,19 @@ def main():
     assert lib.quest_debug_estimate_clocks(be, ne) == 0 and lib.quest_debug_decode_clocks(bd, nd) == 0
     te = np.frombuffer(be, dtype=np.uint64).reshape(ne, 4).astype(np.int64)[:296]
     td = np.frombuffer(bd, dtype=np.uint64).reshape(nd, 8).astype(np.int64)
+    tt = None
+    if hasattr(lib, "quest_debug_topk_hist_clocks"):
+        bt = (ctypes.c_ulonglong * (32 * 4))()
+        lib.quest_debug_topk_hist_clocks.restype = ctypes.c_int
+        assert lib.quest_debug_topk_hist_clocks(bt, 32) == 0
+        tt = np.frombuffer(bt, dtype=np.uint64).reshape(32, 4).astype(np.int64)
     t0 = np.median(te[:, 0])
     print(f"layer step timeline (last layer of the graph), us relative to the median estimate CTA start")
     print(f"{'event':30s} {'n':>5s} {'min':>8s} {'p10':>8s} {'p50':>8s} {'p90':>8s} {'max':>8s}")
-    for names, t in ((EST, te), (DEC, td)):
+    TOPK = ["topk: cta start", "topk: launch wait done", "topk: ids written"]
+    for names, t in ((EST, te), (TOPK, tt), (DEC, td)):
+        if t is None:
+            continue
         order = range(len(names))
         for e in order:
             v = t[:, e]
