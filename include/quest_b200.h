@@ -241,6 +241,33 @@ int quest_prefill(const void* q, void* o, uint32_t qo_len,
                   uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
                   uint32_t page_size, void* stream);
 
+/* ---- prefill producer and whole prefill layer step -------------------------
+ * quest_rope_append_prefill replaces, in ONE launch, the reference's two launches ahead of prefill attention:
+ * apply_rope_in_place over q and k (bsk_ops.h:41-48, quest/ops/csrc/page.cu:212-253, decode_page.cuh:644-728) followed by
+ * append_kv_cache_prefill (bsk_ops.h:50-62, page.cu:101-210, decode_page.cuh:471-562).  q [append_len, num_qo_heads, head_dim]
+ * is rotated in place at positions kv_len - append_len ..; k [append_len, num_kv_heads, head_dim] is rotated in registers and
+ * the rounded result is scattered into the pages and folded into the pages' min/max metadata, v is copied; the pool, the
+ * metadata and q come out bit-identical to the two-call sequence.  k itself is left untouched unless flags has
+ * QUEST_PF_WRITE_BACK_K (the reference's in-place side effect; nothing on the path reads k again).  Cache arguments as for
+ * quest_append_prefill: the page counts and kv_last_page_len already include the new tokens. */
+#define QUEST_PF_WRITE_BACK_K 1u
+int quest_rope_append_prefill(void* q, void* k, const void* v, uint32_t append_len,
+                              void* kv_data, const int32_t* kv_indices, uint32_t num_kv_pages,
+                              uint32_t kv_last_page_len,
+                              void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                              uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                              float rope_scale, float rope_theta, uint32_t flags, void* stream);
+/* The prompt's whole attention layer -- quest/models/QuestAttention.py:85-99 (apply_rope_in_place, append_kv,
+ * prefill_forward: three operator calls, three launches and a host sync at batch_prefill.cu:84) -- as one call and two launches
+ * chained with programmatic dependent launch: quest_rope_append_prefill, then causal quest_prefill of the rotated q over the
+ * pages into o [append_len, num_qo_heads, head_dim]. */
+int quest_prefill_layer_step(void* q, void* k, const void* v, void* o, uint32_t append_len,
+                             void* kv_data, const int32_t* kv_indices, uint32_t num_kv_pages,
+                             uint32_t kv_last_page_len,
+                             void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                             uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                             float rope_scale, float rope_theta, uint32_t flags, void* stream);
+
 /* ---- combine of partial attention states (sequence-sharded multi-GPU path) ----------------------
  * Merges n partial states (o_i fp32 [n, num_heads, head_dim] normalised, lse_i fp32 [n, num_heads]
  * base-2) into o fp16 [num_heads, head_dim]: flashinfer state.cuh:53-62 / cascade.cuh:279-340.
@@ -290,6 +317,7 @@ void quest_device_error_clear(void);
 #define QUEST_DBG_TOPK_NO_CLUSTER 4  /* 1: one CTA per top-k row for every length                              */
 #define QUEST_DBG_TOPK_GENERIC 5     /* 1: shared-memory-key top-k kernel for every length                     */
 #define QUEST_DBG_TOPK_NO_HIST 6     /* 1: layer step selects with the stand-alone top-k kernels (no bin totals) */
+#define QUEST_DBG_EST_PER_Q 7        /* 1: GQA groups of 2 / 4 use one lane row per q head (the round-1 layout)  */
 #define QUEST_DBG_COUNT 8
 int quest_debug_set_option(int option, int value);
 

@@ -41,6 +41,10 @@ SIGNATURES = {
                                                  _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_rope_decode_batch": (_c.c_int, [_vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _f32, _vp]),
     "quest_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _c.c_int, _u32, _u32, _u32, _u32, _vp]),
+    "quest_rope_append_prefill": (_c.c_int, [_vp, _vp, _vp, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _u32,
+                                             _f32, _f32, _u32, _vp]),
+    "quest_prefill_layer_step": (_c.c_int, [_vp, _vp, _vp, _vp, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _u32,
+                                            _u32, _f32, _f32, _u32, _vp]),
     "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _u32, _vp, _vp, _u32, _u32, _vp]),
     "quest_peer_staging_bytes": (_sz, [_u32, _u32, _u32]),
     "quest_peer_allgather": (_c.c_int, [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _vp]),
@@ -73,7 +77,7 @@ def load_library():
 
 
 # include/quest_b200.h QUEST_DBG_*: explicit test / A-B switches (the library never reads the environment)
-DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC, DBG_TOPK_NO_HIST = range(7)
+DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC, DBG_TOPK_NO_HIST, DBG_EST_PER_Q = range(8)
 DEVERR_PREFILL, DEVERR_PEER = 1, 2
 
 
@@ -275,6 +279,48 @@ def prefill_with_paged_kv_cache(q, kv_data, kv_indices, kv_last_page_len, causal
     _rc(load_library().quest_prefill(q.data_ptr(), o.data_ptr(), q.size(0), kv_data.data_ptr(), kv_indices.data_ptr(),
                                      kv_indices.size(0), int(kv_last_page_len), 1 if causal else 0, q.size(1), Hkv, D,
                                      P, _stream()), "prefill_with_paged_kv_cache")
+    return o
+
+
+PF_WRITE_BACK_K = 1  # include/quest_b200.h QUEST_PF_WRITE_BACK_K
+
+
+def _prefill_producer_checks(q, k, v, kv_data, kv_indices, metadata_data, metadata_indices, op):
+    _check_input(q, "q")
+    _check(q.dim() == 3, "q must be a 3D tensor")
+    P, H, D = _append_checks(k, v, kv_data, kv_indices, kv_indices, metadata_data, metadata_indices, metadata_indices, _NHD, op)
+    _check(q.size(0) == k.size(0), "CHECK_EQ(q.size(0), k.size(0)) failed")
+    _check(q.size(2) == D, "CHECK_EQ(q.size(2), kv_data.size(4)) failed")
+    _check_half(q, op)
+    return P, H, D
+
+
+def rope_append_kv_cache_prefill(q, k, v, kv_data, kv_indices, kv_last_page_len, metadata_data, metadata_indices, rope_scale,
+                                 rope_theta, write_back_k=False):
+    """apply_rope_in_place(q, k) + append_kv_cache_prefill(k, v) in one launch (reference quest/ops/csrc/page.cu:212-253 then
+    :101-210): q is rotated in place, the rotated k goes straight into the pages and their min/max metadata; k itself is
+    rewritten only with write_back_k.  The RoPE position of the first new token is the cache length before the append."""
+    P, H, D = _prefill_producer_checks(q, k, v, kv_data, kv_indices, metadata_data, metadata_indices, "rope_append_kv_cache_prefill")
+    _rc(load_library().quest_rope_append_prefill(q.data_ptr(), k.data_ptr(), v.data_ptr(), k.size(0), kv_data.data_ptr(),
+                                                 kv_indices.data_ptr(), kv_indices.size(0), int(kv_last_page_len),
+                                                 metadata_data.data_ptr(), metadata_indices.data_ptr(), metadata_indices.size(0),
+                                                 q.size(1), H, D, P, float(rope_scale), float(rope_theta),
+                                                 PF_WRITE_BACK_K if write_back_k else 0, _stream()), "rope_append_kv_cache_prefill")
+
+
+def prefill_layer_step(q, k, v, kv_data, kv_indices, kv_last_page_len, metadata_data, metadata_indices, rope_scale, rope_theta,
+                       write_back_k=False):
+    """The prompt's attention layer in one native call (reference quest/models/QuestAttention.py:85-99: apply_rope_in_place,
+    append_kv, prefill_forward): fused RoPE + append + metadata, then causal paged prefill, chained with programmatic
+    dependent launch.  Returns o like prefill_with_paged_kv_cache."""
+    P, H, D = _prefill_producer_checks(q, k, v, kv_data, kv_indices, metadata_data, metadata_indices, "prefill_layer_step")
+    o = torch.empty_like(q)
+    _rc(load_library().quest_prefill_layer_step(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), k.size(0),
+                                                kv_data.data_ptr(), kv_indices.data_ptr(), kv_indices.size(0),
+                                                int(kv_last_page_len), metadata_data.data_ptr(), metadata_indices.data_ptr(),
+                                                metadata_indices.size(0), q.size(1), H, D, P, float(rope_scale),
+                                                float(rope_theta), PF_WRITE_BACK_K if write_back_k else 0, _stream()),
+        "prefill_layer_step")
     return o
 
 

@@ -192,3 +192,19 @@ extern "C" int quest_decode_layer_step_batch(const void* q, const void* k_new, c
   return quest::decode_batch(q, o, topk_idx, k, num_qo_heads, num_kv_heads, head_dim, page_size, pages_per_chunk, workspace,
                              ba, batch, s);
 }
+
+// The prompt's attention layer as one call: fused RoPE + append + metadata, then the causal paged prefill, chained with
+// programmatic dependent launch (the prefill kernel's barrier / tensor-memory set-up runs under the producer's tail).
+extern "C" int quest_prefill_layer_step(void* q, void* k, const void* v, void* o, uint32_t append_len, void* kv_data,
+                                        const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_len,
+                                        void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                                        uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                                        float rope_scale, float rope_theta, uint32_t flags, void* stream) {
+  if (!o) return QUEST_ERR_BAD_ARG;
+  int rc = quest_rope_append_prefill(q, k, v, append_len, kv_data, kv_indices, num_kv_pages, kv_last_page_len, meta_data,
+                                     meta_indices, num_meta_pages, num_qo_heads, num_kv_heads, head_dim, page_size, rope_scale,
+                                     rope_theta, flags, stream);
+  if (rc != QUEST_OK) return rc;
+  return quest_prefill(q, o, append_len, kv_data, kv_indices, num_kv_pages, kv_last_page_len, 1, num_qo_heads, num_kv_heads,
+                       head_dim, page_size, stream);
+}

@@ -54,6 +54,17 @@ __device__ __forceinline__ H8 ld_stream(const void* p) {
                : "l"(p));
   return r;
 }
+// The same load without .nc: ptxas moves non-coherent (read-only) loads freely, also DOWN across griddepcontrol.wait and CTA
+// barriers; a kernel that wants loads in flight BEFORE its programmatic-dependency wait issues them with this form.
+__device__ __forceinline__ H8 ld_stream_ordered(const void* p) {
+  H8 r;
+  uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3])
+               : "l"(p)
+               : "memory");
+  return r;
+}
 // Predicated form: r keeps its previous contents when !pred (no memory access is made).
 __device__ __forceinline__ void ld_stream_if(H8& r, const void* p, bool pred) {
   uint32_t* u = reinterpret_cast<uint32_t*>(&r);
@@ -85,6 +96,38 @@ __device__ __forceinline__ float lg2(float x) {
   return y;
 }
 
+// c + a.lo*b.lo, then + a.hi*b.hi, each a single-rounding fp32 FMA whose multiplicands are fp16 (PTX fma.rn.f32.f16, sm_100+:
+// one FHFMA each, operands taken from the .H0 / .H1 halves of the packed registers, no conversion instructions).  The product of
+// two halves is exact in fp32, so this is bit-identical to __fmaf_rn(float(a), float(b), c) in the same order.
+__device__ __forceinline__ float fma_h2_seq(uint32_t a, uint32_t b, float c) {
+#ifdef QUEST_NO_FHFMA  // A/B build: convert, then two FFMAs (same bits)
+  const float2 fa = __half22float2(*reinterpret_cast<const __half2*>(&a));
+  const float2 fb = __half22float2(*reinterpret_cast<const __half2*>(&b));
+  return __fmaf_rn(fa.y, fb.y, __fmaf_rn(fa.x, fb.x, c));
+#else
+  float d;
+  asm("{\n.reg .b16 al, ah, bl, bh;\n.reg .f32 t;\nmov.b32 {al, ah}, %1;\nmov.b32 {bl, bh}, %2;\n"
+      "fma.rn.f32.f16 t, al, bl, %3;\nfma.rn.f32.f16 %0, ah, bh, t;\n}"
+      : "=f"(d)
+      : "r"(a), "r"(b), "f"(c));
+  return d;
+#endif
+}
+
+// Loads of data the launch immediately before this one produced (q, page ids): plain ld.global, never .nc -- under programmatic
+// dependent launch the kernel's lifetime starts before griddepcontrol.wait, the data is not read-only over that lifetime, and
+// ptxas does hoist .nc loads above the wait (it did for the estimate kernel's q in the round-1 build).
+__device__ __forceinline__ uint4 ld_ordered16(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_ordered32(const void* p) {
+  uint32_t v;
+  asm volatile("ld.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // Programmatic dependent launch: wait for the producer grid / release the consumer grid.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -109,6 +152,32 @@ __device__ __forceinline__ H8 h8_fill(float x) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) r.h[i] = v;
   return r;
+}
+
+// Llama rotate-half RoPE of 8 consecutive dims (reference decode_page.cuh:644-728, flashinfer rope.cuh:64-83): a = the dims
+// themselves, b = their partners D/2 away; out = a*cos + (lo_half ? -b : b)*sin at angle pos*freq[i], with the reference's fast
+// intrinsics.  Written with explicit fp32 intrinsics so that every kernel that rotates (rope_norm.cu, page.cu) rounds alike.
+__device__ __forceinline__ H8 rope_rotate8(const float a[8], const float b[8], bool lo_half, float pos, const float freq[8]) {
+  H8 out;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float r2[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int e = 2 * i + j;
+      float sn, cs;
+      __sincosf(__fmul_rn(pos, freq[e]), &sn, &cs);
+      r2[j] = __fmaf_rn(a[e], cs, __fmul_rn(lo_half ? -b[e] : b[e], sn));
+    }
+    out.h[i] = __floats2half2_rn(r2[0], r2[1]);
+  }
+  return out;
+}
+// freq_i = (1/scale) * (1/theta)^(2 (i mod D/2) / D) for the 8 dims starting at d0
+template <int D>
+__device__ __forceinline__ void rope_freq8(uint32_t d0, float rcp_scale, float rcp_theta, float freq[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) freq[i] = rcp_scale * __powf(rcp_theta, float(2 * ((d0 + i) % (D / 2))) / float(D));
 }
 
 constexpr float kMaxHalf = 65504.f;  // CUDART_MAX_NORMAL_FP16 (decode_page.cuh:430-431)

@@ -98,17 +98,15 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
 
   D_STAMP(0);
   const int32_t* idx_row = indices + (size_t)h * idx_stride;
-  float qv[8];
+  uint32_t qh[4];  // this lane's 8 q dims as packed halves: q.k runs on mixed-precision FMAs (fp16 x fp16 + fp32, exact products)
   pdl_wait();  // q, the page ids (top-k kernel) and the last page's new row (append) come from earlier kernels
   D_STAMP(1);
   for (uint32_t i = tid; i < npg; i += kThreads)
-    s_pages[i] = pg0 + i < n_sel ? __ldg(idx_row + pg0 + i) : (int32_t)last_page_idx;
+    s_pages[i] = pg0 + i < n_sel ? (int32_t)ld_ordered32(idx_row + pg0 + i) : (int32_t)last_page_idx;
   {
-    const H8 qh = ld_plain(q + (size_t)h * D + lir * 8);
-    h8_to_float(qh, qv);
+    const uint4 raw = ld_ordered16(q + (size_t)h * D + lir * 8);
+    qh[0] = raw.x, qh[1] = raw.y, qh[2] = raw.z, qh[3] = raw.w;
   }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) qv[i] *= sm_scale_log2;
   __syncthreads();
   D_STAMP(2);  // page ids and q are in
 #if QUEST_TRIG_DEC
@@ -167,14 +165,12 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
     float mt = m;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      float kf[8];
-      h8_to_float(kk[st + j], kf);
       float a = 0.f;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) a = fmaf(qv[i], kf[i], a);
+      for (int i = 0; i < 4; ++i) a = fma_h2_seq(qh[i], *reinterpret_cast<const uint32_t*>(&kk[st + j].h[i]), a);
 #pragma unroll
       for (int off = LPR / 2; off > 0; off >>= 1) a += __shfl_xor_sync(0xffffffffu, a, off);
-      sc[j] = (okm >> (st + j)) & 1u ? a : kNegBig;
+      sc[j] = (okm >> (st + j)) & 1u ? a * sm_scale_log2 : kNegBig;  // softmax scale and log2(e) applied to the fp32 dot product
       mt = fmaxf(mt, sc[j]);
     }
     const float scale = ex2(m - mt);

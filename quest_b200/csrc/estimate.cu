@@ -16,7 +16,8 @@
 //   max(q*kmax, q*kmin) == q * (q >= 0 ? max(kmax,kmin) : min(kmax,kmin))
 // for all finite inputs with no assumption that kmax >= kmin (signed zeros cannot change the running sum,
 // which is never -0).  The select runs on packed halves (one LOP3 per pair against a sign mask), and
-// s + q*x is one FFMA because the product is exact.  With QUEST_EST_META_ORDERED the caller promises
+// s + q*x is one mixed-precision FMA (fma.rn.f32.f16 -> FHFMA: fp16 multiplicands straight from the packed registers,
+// fp32 addend, one rounding) because the product is exact: no fp16 -> fp32 conversion instructions at all.  With QUEST_EST_META_ORDERED the caller promises
 // kmax >= kmin elementwise (true for metadata written by append_kv) and the HMNMX2 pair is skipped.
 // The transposed butterfly adds the same operand pairs in the same order as the reference's
 // shfl_xor(8,4,2,1) tree (own + partner at every level), so the fp32 sum is unchanged.
@@ -39,8 +40,8 @@ estimate_rows_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
   constexpr int LPR = D / 8;     // lanes per metadata row (reference bdx)
   constexpr int RPL = 32 / LPR;  // rows per warp-wide load
   extern __shared__ __align__(16) uint8_t est_smem[];
-  float* q_s = reinterpret_cast<float*>(est_smem);                          // [Hq][D] fp32
-  uint32_t* m_s = reinterpret_cast<uint32_t*>(q_s + (size_t)Hq * D);        // [Hq][D/2] 0xffff where q >= 0
+  uint32_t* q_s = reinterpret_cast<uint32_t*>(est_smem);                    // [Hq][D/2] packed halves (region sized for fp32)
+  uint32_t* m_s = q_s + (size_t)Hq * D;                                     // [Hq][D/2] 0xffff where q >= 0
   int32_t* idx_s = reinterpret_cast<int32_t*>(m_s + (size_t)Hq * D / 2);    // [ceil(len/P)] metadata page table
   const uint32_t G = kG ? kG : Hq / Hkv;  // kG = 0: any group size
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -79,12 +80,9 @@ estimate_rows_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
 
   if (meta_stable) pdl_wait();
   for (uint32_t i = tid; i < Hq * D / 2; i += kEstThreads) {
-    const __half2 h2 = reinterpret_cast<const __half2*>(q)[i];
-    const float2 f = __half22float2(h2);
-    q_s[2 * i] = f.x;
-    q_s[2 * i + 1] = f.y;
     // sign-bit test: for q = -0 either choice gives a +-0 product, which cannot change the sum
-    const uint32_t bits = *reinterpret_cast<const uint32_t*>(&h2);
+    const uint32_t bits = reinterpret_cast<const uint32_t*>(q)[i];
+    q_s[i] = bits;
     m_s[i] = ((bits & 0x8000u) ? 0u : 0xffffu) | ((bits & 0x80000000u) ? 0u : 0xffff0000u);
   }
   __syncthreads();
@@ -113,19 +111,16 @@ estimate_rows_kernel(const __half* __restrict__ q, __half* __restrict__ o, uint3
 #pragma unroll
       for (uint32_t g = 0; g < G; ++g) {
         const uint32_t h = kvh * G + g;
-        const float4* qp = reinterpret_cast<const float4*>(q_s + h * D + lir * 8);
-        const float4 q0 = qp[0], q1 = qp[1];
+        const uint4 qq = *reinterpret_cast<const uint4*>(q_s + h * (D / 2) + lir * 4);
         const uint4 msk = *reinterpret_cast<const uint4*>(m_s + h * (D / 2) + lir * 4);
-        const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        const uint32_t qh[4] = {qq.x, qq.y, qq.z, qq.w};
         const uint32_t mk[4] = {msk.x, msk.y, msk.z, msk.w};
         float sacc = 0.f;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const uint32_t sel = (hi[i] & mk[i]) | (lo[i] & ~mk[i]);
-          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&sel));
           // reference order (decode_attn.cuh:152-160): 8 sequential fp32 adds of exact products
-          sacc = __fmaf_rn(qv[2 * i], f.x, sacc);
-          sacc = __fmaf_rn(qv[2 * i + 1], f.y, sacc);
+          sacc = fma_h2_seq(qh[i], sel, sacc);
         }
 #pragma unroll
         for (int off = LPR / 2; off > 0; off >>= 1) sacc = __fadd_rn(sacc, __shfl_xor_sync(0xffffffffu, sacc, off));
@@ -162,6 +157,9 @@ __device__ __forceinline__ float reduce4_transposed(const float a[4], uint32_t l
 // kv-head row (the two rows of one warp-wide load coalesce; rows in different warps are served by L2), so the
 // arithmetic per lane and the refill-after-use ring are exactly the MHA ones and DRAM still sees every byte once.
 // kG = 0: any group size, one lane row per kv head looping over its q heads, q/mask in smem.
+// kG = 100 + G (G = 2, 4): one lane row per KV head with the q rows and sign masks of its G q heads in registers (8 registers per
+// q head as packed halves): every metadata byte is loaded once per group and scored G times, 12 instructions per (page, q head)
+// plus the shared butterfly, against 4x the whole MHA loop when every q head has its own lane row.
 // -DQUEST_EST_CLOCKS: every CTA stamps %globaltimer at its phase boundaries (tools/step_timeline.py)
 #ifdef QUEST_EST_CLOCKS
 __device__ unsigned long long g_est_clk[1024 * 4];
@@ -177,8 +175,12 @@ __device__ unsigned long long g_est_clk[1024 * 4];
 #define E_STAMP(i) do { } while (0)
 #endif
 
+// Groups of 4 in registers: 16 registers of q + 16 of sign masks do not fit the 64-register budget of two 16-warp CTAs per SM,
+// so that instantiation runs one CTA per SM at up to 128 registers.  Measured alternatives (32q/8kv, 128K: 11.9 us with one lane
+// row per q head): this layout 10.2 us; the same with the ring in shared memory (per-lane cp.async slots, 192 KB in flight per
+// SM) 12.45 us; two CTAs per SM with the masks rebuilt by PRMT spills (profiles/r02_gqa_estimate.txt).
 template <int D, int kOrdered, int kG>
-__global__ void __launch_bounds__(kTileWarps * 32, 2)
+__global__ void __launch_bounds__(kTileWarps * 32, kG == 104 ? 1 : 2)
 estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uint32_t len_,
                      const __half* __restrict__ meta_, const int32_t* __restrict__ meta_indices_,
                      uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_magic /* ceil(2^32/P), 0 for P=1 */,
@@ -219,9 +221,10 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   extern __shared__ __align__(16) uint8_t est_smem[];
   int32_t* idx_s = reinterpret_cast<int32_t*>(est_smem);                       // [ceil(len/P)]
   const uint32_t n_meta = (len + P - 1) / P;
-  float* q_s = reinterpret_cast<float*>(est_smem + (((size_t)n_meta * 4 + 15) & ~(size_t)15));  // kG == 0 only
-  uint32_t* m_s = reinterpret_cast<uint32_t*>(q_s + (size_t)Hq * D);
-  const uint32_t G = kG ? kG : Hq / Hkv;
+  uint32_t* q_s = reinterpret_cast<uint32_t*>(est_smem + (((size_t)n_meta * 4 + 15) & ~(size_t)15));  // kG == 0 only: packed halves
+  uint32_t* m_s = q_s + (size_t)Hq * D;
+  constexpr int kGr = kG >= 100 ? kG - 100 : 0;  // group size held in registers
+  const uint32_t G = kGr ? (uint32_t)kGr : kG ? (uint32_t)kG : Hq / Hkv;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lir = lane % LPR, rsub = lane / LPR;
   const uint32_t HV = kG == 1 ? Hq : Hkv;               // heads a pass walks per page: q heads (kG = 1) or kv heads
@@ -256,43 +259,46 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   const uint32_t p_clamp = max(p_end, 1u) - 1u;
   uint32_t p_ld = p_begin + pg_in, p = p_ld;
   H8 mx[kDepth], mn[kDepth];
-  auto issue = [&](int s) {
+  auto issue = [&](int s, bool ordered = false) {
     // past the end of THIS CTA's range: re-read its own last page (never stored; an L2 hit) -- running on into the
     // neighbour's pages cost 15 % extra DRAM traffic at 128K, where the neighbour's copy has long left L2
     const uint32_t pc = min(p_ld, p_clamp);
     const uint32_t mp = p_magic ? __umulhi(pc, p_magic) : pc;
     const uint32_t e = pc - mp * P;
     const uint8_t* a = base + (uint64_t)(uint32_t)idx_s[mp] * (2u * slab_bytes) + e * row_bytes;
-    mx[s] = ld_stream(a);
-    mn[s] = ld_stream(a + slab_bytes);
+    if (ordered) {  // the first ring: must be in flight before the launch wait below (see ld_stream_ordered)
+      mx[s] = ld_stream_ordered(a);
+      mn[s] = ld_stream_ordered(a + slab_bytes);
+    } else {
+      mx[s] = ld_stream(a);
+      mn[s] = ld_stream(a + slab_bytes);
+    }
     p_ld += PPP;
   };
 #pragma unroll
-  for (int s = 0; s < kDepth; ++s) issue(s);
+  for (int s = 0; s < kDepth; ++s) issue(s, true);
   E_STAMP(1);  // first ring of metadata loads issued
 
   if (meta_stable && !carries_append) pdl_wait();
   E_STAMP(2);  // the launch before this one has completed
-  float qv[8];
-  uint32_t mk[4];
-  if (kG == 1) {
-    const uint4 raw = *reinterpret_cast<const uint4*>(q + (size_t)kvh * D + lir * 8);
-    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+  constexpr int kQR = kGr ? kGr : 1;  // q rows a lane keeps in registers
+  uint32_t qh[kQR][4], mk[kQR][4];
+  if (kG == 1 || kGr) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
-      qv[2 * i] = f.x;
-      qv[2 * i + 1] = f.y;
-      // sign-bit test: for q = -0 either choice gives a +-0 product, which cannot change the sum
-      mk[i] = ((w[i] & 0x8000u) ? 0u : 0xffffu) | ((w[i] & 0x80000000u) ? 0u : 0xffff0000u);
+    for (int g = 0; g < kQR; ++g) {
+      const uint4 raw = ld_ordered16(q + (size_t)(kvh * kQR + g) * D + lir * 8);  // written by the launch before this one
+      const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        qh[g][i] = w[i];
+        // sign-bit test: for q = -0 either choice gives a +-0 product, which cannot change the sum
+        mk[g][i] = ((w[i] & 0x8000u) ? 0u : 0xffffu) | ((w[i] & 0x80000000u) ? 0u : 0xffff0000u);
+      }
     }
   } else {
     for (uint32_t i = tid; i < Hq * D / 2; i += kThreads) {
-      const __half2 h2 = reinterpret_cast<const __half2*>(q)[i];
-      const float2 f = __half22float2(h2);
-      q_s[2 * i] = f.x;
-      q_s[2 * i + 1] = f.y;
-      const uint32_t bits = *reinterpret_cast<const uint32_t*>(&h2);
+      const uint32_t bits = reinterpret_cast<const uint32_t*>(q)[i];
+      q_s[i] = bits;
       m_s[i] = ((bits & 0x8000u) ? 0u : 0xffffu) | ((bits & 0x80000000u) ? 0u : 0xffff0000u);
     }
     __syncthreads();
@@ -301,7 +307,48 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   pdl_trigger();
 #endif
 
-  while (p - pg_in < p_end) {  // uniform over the CTA: the pass's first page is still in range
+  while (kGr && p - pg_in < p_end) {  // group in registers: a stage is scored for its G q heads, then refilled at once
+    float sa[kQR][kDepth];
+#pragma unroll
+    for (int s = 0; s < kDepth; ++s) {
+      uint32_t hi[4], lo[4];
+      const int rs = s;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (kOrdered) {
+          hi[i] = *reinterpret_cast<const uint32_t*>(&mx[rs].h[i]);
+          lo[i] = *reinterpret_cast<const uint32_t*>(&mn[rs].h[i]);
+        } else {
+          const __half2 a = __hmax2(mx[rs].h[i], mn[rs].h[i]);
+          const __half2 b = __hmin2(mx[rs].h[i], mn[rs].h[i]);
+          hi[i] = *reinterpret_cast<const uint32_t*>(&a);
+          lo[i] = *reinterpret_cast<const uint32_t*>(&b);
+        }
+      }
+      issue(s);  // refill: the stage's contents are in hi / lo
+#pragma unroll
+      for (int g = 0; g < kQR; ++g) {
+        float sacc = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) sacc = fma_h2_seq(qh[g][i], (hi[i] & mk[g][i]) | (lo[i] & ~mk[g][i]), sacc);
+        sa[g][s] = sacc;
+      }
+    }
+    const uint32_t pp = p + (lir / (LPR / 4)) * PPP;
+    const bool st = (lir % (LPR / 4)) == 0 && pp < p_end;
+#pragma unroll
+    for (int g = 0; g < kQR; ++g) {
+      const float v = reduce4_transposed<LPR>(sa[g], lir);
+      if (st) {
+        const uint32_t h = kvh * kQR + g;
+        const __half sv = __float2half_rn(v);
+        o[(size_t)h * len + pp] = sv;
+        if (hist != nullptr) hist_count(hist, h, sv);
+      }
+    }
+    p += kDepth * PPP;
+  }
+  while (!kGr && p - pg_in < p_end) {  // uniform over the CTA: the pass's first page is still in range
     uint32_t sel[kDepth][4];
 #pragma unroll
     for (int s = 0; s < kDepth; ++s) {
@@ -318,7 +365,7 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
           lo = *reinterpret_cast<const uint32_t*>(&b);
         }
         if (kG == 1) {
-          sel[s][i] = (hi & mk[i]) | (lo & ~mk[i]);
+          sel[s][i] = (hi & mk[0][i]) | (lo & ~mk[0][i]);
         } else {  // keep both; the select depends on the q head
           sel[s][i] = hi;
           mx[s].h[i] = *reinterpret_cast<const __half2*>(&lo);  // parked until the refill below
@@ -334,12 +381,8 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
       for (int s = 0; s < kDepth; ++s) {
         float sacc = 0.f;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&sel[s][i]));
-          // reference order (decode_attn.cuh:152-160): 8 sequential fp32 adds of exact products
-          sacc = __fmaf_rn(qv[2 * i], f.x, sacc);
-          sacc = __fmaf_rn(qv[2 * i + 1], f.y, sacc);
-        }
+        // reference order (decode_attn.cuh:152-160): 8 sequential fp32 adds of exact products
+        for (int i = 0; i < 4; ++i) sacc = fma_h2_seq(qh[0][i], sel[s][i], sacc);
         sa[s] = sacc;
       }
       const float v = reduce4_transposed<LPR>(sa, lir);
@@ -351,10 +394,9 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
     } else {
       for (uint32_t g = 0; g < G; ++g) {
         const uint32_t h = kvh * G + g;
-        const float4* qp = reinterpret_cast<const float4*>(q_s + h * D + lir * 8);
-        const float4 q0 = qp[0], q1 = qp[1];
+        const uint4 qq = *reinterpret_cast<const uint4*>(q_s + h * (D / 2) + lir * 4);
         const uint4 msk = *reinterpret_cast<const uint4*>(m_s + h * (D / 2) + lir * 4);
-        const float qg[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        const uint32_t qg[4] = {qq.x, qq.y, qq.z, qq.w};
         const uint32_t mg[4] = {msk.x, msk.y, msk.z, msk.w};
         float sa[kDepth];
 #pragma unroll
@@ -363,10 +405,7 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const uint32_t lo = *reinterpret_cast<const uint32_t*>(&mx[s].h[i]);
-            const uint32_t x = (sel[s][i] & mg[i]) | (lo & ~mg[i]);
-            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&x));
-            sacc = __fmaf_rn(qg[2 * i], f.x, sacc);
-            sacc = __fmaf_rn(qg[2 * i + 1], f.y, sacc);
+            sacc = fma_h2_seq(qg[i], (sel[s][i] & mg[i]) | (lo & ~mg[i]), sacc);
           }
           sa[s] = sacc;
         }
@@ -400,11 +439,13 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
     if (num_sms <= 0) num_sms = 148;
   }
   const uint32_t G = Hq / Hkv;
-  const bool per_q = (G & (G - 1)) == 0 && T_r % Hq == 0;  // one q head per lane row (MHA and power-of-two groups)
+  const bool in_regs = (G == 2 || G == 4) && debug_option(QUEST_DBG_EST_PER_Q) != 1;  // the group's q rows in registers
+  const bool per_q = !in_regs && (G & (G - 1)) == 0 && T_r % Hq == 0;  // one q head per lane row (MHA, other power-of-two groups)
   uint32_t g_shift = 0;
   while ((1u << g_shift) < G) ++g_shift;
   const uint32_t PPP = T_r / (per_q ? Hq : Hkv);
-  uint32_t grid = 2 * num_sms / batch;  // CTAs per sequence
+  const uint32_t occ = (in_regs && G == 4) ? 1u : 2u;  // resident CTAs per SM
+  uint32_t grid = occ * num_sms / batch;  // CTAs per sequence
   if (grid < 8) grid = 8;
   grid -= (ap.k != nullptr ? 1u : 0u);  // scanning CTAs
   const uint32_t need = (len + PPP - 1) / PPP;  // at least one pass of pages per CTA
@@ -412,11 +453,13 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   if (ap.k != nullptr) ++grid;  // + the CTA that carries the append
   const uint32_t n_meta = (len + P - 1) / P;
   size_t smem = ((size_t)n_meta * 4 + 15) & ~(size_t)15;
-  if (!per_q) smem += (size_t)Hq * D * 6;
+  if (!per_q && !in_regs) smem += (size_t)Hq * D * 6;
   if (smem > 100 * 1024) return QUEST_ERR_UNSUPPORTED;
   const bool ord = flags & QUEST_EST_META_ORDERED;
-  auto kern = per_q ? (ord ? estimate_tile_kernel<D, 1, 1> : estimate_tile_kernel<D, 0, 1>)
-                    : (ord ? estimate_tile_kernel<D, 1, 0> : estimate_tile_kernel<D, 0, 0>);
+  auto kern = per_q     ? (ord ? estimate_tile_kernel<D, 1, 1> : estimate_tile_kernel<D, 0, 1>)
+              : !in_regs ? (ord ? estimate_tile_kernel<D, 1, 0> : estimate_tile_kernel<D, 0, 0>)
+              : G == 2   ? (ord ? estimate_tile_kernel<D, 1, 102> : estimate_tile_kernel<D, 0, 102>)
+                         : (ord ? estimate_tile_kernel<D, 1, 104> : estimate_tile_kernel<D, 0, 104>);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;

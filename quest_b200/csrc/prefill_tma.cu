@@ -412,9 +412,21 @@ static int launch_tma(const __half* q, __half* o, uint32_t qo_len, const __half*
       return QUEST_ERR_UNSUPPORTED;
   }
   dim3 grid((qo_len + kTmBQ - 1) / kTmBQ, Hq);
-  prefill_tma_kernel<D, kPTmem><<<grid, kTmThreads, TmSmem<D>::total, s>>>(qmap, kvmap, o, qo_len, kv_indices, num_pages, kv_len, causal, Hq,
-                                                                  Hkv, p_shift, sc, device_error_word());
-  return QUEST_OK;
+  // programmatic dependent launch: barrier init and tensor-memory allocation run before griddepcontrol.wait, i.e. under the tail
+  // of the launch before this one (the RoPE + append producer in quest_prefill_layer_step); everything that reads memory is after it
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kTmThreads);
+  cfg.dynamicSmemBytes = TmSmem<D>::total;
+  cfg.stream = s;
+  cudaLaunchAttribute lattr[1];
+  lattr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  lattr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
+  cfg.attrs = lattr;
+  cfg.numAttrs = 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, prefill_tma_kernel<D, kPTmem>, qmap, kvmap, o, qo_len, kv_indices, num_pages, kv_len,
+                                           causal, Hq, Hkv, p_shift, sc, device_error_word());
+  return e == cudaSuccess ? QUEST_OK : (int)e;
 }
 
 // QUEST_OK: launched; QUEST_ERR_UNSUPPORTED: shape not covered here (the caller falls back); else a CUDA error code.

@@ -16,9 +16,7 @@ rope_kernel(__half* __restrict__ q, __half* __restrict__ k, uint32_t seq_len, ui
   pdl_wait();
   const uint32_t lir = threadIdx.x % LPR;
   float freq[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i)
-    freq[i] = rcp_scale * __powf(rcp_theta, float(2 * ((lir * 8 + i) % (D / 2))) / float(D));
+  rope_freq8<D>(lir * 8, rcp_scale, rcp_theta, freq);
   const size_t q_rows = (size_t)seq_len * Hq, rows = q_rows + (size_t)seq_len * Hkv;
   const size_t stride = (size_t)gridDim.x * (blockDim.x / LPR);
   for (size_t r = (size_t)blockIdx.x * (blockDim.x / LPR) + threadIdx.x / LPR; r < rows; r += stride) {
@@ -33,19 +31,7 @@ rope_kernel(__half* __restrict__ q, __half* __restrict__ k, uint32_t seq_len, ui
     h8_to_float(ld_plain(x + lir * 8), a);
     h8_to_float(ld_plain(x + (lo_half ? lir * 8 + D / 2 : lir * 8 - D / 2)), b);
     __syncwarp();  // partner lanes have read their halves before anyone overwrites them
-    H8 out;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      float r2[2];
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const int e = 2 * i + j;
-        float sn, cs;
-        __sincosf(float(pos) * freq[e], &sn, &cs);
-        r2[j] = a[e] * cs + (lo_half ? -b[e] : b[e]) * sn;
-      }
-      out.h[i] = __floats2half2_rn(r2[0], r2[1]);
-    }
+    const H8 out = rope_rotate8(a, b, lo_half, float(pos), freq);
     st_plain(x + lir * 8, out);
   }
 }

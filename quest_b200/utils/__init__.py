@@ -39,6 +39,7 @@ __all__ = [
     "BatchDecodeWithPagedKVCacheWrapper",
     "append_kv",
     "prefill_forward",
+    "prefill_layer_step",
     "decode_estimate",
     "decode_topk",
     "decode_sparse_attn",
@@ -106,6 +107,31 @@ def prefill_forward(q: torch.Tensor, iController: InferenceController, layer_idx
         rope_scale,
         rope_theta,
     )
+
+
+def prefill_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iController: InferenceController, layer_idx: int,
+                       rope_scale: Optional[float] = None, rope_theta: Optional[float] = None,
+                       write_back_k: bool = False) -> torch.Tensor:
+    """The prompt's attention layer in one native call: what quest/models/QuestAttention.py:85-99 does with
+    apply_rope_in_place(q, k, past) -> append_kv(k, v) -> prefill_forward(q).  Call it between begin_forward and end_forward
+    like the three operators; the RoPE positions start at the cache length before this append.  q is rotated in place; k is
+    left as it was unless write_back_k (nothing on the path reads it again)."""
+    _nvtx.range_push("prefill_layer_step")
+    o = _kernels.prefill_layer_step(
+        q,
+        k,
+        v,
+        iController.kv_cache.buf_layer(layer_idx),
+        iController.kv_indices_with_last,
+        iController.kv_cache.last_page_len,
+        iController.metadata_cache.buf_layer(layer_idx),
+        iController.metadata_indices,
+        1.0 if rope_scale is None else rope_scale,
+        1e4 if rope_theta is None else rope_theta,
+        write_back_k,
+    )
+    _nvtx.range_pop()
+    return o
 
 
 def decode_estimate(q: torch.Tensor, iController: InferenceController, layer_idx: int) -> torch.Tensor:

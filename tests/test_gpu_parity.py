@@ -128,7 +128,24 @@ def test_estimate_bitexact_shapes_and_gqa(Hq, Hkv, D, P, kv_len, flags):
     np.testing.assert_array_equal(bits(o), orc.estimate_scores(q[0], oc.meta_pool, oc.meta_indices, n, Hq).view(np.int16))
 
 
-@pytest.mark.parametrize("Hq,Hkv,D,P,n_pages", [(32, 32, 128, 16, 519), (8, 2, 64, 3, 77), (4, 4, 256, 7, 100), (6, 3, 128, 16, 65)])
+@pytest.mark.parametrize("per_q", [0, 1])
+@pytest.mark.parametrize("Hq,Hkv,D,P,kv_len", [(32, 8, 128, 16, 5000), (16, 8, 128, 16, 1300), (8, 4, 64, 16, 700), (16, 4, 256, 16, 900),
+                                                (16, 2, 128, 16, 777), (64, 8, 128, 16, 2100)])
+def test_estimate_bitexact_gqa_layouts(Hq, Hkv, D, P, kv_len, per_q):
+    """Groups of 2 and 4 keep the group's q rows in registers and score each kv row once per q head (mixed-precision FMAs);
+    DBG_EST_PER_Q = 1 selects the one-q-head-per-lane-row layout for the same shapes (the layout groups of 8 always use)."""
+    oc, gc, k, v, rng = make_pair(kv_len, P, Hkv, D, seed=kv_len + Hq)
+    q = rng.standard_normal((1, Hq, D), dtype=np.float32).astype(np.float16)
+    n = len(oc.kv_indices) - 1
+    o = torch.empty((Hq, n), dtype=torch.float16, device=DEV)
+    kvi, kvp, mi, mp = gc.tables()
+    with K.debug_option(K.DBG_EST_PER_Q, per_q):
+        K.estimate_attn_score(t(q), o, gc.meta, mi, mp, oc.meta_last_page_len, oc.meta_indices[-1], 0, K.EST_META_ORDERED)
+    np.testing.assert_array_equal(bits(o), orc.estimate_scores(q[0], oc.meta_pool, oc.meta_indices, n, Hq).view(np.int16))
+
+
+@pytest.mark.parametrize("Hq,Hkv,D,P,n_pages", [(32, 32, 128, 16, 519), (8, 2, 64, 3, 77), (4, 4, 256, 7, 100), (6, 3, 128, 16, 65),
+                                                 (8, 4, 128, 16, 333)])
 def test_estimate_unordered_random_metadata(Hq, Hkv, D, P, n_pages):
     """Reference kernels/src/test/test_max_possible.cu:29-154: max and min slabs are independent N(0,1) draws (so
     max >= min does NOT hold) behind a shuffled page table; sum_d max(q*max, q*min) must still be bit-exact."""
