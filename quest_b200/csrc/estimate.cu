@@ -235,6 +235,8 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   // with an append to carry, the last CTA does only that and the scan is shared by the others
   const uint32_t n_scan = ap.k != nullptr ? gridDim.x - 1 : gridDim.x;
   const bool scans = blockIdx.x < n_scan;
+  // (a partition skewed towards the CTAs that start first -- they are placed in blockIdx order as the launch before drains --
+  // was measured: no gain, every CTA finishes when the DRAM stream does; profiles/r02_b_experiments.md)
   const uint32_t p_begin = scans ? (uint32_t)(((uint64_t)blockIdx.x * len) / n_scan) : 0u;
   const uint32_t p_end = scans ? (uint32_t)(((uint64_t)(blockIdx.x + 1) * len) / n_scan) : 0u;
   const uint32_t row_bytes = Hkv * D * 2, slab_bytes = P * row_bytes;

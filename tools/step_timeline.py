@@ -59,5 +59,13 @@ def main():
                 print(f"{names[e]:30s} {v.size:5d} {r.min():8.2f} {np.percentile(r, 10):8.2f} {np.median(r):8.2f} {np.percentile(r, 90):8.2f} {r.max():8.2f}")
 
 
+    # estimate CTAs by blockIdx decile: are the late starters the high block indices?
+    print("estimate CTAs by blockIdx decile: mean start / mean finish (us)")
+    for d in range(10):
+        sl = te[d * 296 // 10:(d + 1) * 296 // 10]
+        print(f"  blocks {d * 296 // 10:3d}-{(d + 1) * 296 // 10 - 1:3d}: start {(sl[:, 0].mean() - t0) / 1e3:6.2f}  finish {(sl[:, 3].mean() - t0) / 1e3:6.2f}"
+              f"  (max finish {(sl[:, 3].max() - t0) / 1e3:6.2f})")
+
+
 if __name__ == "__main__":
     main()
