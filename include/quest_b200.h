@@ -268,6 +268,30 @@ int quest_prefill_layer_step(void* q, void* k, const void* v, void* o, uint32_t 
                              uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
                              float rope_scale, float rope_theta, uint32_t flags, void* stream);
 
+/* ---- fp8 (e4m3) page metadata: SURVEY.md section 8 row f-4, a flag-gated variant with NO counterpart in the reference ---------
+ * (its metadata is fp16 only, decode_page.cuh:79-352).  A second pool of the same shape [pages, 2, page_size, num_heads,
+ * head_dim] with ONE BYTE per bound, indexed by the same metadata page table, holds every per-page max rounded UP and every min
+ * rounded DOWN to e4m3, so the estimate over it is still an upper bound of every q.k in the page (and >= the fp16 score) while
+ * it streams half the bytes.  |x| > 448 saturates (the bound is lost there; fp16 keys of that size do not occur).  Scores are NOT
+ * bit-identical to the reference's -- this is why it is a separate entry point and off by default; the selected set is the
+ * reference's top-k of the widened bounds.
+ * quest_metadata_to_fp8: (re)builds the e4m3 entries of KV pages [first_kv_page, end_kv_page) from the fp16 pool -- call it
+ *   after quest_append_prefill / quest_rope_append_prefill / quest_append_decode for the pages they touched.
+ * quest_estimate_fp8: quest_estimate over the e4m3 pool (flags: QUEST_EST_META_STABLE only; the pool is ordered by construction).
+ * quest_decode_layer_step_fp8: quest_decode_layer_step scoring from meta8_data; the append keeps both pools current. */
+int quest_metadata_to_fp8(const void* meta_data, const int32_t* meta_indices, uint32_t first_kv_page, uint32_t end_kv_page,
+                          void* meta8_data, uint32_t num_heads, uint32_t head_dim, uint32_t page_size, void* stream);
+int quest_estimate_fp8(const void* q, void* o, uint32_t len, const void* meta8_data, const int32_t* meta_indices,
+                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                       uint32_t flags, void* stream);
+int quest_decode_layer_step_fp8(const void* q, const void* k_new, const void* v_new, void* o, void* kv_data,
+                                const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_idx,
+                                uint32_t kv_last_page_len, void* meta_data, void* meta8_data, const int32_t* meta_indices,
+                                uint32_t num_meta_pages, uint32_t meta_last_page_len, void* scores, int32_t* topk_idx,
+                                uint32_t k, uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                                uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                                size_t workspace_bytes, void* stream);
+
 /* ---- combine of partial attention states (sequence-sharded multi-GPU path) ----------------------
  * Merges n partial states (o_i fp32 [n, num_heads, head_dim] normalised, lse_i fp32 [n, num_heads]
  * base-2) into o fp16 [num_heads, head_dim]: flashinfer state.cuh:53-62 / cascade.cuh:279-340.

@@ -91,6 +91,58 @@ def estimate_scores(q, meta_pool, meta_indices, num_scored_pages, num_qo_heads=N
     return np.ascontiguousarray(s[..., 0].astype(np.float16).T)
 
 
+# ----------------------------------------------------------------------------------------------------
+# fp8 (e4m3) metadata, SURVEY.md section 8 row f-4 (a variant of this framework; the reference's metadata is fp16 only,
+# decode_page.cuh:79-352).  OCP FP8 E4M3: 1 sign, 4 exponent (bias 7), 3 mantissa bits, subnormals at exponent 0, largest
+# finite 448 (0x7e), 0x7f / 0xff = NaN, no infinities.  The pool stores every max rounded UP and every min rounded DOWN.
+# ----------------------------------------------------------------------------------------------------
+def _e4m3_table():
+    vals = np.zeros(256, dtype=np.float64)
+    for b in range(256):
+        sgn = -1.0 if b & 0x80 else 1.0
+        e, m = (b >> 3) & 0xF, b & 7
+        if e == 15 and m == 7:
+            vals[b] = np.nan
+        elif e == 0:
+            vals[b] = sgn * (m / 8.0) * 2.0 ** -6
+        else:
+            vals[b] = sgn * (1.0 + m / 8.0) * 2.0 ** (e - 7)
+    return vals
+
+
+E4M3_VALUES = _e4m3_table()
+_E4M3_FINITE = np.array([b for b in range(256) if not np.isnan(E4M3_VALUES[b]) and b != 0x80], dtype=np.uint8)  # -0 left out
+_E4M3_ORDER = _E4M3_FINITE[np.argsort(E4M3_VALUES[_E4M3_FINITE], kind="stable")]
+_E4M3_SORTED = E4M3_VALUES[_E4M3_ORDER]
+
+
+def e4m3_round_up(x):
+    """Byte of the smallest e4m3 value >= x (x fp16 array); values above 448 saturate to 448."""
+    xf = np.asarray(x, dtype=np.float64)
+    i = np.searchsorted(_E4M3_SORTED, xf, side="left")
+    return _E4M3_ORDER[np.minimum(i, len(_E4M3_SORTED) - 1)]
+
+
+def e4m3_round_down(x):
+    """Byte of the largest e4m3 value <= x; values below -448 saturate to -448."""
+    xf = np.asarray(x, dtype=np.float64)
+    i = np.searchsorted(_E4M3_SORTED, xf, side="right") - 1
+    return _E4M3_ORDER[np.maximum(i, 0)]
+
+
+def metadata_to_fp8(meta_pool):
+    """fp16 metadata pool [pages, 2, P, H, D] -> uint8 pool of the same shape: slab 0 (max) rounded up, slab 1 (min) down."""
+    out = np.zeros(meta_pool.shape, dtype=np.uint8)
+    out[:, 0] = e4m3_round_up(meta_pool[:, 0])
+    out[:, 1] = e4m3_round_down(meta_pool[:, 1])
+    return out
+
+
+def fp8_pool_to_f16(meta8_pool):
+    """The fp16 values an e4m3 pool stands for (every e4m3 value is exactly representable in fp16)."""
+    return E4M3_VALUES[meta8_pool].astype(np.float16)
+
+
 def estimate_scores_torch_ref(q, k, page_size):
     """The reference's own torch restatement (quest/tests/test_estimate.py:17-75), in numpy fp32:
     score[h, p] = sum_d |q_d| * max_{t in page p} (k_td * sign q_d), last page dropped.  Used to pin

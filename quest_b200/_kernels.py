@@ -45,6 +45,10 @@ SIGNATURES = {
                                              _f32, _f32, _u32, _vp]),
     "quest_prefill_layer_step": (_c.c_int, [_vp, _vp, _vp, _vp, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _u32,
                                             _u32, _f32, _f32, _u32, _vp]),
+    "quest_metadata_to_fp8": (_c.c_int, [_vp, _i32p, _u32, _u32, _vp, _u32, _u32, _u32, _vp]),
+    "quest_estimate_fp8": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _vp]),
+    "quest_decode_layer_step_fp8": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _vp, _i32p, _u32, _u32, _vp,
+                                               _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _u32, _vp, _vp, _u32, _u32, _vp]),
     "quest_peer_staging_bytes": (_sz, [_u32, _u32, _u32]),
     "quest_peer_allgather": (_c.c_int, [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _vp]),
@@ -280,6 +284,26 @@ def prefill_with_paged_kv_cache(q, kv_data, kv_indices, kv_last_page_len, causal
                                      kv_indices.size(0), int(kv_last_page_len), 1 if causal else 0, q.size(1), Hkv, D,
                                      P, _stream()), "prefill_with_paged_kv_cache")
     return o
+
+
+def metadata_to_fp8(metadata_data, metadata_indices, first_kv_page, end_kv_page, meta8_data):
+    """e4m3 copies (max rounded up, min rounded down) of the metadata entries of KV pages [first, end): the flag-gated fp8
+    metadata variant (no counterpart in the reference).  meta8_data: uint8 pool of metadata_data's shape."""
+    _check_input(metadata_data, "metadata_data"), _check_input(metadata_indices, "metadata_indices"), _check_input(meta8_data, "meta8_data")
+    _check(meta8_data.dtype == torch.uint8 and meta8_data.shape == metadata_data.shape, "meta8_data must be a uint8 pool of metadata_data's shape")
+    P, H, D = _pool_dims(metadata_data, "metadata_data")
+    _rc(load_library().quest_metadata_to_fp8(metadata_data.data_ptr(), metadata_indices.data_ptr(), int(first_kv_page),
+                                             int(end_kv_page), meta8_data.data_ptr(), H, D, P, _stream()), "metadata_to_fp8")
+
+
+def estimate_attn_score_fp8(q, o, meta8_data, metadata_indices, flags=0):
+    """estimate_attn_score over the e4m3 metadata pool; o [num_qo_heads, scored pages] fp16."""
+    _check_input(q, "q"), _check_input(o, "o"), _check_input(meta8_data, "meta8_data"), _check_input(metadata_indices, "metadata_indices")
+    _check(meta8_data.dtype == torch.uint8 and meta8_data.dim() == 5, "meta8_data must be a 5D uint8 pool")
+    _check_half(q, "estimate_attn_score_fp8")
+    P, H, D = meta8_data.size(2), meta8_data.size(3), meta8_data.size(4)
+    _rc(load_library().quest_estimate_fp8(q.data_ptr(), o.data_ptr(), o.size(1), meta8_data.data_ptr(), metadata_indices.data_ptr(),
+                                          q.size(1), H, D, P, int(flags), _stream()), "estimate_attn_score_fp8")
 
 
 PF_WRITE_BACK_K = 1  # include/quest_b200.h QUEST_PF_WRITE_BACK_K

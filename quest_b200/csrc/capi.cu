@@ -117,13 +117,13 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
 // One decode step of one layer: append_kv + estimate + top-k + sparse decode (the four calls of
 // quest/models/QuestAttention.py:100-150 in the reference).  The append rides on one extra CTA of the estimate launch, so the
 // step is three launches.
-extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new, void* o, void* kv_data,
-                                       const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_idx,
-                                       uint32_t kv_last_page_len, void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
-                                       uint32_t meta_last_page_len, void* scores, int32_t* topk_idx, uint32_t k,
-                                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
-                                       uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
-                                       size_t workspace_bytes, void* stream) {
+static int layer_step_impl(const void* q, const void* k_new, const void* v_new, void* o, void* kv_data,
+                           const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_idx,
+                           uint32_t kv_last_page_len, void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                           uint32_t meta_last_page_len, void* scores, int32_t* topk_idx, uint32_t k,
+                           uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                           uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                           size_t workspace_bytes, void* stream, void* meta8 /* e4m3 metadata pool to score from, or nullptr */) {
   if (!q || !k_new || !v_new || !o || !kv_data || !kv_indices || !meta_data || !meta_indices) return QUEST_ERR_BAD_ARG;
   if (!num_kv_pages || !num_meta_pages || !num_qo_heads || !num_kv_heads || !page_size || !pages_per_chunk) return QUEST_ERR_BAD_ARG;
   if (num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
@@ -135,17 +135,21 @@ extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const v
   const uint32_t len = num_kv_pages - 1;  // scored pages: all but the last
   if (k > len || (k && (!scores || !topk_idx))) return QUEST_ERR_BAD_ARG;
   quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, (__half*)kv_data, kv_indices, (__half*)meta_data,
-                          num_kv_pages, kv_last_page_len, num_meta_pages, meta_last_page_len};
+                          num_kv_pages, kv_last_page_len, num_meta_pages, meta_last_page_len, (uint8_t*)meta8};
   int rc;
   if (k == 0) {  // nothing to select: attend to the last page only
     rc = quest_append_decode(k_new, v_new, kv_data, kv_indices, num_kv_pages, kv_last_page_len, meta_data, meta_indices,
                              num_meta_pages, meta_last_page_len, num_kv_heads, head_dim, page_size, stream);
+    if (rc == QUEST_OK && meta8)  // keep the e4m3 copy of the entry just updated current
+      rc = quest_metadata_to_fp8(meta_data, meta_indices, num_kv_pages - 1, num_kv_pages, meta8, num_kv_heads, head_dim, page_size, stream);
   } else {
     // the estimate kernel counts the scores into per-head bin totals, from which the top-k kernel selects in one pass
     uint32_t* hist = quest::step_hist(workspace, workspace_bytes, num_qo_heads, len);
-    rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                  QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream, quest::BatchArgs{}, 1, hist);
-    if (rc == QUEST_ERR_UNSUPPORTED && hist) {  // shapes only the generic estimate kernel takes (it launches the append itself)
+    const uint32_t fl = QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED | (meta8 ? quest::kEstMetaFp8 : 0u);
+    const void* scored = meta8 ? meta8 : meta_data;  // the append CTA still updates the fp16 pool (ap.meta) and its e4m3 copy
+    rc = quest::estimate_dispatch(q, scores, len, scored, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size, fl, ap,
+                                  (cudaStream_t)stream, quest::BatchArgs{}, 1, hist);
+    if (rc == QUEST_ERR_UNSUPPORTED && hist && !meta8) {  // shapes only the generic estimate kernel takes (it launches the append itself)
       hist = nullptr;
       rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                                     QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream);
@@ -158,6 +162,33 @@ extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const v
   if (rc) return rc;
   return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, kv_last_page_idx, kv_last_page_len, num_qo_heads, num_kv_heads,
                           head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
+}
+
+extern "C" int quest_decode_layer_step(const void* q, const void* k_new, const void* v_new, void* o, void* kv_data,
+                                       const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_idx,
+                                       uint32_t kv_last_page_len, void* meta_data, const int32_t* meta_indices, uint32_t num_meta_pages,
+                                       uint32_t meta_last_page_len, void* scores, int32_t* topk_idx, uint32_t k,
+                                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                                       uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+  return layer_step_impl(q, k_new, v_new, o, kv_data, kv_indices, num_kv_pages, kv_last_page_idx, kv_last_page_len, meta_data,
+                         meta_indices, num_meta_pages, meta_last_page_len, scores, topk_idx, k, num_qo_heads, num_kv_heads,
+                         head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream, nullptr);
+}
+
+// The same step scoring from the e4m3 copy of the metadata (flag-gated variant, no counterpart in
+// the reference): the estimate streams half the bytes; the append CTA updates the fp16 entry of the last page and its e4m3 copy.
+extern "C" int quest_decode_layer_step_fp8(const void* q, const void* k_new, const void* v_new, void* o, void* kv_data,
+                                           const int32_t* kv_indices, uint32_t num_kv_pages, uint32_t kv_last_page_idx,
+                                           uint32_t kv_last_page_len, void* meta_data, void* meta8_data, const int32_t* meta_indices,
+                                           uint32_t num_meta_pages, uint32_t meta_last_page_len, void* scores, int32_t* topk_idx,
+                                           uint32_t k, uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim,
+                                           uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
+                                           size_t workspace_bytes, void* stream) {
+  if (!meta8_data) return QUEST_ERR_BAD_ARG;
+  return layer_step_impl(q, k_new, v_new, o, kv_data, kv_indices, num_kv_pages, kv_last_page_idx, kv_last_page_len, meta_data,
+                         meta_indices, num_meta_pages, meta_last_page_len, scores, topk_idx, k, num_qo_heads, num_kv_heads,
+                         head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream, meta8_data);
 }
 
 // The layer step for a batch of sequences, driven by per-sequence records in device memory (see include/quest_b200.h).
@@ -179,7 +210,7 @@ extern "C" int quest_decode_layer_step_batch(const void* q, const void* k_new, c
   quest::BatchArgs ba = {reinterpret_cast<const quest::SeqDesc*>(descs), kv_layer_offset, meta_layer_offset,
                          scores_seq_stride, workspace_seq_bytes};
   // the append rides on the estimate launch; its pointers and lengths are taken from the records inside the kernel
-  quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, nullptr, nullptr, nullptr, 0, 0, 0, 0};
+  quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, nullptr, nullptr, nullptr, 0, 0, 0, 0, nullptr};
   cudaStream_t s = (cudaStream_t)stream;
   const uint32_t flags = QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED;
   uint32_t* hist = quest::step_hist(workspace, workspace_seq_bytes, num_qo_heads, max_len);

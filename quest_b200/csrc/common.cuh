@@ -65,6 +65,19 @@ __device__ __forceinline__ H8 ld_stream_ordered(const void* p) {
                : "memory");
   return r;
 }
+// 8-byte forms (fp8 metadata rows: 8 dims per lane): the bytes land in the first two words of the H8
+__device__ __forceinline__ H8 ld_stream8(const void* p) {
+  H8 r;
+  uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(u[0]), "=r"(u[1]) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ H8 ld_stream8_ordered(const void* p) {
+  H8 r;
+  uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+  asm volatile("ld.global.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(u[0]), "=r"(u[1]) : "l"(p) : "memory");
+  return r;
+}
 // Predicated form: r keeps its previous contents when !pred (no memory access is made).
 __device__ __forceinline__ void ld_stream_if(H8& r, const void* p, bool pred) {
   uint32_t* u = reinterpret_cast<uint32_t*>(&r);
@@ -121,6 +134,10 @@ __device__ __forceinline__ uint4 ld_ordered16(const void* p) {
   uint4 v;
   asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ H8 ld_ordered_h8(const void* p) {
+  const uint4 v = ld_ordered16(p);
+  return *reinterpret_cast<const H8*>(&v);
 }
 __device__ __forceinline__ uint32_t ld_ordered32(const void* p) {
   uint32_t v;
@@ -180,6 +197,50 @@ __device__ __forceinline__ void rope_freq8(uint32_t d0, float rcp_scale, float r
   for (int i = 0; i < 8; ++i) freq[i] = rcp_scale * __powf(rcp_theta, float(2 * ((d0 + i) % (D / 2))) / float(D));
 }
 
+// ---- fp8 (e4m3) copy of the page metadata, SURVEY.md section 8 row f-4 (flag-gated; the reference has fp16 only) -----------
+// A second pool of the same shape holds every bound as one e4m3 byte, rounded OUTWARD: max entries up, min entries down, so
+// sum_d max(q*max8, q*min8) is still an upper bound of every q.k in the page and the estimate streams half the bytes.
+// |x| > 448 (the largest e4m3) saturates to +-448 -- the one case where the bound is lost; fp16 keys of that size do not occur.
+__device__ __forceinline__ uint32_t f16x2_to_e4m3x2_rn(uint32_t h2) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f16x2 %0, %1;" : "=h"(r) : "r"(h2));
+  return r;
+}
+__device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t b2) {
+  uint32_t r;
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(r) : "h"((uint16_t)b2));
+  return r;
+}
+// smallest e4m3 >= x for both halves of h2 (two bytes, low half in the low byte)
+__device__ __forceinline__ uint32_t e4m3x2_round_up(uint32_t h2) {
+  const uint32_t b = f16x2_to_e4m3x2_rn(h2);
+  const uint32_t y = e4m3x2_to_f16x2(b);
+  const __half2 lt = __hlt2(*reinterpret_cast<const __half2*>(&y), *reinterpret_cast<const __half2*>(&h2));  // 1.0 where y < x
+  const uint32_t m = *reinterpret_cast<const uint32_t*>(&lt);
+  uint32_t lo = b & 0xffu, hi = (b >> 8) & 0xffu;
+  // one step towards +inf: magnitude up for positives (not past 448 = 0x7e), magnitude down for negatives
+  if (m & 0xffffu) lo = (lo & 0x80u) ? lo - 1u : (lo < 0x7eu ? lo + 1u : lo);
+  if (m >> 16) hi = (hi & 0x80u) ? hi - 1u : (hi < 0x7eu ? hi + 1u : hi);
+  return lo | (hi << 8);
+}
+__device__ __forceinline__ uint32_t e4m3x2_round_down(uint32_t h2) { return e4m3x2_round_up(h2 ^ 0x80008000u) ^ 0x8080u; }
+__device__ __forceinline__ uint2 h8_to_e4m3_up(const H8& v) {
+  const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+  return make_uint2(e4m3x2_round_up(u[0]) | (e4m3x2_round_up(u[1]) << 16), e4m3x2_round_up(u[2]) | (e4m3x2_round_up(u[3]) << 16));
+}
+__device__ __forceinline__ uint2 h8_to_e4m3_down(const H8& v) {
+  const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+  return make_uint2(e4m3x2_round_down(u[0]) | (e4m3x2_round_down(u[1]) << 16),
+                    e4m3x2_round_down(u[2]) | (e4m3x2_round_down(u[3]) << 16));
+}
+__device__ __forceinline__ H8 e4m3x8_to_h8(uint2 b) {
+  H8 r;
+  uint32_t* u = reinterpret_cast<uint32_t*>(&r);
+  u[0] = e4m3x2_to_f16x2(b.x & 0xffffu), u[1] = e4m3x2_to_f16x2(b.x >> 16);
+  u[2] = e4m3x2_to_f16x2(b.y & 0xffffu), u[3] = e4m3x2_to_f16x2(b.y >> 16);
+  return r;
+}
+
 constexpr float kMaxHalf = 65504.f;  // CUDART_MAX_NORMAL_FP16 (decode_page.cuh:430-431)
 
 // append_kv of one token for one 16-byte column c of the [H*D] row: K/V rows into the last KV page, running
@@ -189,7 +250,7 @@ __device__ __forceinline__ void append_decode_column(const __half* __restrict__ 
                                                      uint32_t num_kv_pages, uint32_t kv_last_len, __half* __restrict__ meta,
                                                      const int32_t* __restrict__ meta_indices, uint32_t num_meta_pages,
                                                      uint32_t meta_last_len, uint32_t row_vecs /* H*D/8 */, uint32_t P,
-                                                     uint32_t c) {
+                                                     uint32_t c, uint8_t* __restrict__ meta8 = nullptr) {
   const size_t row = (size_t)row_vecs * 8;  // H*D elements
   const size_t page = (size_t)__ldg(kv_indices + num_kv_pages - 1);
   const uint32_t entry = kv_last_len - 1;
@@ -215,6 +276,11 @@ __device__ __forceinline__ void append_decode_column(const __half* __restrict__ 
   st_plain(vdst, vv);
   st_plain(mxp, mx);
   st_plain(mnp, mn);
+  if (meta8 != nullptr) {  // fp8 copy of the entry just updated: current by the time the page stops being the last (unscored) one
+    uint8_t* m8 = meta8 + ((mpage * 2) * P + mentry) * row + c * 8;
+    *reinterpret_cast<uint2*>(m8) = h8_to_e4m3_up(mx);
+    *reinterpret_cast<uint2*>(m8 + (size_t)P * row) = h8_to_e4m3_down(mn);
+  }
 }
 
 // Optional append_kv work carried by another kernel's first CTA (estimate.cu); k == nullptr: none.
@@ -225,6 +291,7 @@ struct AppendArgs {
   const int32_t* kv_indices;
   __half* meta;
   uint32_t num_kv_pages, kv_last_len, num_meta_pages, meta_last_len;
+  uint8_t* meta8;  // fp8 metadata pool to keep in step with the entry the append updates (nullptr: none)
 };
 
 // Descriptor-driven launches (quest_decode_layer_step_batch): everything that changes from token to token lives in one
@@ -247,6 +314,7 @@ struct BatchArgs {
 };
 
 constexpr float kLog2e = 1.44269504088896340736f;
+constexpr uint32_t kEstMetaFp8 = 0x100u;  // internal estimate flag (beside QUEST_EST_META_*): meta_data is the e4m3 pool
 
 // fp16 bits -> order-preserving 16-bit key (raft select_radix.cuh:82-90 twiddle_in)
 __device__ __forceinline__ uint16_t score_key(uint16_t h) { return (h & 0x8000u) ? (uint16_t)~h : (uint16_t)(h | 0x8000u); }

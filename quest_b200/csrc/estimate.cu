@@ -239,8 +239,12 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   // was measured: no gain, every CTA finishes when the DRAM stream does; profiles/r02_b_experiments.md)
   const uint32_t p_begin = scans ? (uint32_t)(((uint64_t)blockIdx.x * len) / n_scan) : 0u;
   const uint32_t p_end = scans ? (uint32_t)(((uint64_t)(blockIdx.x + 1) * len) / n_scan) : 0u;
-  const uint32_t row_bytes = Hkv * D * 2, slab_bytes = P * row_bytes;
-  const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + (size_t)(kG == 1 ? kvh >> g_shift : kvh) * (D * 2) + lir * 16;
+  // kOrdered == 2: the metadata is the e4m3 pool (one byte per bound, max >= min by construction): 8 bytes per lane and slab,
+  // widened to halves when a stage is consumed; everything after that is the fp16 arithmetic
+  constexpr bool kF8 = kOrdered == 2;
+  constexpr uint32_t kEB = kF8 ? 1 : 2;  // bytes per bound
+  const uint32_t row_bytes = Hkv * D * kEB, slab_bytes = P * row_bytes;
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + (size_t)(kG == 1 ? kvh >> g_shift : kvh) * (D * kEB) + lir * (8 * kEB);
 
   // append_kv of the step's new token rides on one extra CTA of this launch.  The entry it updates (the last
   // page's) is not one of the scored ones; the decode kernel two launches later reads the new K/V row.
@@ -252,7 +256,7 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
     const uint32_t row_vecs = Hkv * D / 8;
     for (uint32_t c = tid; c < row_vecs; c += kThreads)
       append_decode_column(ap.k, ap.v, ap.kv, ap.kv_indices, ap.num_kv_pages, ap.kv_last_len, ap.meta, meta_indices,
-                           ap.num_meta_pages, ap.meta_last_len, row_vecs, P, c);
+                           ap.num_meta_pages, ap.meta_last_len, row_vecs, P, c, ap.meta8);
     return;
   }
   for (uint32_t i = tid; i < n_meta; i += kThreads) idx_s[i] = __ldg(meta_indices + i);
@@ -269,11 +273,11 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
     const uint32_t e = pc - mp * P;
     const uint8_t* a = base + (uint64_t)(uint32_t)idx_s[mp] * (2u * slab_bytes) + e * row_bytes;
     if (ordered) {  // the first ring: must be in flight before the launch wait below (see ld_stream_ordered)
-      mx[s] = ld_stream_ordered(a);
-      mn[s] = ld_stream_ordered(a + slab_bytes);
+      mx[s] = kF8 ? ld_stream8_ordered(a) : ld_stream_ordered(a);
+      mn[s] = kF8 ? ld_stream8_ordered(a + slab_bytes) : ld_stream_ordered(a + slab_bytes);
     } else {
-      mx[s] = ld_stream(a);
-      mn[s] = ld_stream(a + slab_bytes);
+      mx[s] = kF8 ? ld_stream8(a) : ld_stream(a);
+      mn[s] = kF8 ? ld_stream8(a + slab_bytes) : ld_stream(a + slab_bytes);
     }
     p_ld += PPP;
   };
@@ -314,15 +318,16 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
 #pragma unroll
     for (int s = 0; s < kDepth; ++s) {
       uint32_t hi[4], lo[4];
-      const int rs = s;
+      const H8 vmx = kF8 ? e4m3x8_to_h8(*reinterpret_cast<const uint2*>(&mx[s])) : mx[s];
+      const H8 vmn = kF8 ? e4m3x8_to_h8(*reinterpret_cast<const uint2*>(&mn[s])) : mn[s];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         if (kOrdered) {
-          hi[i] = *reinterpret_cast<const uint32_t*>(&mx[rs].h[i]);
-          lo[i] = *reinterpret_cast<const uint32_t*>(&mn[rs].h[i]);
+          hi[i] = *reinterpret_cast<const uint32_t*>(&vmx.h[i]);
+          lo[i] = *reinterpret_cast<const uint32_t*>(&vmn.h[i]);
         } else {
-          const __half2 a = __hmax2(mx[rs].h[i], mn[rs].h[i]);
-          const __half2 b = __hmin2(mx[rs].h[i], mn[rs].h[i]);
+          const __half2 a = __hmax2(vmx.h[i], vmn.h[i]);
+          const __half2 b = __hmin2(vmx.h[i], vmn.h[i]);
           hi[i] = *reinterpret_cast<const uint32_t*>(&a);
           lo[i] = *reinterpret_cast<const uint32_t*>(&b);
         }
@@ -354,15 +359,17 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
     uint32_t sel[kDepth][4];
 #pragma unroll
     for (int s = 0; s < kDepth; ++s) {
+      const H8 vmx = kF8 ? e4m3x8_to_h8(*reinterpret_cast<const uint2*>(&mx[s])) : mx[s];
+      const H8 vmn = kF8 ? e4m3x8_to_h8(*reinterpret_cast<const uint2*>(&mn[s])) : mn[s];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         uint32_t hi, lo;
         if (kOrdered) {
-          hi = *reinterpret_cast<const uint32_t*>(&mx[s].h[i]);
-          lo = *reinterpret_cast<const uint32_t*>(&mn[s].h[i]);
+          hi = *reinterpret_cast<const uint32_t*>(&vmx.h[i]);
+          lo = *reinterpret_cast<const uint32_t*>(&vmn.h[i]);
         } else {
-          const __half2 a = __hmax2(mx[s].h[i], mn[s].h[i]);
-          const __half2 b = __hmin2(mx[s].h[i], mn[s].h[i]);
+          const __half2 a = __hmax2(vmx.h[i], vmn.h[i]);
+          const __half2 b = __hmin2(vmx.h[i], vmn.h[i]);
           hi = *reinterpret_cast<const uint32_t*>(&a);
           lo = *reinterpret_cast<const uint32_t*>(&b);
         }
@@ -457,11 +464,12 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   size_t smem = ((size_t)n_meta * 4 + 15) & ~(size_t)15;
   if (!per_q && !in_regs) smem += (size_t)Hq * D * 6;
   if (smem > 100 * 1024) return QUEST_ERR_UNSUPPORTED;
+  const bool f8 = flags & kEstMetaFp8;
+  if (f8 && ba.descs != nullptr) return QUEST_ERR_UNSUPPORTED;  // the descriptor records name the fp16 pool only
   const bool ord = flags & QUEST_EST_META_ORDERED;
-  auto kern = per_q     ? (ord ? estimate_tile_kernel<D, 1, 1> : estimate_tile_kernel<D, 0, 1>)
-              : !in_regs ? (ord ? estimate_tile_kernel<D, 1, 0> : estimate_tile_kernel<D, 0, 0>)
-              : G == 2   ? (ord ? estimate_tile_kernel<D, 1, 102> : estimate_tile_kernel<D, 0, 102>)
-                         : (ord ? estimate_tile_kernel<D, 1, 104> : estimate_tile_kernel<D, 0, 104>);
+#define QUEST_EST_KERN(KG) (f8 ? estimate_tile_kernel<D, 2, KG> : ord ? estimate_tile_kernel<D, 1, KG> : estimate_tile_kernel<D, 0, KG>)
+  auto kern = per_q ? QUEST_EST_KERN(1) : !in_regs ? QUEST_EST_KERN(0) : G == 2 ? QUEST_EST_KERN(102) : QUEST_EST_KERN(104);
+#undef QUEST_EST_KERN
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -547,7 +555,7 @@ int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_dat
       }
     }
   }
-  if (ba.descs != nullptr || hist != nullptr) return QUEST_ERR_UNSUPPORTED;  // descriptor mode / bin totals: tile kernel only
+  if (ba.descs != nullptr || hist != nullptr || (flags & kEstMetaFp8)) return QUEST_ERR_UNSUPPORTED;  // tile kernel only
   if (ap.k != nullptr) {  // generic path: append as its own launch
     const int rc = quest_append_decode(ap.k, ap.v, ap.kv, ap.kv_indices, ap.num_kv_pages, ap.kv_last_len, ap.meta,
                                        meta_indices, ap.num_meta_pages, ap.meta_last_len, num_kv_heads, head_dim,
@@ -581,4 +589,19 @@ extern "C" int quest_estimate(const void* q, void* o, uint32_t len, const void* 
   quest::AppendArgs none = {};
   return quest::estimate_dispatch(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                                   flags, none, (cudaStream_t)stream, quest::BatchArgs{}, 1, nullptr);
+}
+
+// fp8 metadata (no counterpart in the reference, whose metadata is fp16 only): the same estimate over
+// the e4m3 pool.  The scores are those of the fp16 arithmetic applied to the widened bounds (the tests restate this on the
+// dequantized pool, bit for bit); they are >= the fp16-metadata scores because the pool is rounded outward.
+extern "C" int quest_estimate_fp8(const void* q, void* o, uint32_t len, const void* meta8_data, const int32_t* meta_indices,
+                                  uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
+                                  uint32_t flags, void* stream) {
+  if (!q || !o || !meta8_data || !meta_indices || !num_qo_heads || !num_kv_heads || !page_size) return QUEST_ERR_BAD_ARG;
+  if (num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
+  if (len == 0) return QUEST_OK;
+  quest::AppendArgs none = {};
+  return quest::estimate_dispatch(q, o, len, meta8_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+                                  (flags & QUEST_EST_META_STABLE) | quest::kEstMetaFp8, none, (cudaStream_t)stream,
+                                  quest::BatchArgs{}, 1, nullptr);
 }

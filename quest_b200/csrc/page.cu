@@ -179,6 +179,24 @@ rope_append_prefill_kernel(__half* __restrict__ q, __half* __restrict__ k, const
   }
 }
 
+
+// fp16 metadata entries of KV pages [first, end) -> their e4m3 copies, rounded outward (common.cuh).  grid = (pages, column
+// slices); a thread owns one 8-dim column of the entry.
+__global__ void __launch_bounds__(256)
+metadata_to_fp8_kernel(const __half* __restrict__ meta, const int32_t* __restrict__ meta_indices, uint32_t first,
+                       uint8_t* __restrict__ meta8, uint32_t row_vecs, uint32_t P) {
+  const uint32_t c = blockIdx.y * blockDim.x + threadIdx.x;
+  pdl_wait();
+  if (c >= row_vecs) return;
+  const uint32_t j = first + blockIdx.x;
+  const size_t row = (size_t)row_vecs * 8;
+  const size_t mpage = (size_t)__ldg(meta_indices + j / P);
+  const size_t ent = ((mpage * 2) * P + j % P) * row + c * 8;
+  const H8 mx = ld_ordered_h8(meta + ent), mn = ld_ordered_h8(meta + ent + (size_t)P * row);
+  *reinterpret_cast<uint2*>(meta8 + ent) = h8_to_e4m3_up(mx);
+  *reinterpret_cast<uint2*>(meta8 + ent + (size_t)P * row) = h8_to_e4m3_down(mn);
+}
+
 }  // namespace quest
 
 static bool bad_dims(uint32_t H, uint32_t D, uint32_t P) { return !H || !P || (D != 64 && D != 128 && D != 256); }
@@ -269,5 +287,22 @@ extern "C" int quest_rope_append_prefill(void* q, void* k, const void* v, uint32
   }
 #undef QUEST_RAP
   if (e != cudaSuccess) return (int)e;
+  QUEST_RETURN_LAUNCH();
+}
+
+// fp8 metadata (no counterpart in the reference): e4m3 copies of the metadata entries of KV pages
+// [first_kv_page, end_kv_page), max rounded up and min rounded down.  Call it after quest_append_prefill /
+// quest_rope_append_prefill for the pages they touched (quest_decode_layer_step_fp8 keeps the copy current from then on).
+extern "C" int quest_metadata_to_fp8(const void* meta_data, const int32_t* meta_indices, uint32_t first_kv_page,
+                                     uint32_t end_kv_page, void* meta8_data, uint32_t num_heads, uint32_t head_dim,
+                                     uint32_t page_size, void* stream) {
+  if (!meta_data || !meta_indices || !meta8_data) return QUEST_ERR_BAD_ARG;
+  if (bad_dims(num_heads, head_dim, page_size)) return QUEST_ERR_UNSUPPORTED;
+  if (first_kv_page > end_kv_page) return QUEST_ERR_BAD_ARG;
+  if (first_kv_page == end_kv_page) return QUEST_OK;
+  const uint32_t row_vecs = num_heads * head_dim / 8;
+  dim3 grid(end_kv_page - first_kv_page, (row_vecs + 255) / 256);
+  quest::metadata_to_fp8_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)meta_data, meta_indices, first_kv_page,
+                                                                       (uint8_t*)meta8_data, row_vecs, page_size);
   QUEST_RETURN_LAUNCH();
 }

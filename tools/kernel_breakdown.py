@@ -76,10 +76,32 @@ def main():
                                                scores[l].data_ptr(), sel[l].data_ptr(), k, Hq, Hkv, D, P, ppc.value,
                                                ws.data_ptr(), ws.numel(), st()) == 0
 
+    # flag-gated fp8 metadata (section 8 row f-4): e4m3 copy of every layer's metadata pool, estimate / layer step over it
+    meta8 = [torch.zeros(ic.metadata_cache.buf_layer(l).shape, dtype=torch.uint8, device=dev) for l in range(L)]
+    for l in range(L):
+        assert lib.quest_metadata_to_fp8(ic.metadata_cache.buf_layer(l).data_ptr(), mi.data_ptr(), 0, n_pages, meta8[l].data_ptr(),
+                                         Hkv, D, P, st()) == 0
+
+    def f_est8():
+        for l in range(L):
+            assert lib.quest_estimate_fp8(q[l].data_ptr(), scores[l].data_ptr(), n, meta8[l].data_ptr(), mi.data_ptr(), Hq, Hkv, D, P,
+                                          1, st()) == 0
+
+    def f_layer8():
+        for l in range(L):
+            assert lib.quest_decode_layer_step_fp8(q[l].data_ptr(), kn[l].data_ptr(), vn[l].data_ptr(), o[l].data_ptr(),
+                                                   ic.kv_cache.buf_layer(l).data_ptr(), kvi.data_ptr(), n_pages, last_idx, last_len,
+                                                   ic.metadata_cache.buf_layer(l).data_ptr(), meta8[l].data_ptr(), mi.data_ptr(),
+                                                   mi.numel(), mlast, scores[l].data_ptr(), sel[l].data_ptr(), k, Hq, Hkv, D, P,
+                                                   ppc.value, ws.data_ptr(), ws.numel(), st()) == 0
+
     by = {"estimate": n * Hkv * D * 4 + Hq * n * 2, "topk": Hq * n * 2 + Hq * k * 4, "decode": Hq * (k + 1) * P * 2 * D * 2}
     by["layer_step"] = sum(by.values())
+    by["estimate_fp8"] = n * Hkv * D * 2 + Hq * n * 2
+    by["layer_step_fp8"] = by["layer_step"] - n * Hkv * D * 2
     res = {"shape": {"Hq": Hq, "Hkv": Hkv, "ctx": a.ctx, "pages": n_pages, "k": k, "ppc": ppc.value, "chunks": nch.value}}
-    for name, fn in (("estimate", f_est), ("topk", f_topk), ("decode", f_dec), ("layer_step", f_layer)):
+    for name, fn in (("estimate", f_est), ("topk", f_topk), ("decode", f_dec), ("layer_step", f_layer), ("estimate_fp8", f_est8),
+                     ("layer_step_fp8", f_layer8)):
         fn()
         torch.cuda.synchronize()
         g = try_graph(fn)
