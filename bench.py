@@ -180,6 +180,8 @@ class Workload:
         ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
         assert lib.quest_decode_plan(K_SEL, H, H, D, P, torch.cuda.get_device_properties(self.dev).multi_processor_count,
                                      ctypes.byref(ppc), ctypes.byref(nch)) == 0
+        if os.environ.get("BENCH_NO_HANDOFF"):  # A/B: the decode launch waits for the top-k launch (no page-id hand-over)
+            lib.quest_debug_set_option(K.DBG_NO_HANDOFF, 1)
         if os.environ.get("BENCH_PPC"):  # tuning experiment: override the planner's pages per chunk
             ppc.value = int(os.environ["BENCH_PPC"])
             nch.value = (K_SEL + 1 + ppc.value - 1) // ppc.value

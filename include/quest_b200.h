@@ -328,7 +328,8 @@ int quest_peer_allgather(const void* src, uint32_t rows, uint32_t row_bytes, voi
  * errors (quest/ops/csrc/page.cu:91-93). */
 #define QUEST_DEVERR_PREFILL 1u
 #define QUEST_DEVERR_PEER 2u
-#define QUEST_DEVERR_COUNT 2
+#define QUEST_DEVERR_STEP 4u   /* layer step: a decode CTA never received its page ids from the top-k launch */
+#define QUEST_DEVERR_COUNT 3
 uint32_t quest_device_error(void);
 void quest_device_error_clear(void);
 
@@ -342,7 +343,8 @@ void quest_device_error_clear(void);
 #define QUEST_DBG_TOPK_GENERIC 5     /* 1: shared-memory-key top-k kernel for every length                     */
 #define QUEST_DBG_TOPK_NO_HIST 6     /* 1: layer step selects with the stand-alone top-k kernels (no bin totals) */
 #define QUEST_DBG_EST_PER_Q 7        /* 1: GQA groups of 2 / 4 use one lane row per q head (the round-1 layout)  */
-#define QUEST_DBG_COUNT 8
+#define QUEST_DBG_NO_HANDOFF 8       /* 1: layer step without the page-id hand-over (decode waits for the top-k launch) */
+#define QUEST_DBG_COUNT 9
 int quest_debug_set_option(int option, int value);
 
 /* Counters for bench/tests: number of kernels this library has launched since load / last reset. */

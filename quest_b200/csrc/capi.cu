@@ -12,10 +12,31 @@ unsigned long long g_launch_count = 0;
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
                       uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba = BatchArgs{},
-                      uint32_t batch = 1, uint32_t* hist = nullptr);  // estimate.cu
+                      uint32_t batch = 1, uint32_t* hist = nullptr, uint32_t* epoch = nullptr);  // estimate.cu
 bool topk_hist_covers(uint32_t max_len);  // topk.cu
 int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
-                   uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s);  // topk.cu
+                   uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s,
+                   const Handoff& ho = Handoff{});  // topk.cu
+bool decode_handoff_fits(uint32_t n_sel, uint32_t D, uint32_t ppc);  // decode.cu
+int decode_run_handoff(const void* q, void* o, const void* kv, const int32_t* indices, uint32_t n_sel, uint32_t last_page_idx,
+                       uint32_t last_page_len, uint32_t Hq, uint32_t Hkv, uint32_t D, uint32_t P, uint32_t ppc, void* ws,
+                       cudaStream_t s);  // decode.cu
+// Page-id hand-over of the layer step (common.cuh, Handoff): on when the step selects from the bin totals, the plan fits and the
+// workspace holds it; QUEST_DBG_NO_HANDOFF switches it off (A/B and tests).  Rows of up to 2048 scored pages only: measured
+// 18.63 -> 18.48 us per layer step at 2047 pages, but 30.75 -> 31.1 at 4095 and 52.6 -> 53.2 at 8191, where the decode CTAs
+// would sit polling on their SMs through a selection of several microseconds (profiles/r02_b_experiments.md).
+static Handoff step_handoff(void* workspace, size_t workspace_bytes, uint32_t* hist, uint32_t len, uint32_t k, uint32_t Hq, uint32_t D,
+                            uint32_t ppc) {
+  Handoff ho = {};
+  if (!hist || len > 2048 || debug_option(QUEST_DBG_NO_HANDOFF) || !pdl_enabled() || !decode_handoff_fits(k, D, ppc)) return ho;
+  const uint32_t nchunks = (k + 1 + ppc - 1) / ppc;
+  if (workspace_bytes < ws_bytes(Hq, D, nchunks)) return ho;  // quest_decode_run would refuse it anyway
+  uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
+  ho.epoch = reinterpret_cast<uint32_t*>(ws + kWsEpochOff);
+  ho.slots = ws + ws_o_off(Hq, nchunks);
+  ho.nchunks = nchunks, ho.ppc = ppc, ho.slot_bytes = D * (uint32_t)sizeof(float);
+  return ho;
+}
 // the layer step's bin totals live in its decode workspace (common.cuh); nullptr: the workspace has no room for them
 static uint32_t* step_hist(void* workspace, size_t workspace_bytes, uint32_t Hq, uint32_t max_len) {
   if (!workspace || workspace_bytes < ws_md_off(Hq) || !topk_hist_covers(max_len)) return nullptr;
@@ -96,20 +117,26 @@ extern "C" int quest_sparse_decode_step(const void* q, void* o, const void* kv_d
     return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, last_page_idx, last_page_len, num_qo_heads, num_kv_heads,
                             head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
   // the estimate kernel counts the scores into per-head bin totals, from which the top-k kernel selects in one pass
+  if (quest::device_error_peek() & QUEST_DEVERR_STEP) return QUEST_ERR_DEVICE;  // an earlier step lost its page-id hand-over
   uint32_t* hist = quest::step_hist(workspace, workspace_bytes, num_qo_heads, len);
+  quest::Handoff ho = quest::step_handoff(workspace, workspace_bytes, hist, len, k, num_qo_heads, head_dim, pages_per_chunk);
   int rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                                     QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, quest::AppendArgs{}, (cudaStream_t)stream,
-                                    quest::BatchArgs{}, 1, hist);
+                                    quest::BatchArgs{}, 1, hist, ho.epoch);
   if (rc == QUEST_ERR_UNSUPPORTED && hist) {  // shapes only the generic estimate kernel takes
     hist = nullptr;
+    ho = quest::Handoff{};
     rc = quest_estimate(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                         QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, stream);
   }
   if (rc) return rc;
   // payload ids = the sequence's page table, shared by all heads (row stride 0)
-  rc = hist ? quest::topk_from_hist(scores, hist, kv_indices, 0, topk_idx, num_qo_heads, len, k, quest::BatchArgs{}, 1, (cudaStream_t)stream)
+  rc = hist ? quest::topk_from_hist(scores, hist, kv_indices, 0, topk_idx, num_qo_heads, len, k, quest::BatchArgs{}, 1, (cudaStream_t)stream, ho)
             : quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
   if (rc) return rc;
+  if (ho.epoch)
+    return quest::decode_run_handoff(q, o, kv_data, topk_idx, k, last_page_idx, last_page_len, num_qo_heads, num_kv_heads, head_dim,
+                                     page_size, pages_per_chunk, workspace, (cudaStream_t)stream);
   return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, last_page_idx, last_page_len, num_qo_heads,
                           num_kv_heads, head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
 }
@@ -137,6 +164,7 @@ static int layer_step_impl(const void* q, const void* k_new, const void* v_new, 
   quest::AppendArgs ap = {(const __half*)k_new, (const __half*)v_new, (__half*)kv_data, kv_indices, (__half*)meta_data,
                           num_kv_pages, kv_last_page_len, num_meta_pages, meta_last_page_len, (uint8_t*)meta8};
   int rc;
+  quest::Handoff ho = {};
   if (k == 0) {  // nothing to select: attend to the last page only
     rc = quest_append_decode(k_new, v_new, kv_data, kv_indices, num_kv_pages, kv_last_page_len, meta_data, meta_indices,
                              num_meta_pages, meta_last_page_len, num_kv_heads, head_dim, page_size, stream);
@@ -144,22 +172,28 @@ static int layer_step_impl(const void* q, const void* k_new, const void* v_new, 
       rc = quest_metadata_to_fp8(meta_data, meta_indices, num_kv_pages - 1, num_kv_pages, meta8, num_kv_heads, head_dim, page_size, stream);
   } else {
     // the estimate kernel counts the scores into per-head bin totals, from which the top-k kernel selects in one pass
+    if (quest::device_error_peek() & QUEST_DEVERR_STEP) return QUEST_ERR_DEVICE;  // an earlier step lost its page-id hand-over
     uint32_t* hist = quest::step_hist(workspace, workspace_bytes, num_qo_heads, len);
+    ho = quest::step_handoff(workspace, workspace_bytes, hist, len, k, num_qo_heads, head_dim, pages_per_chunk);
     const uint32_t fl = QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED | (meta8 ? quest::kEstMetaFp8 : 0u);
     const void* scored = meta8 ? meta8 : meta_data;  // the append CTA still updates the fp16 pool (ap.meta) and its e4m3 copy
     rc = quest::estimate_dispatch(q, scores, len, scored, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size, fl, ap,
-                                  (cudaStream_t)stream, quest::BatchArgs{}, 1, hist);
+                                  (cudaStream_t)stream, quest::BatchArgs{}, 1, hist, ho.epoch);
     if (rc == QUEST_ERR_UNSUPPORTED && hist && !meta8) {  // shapes only the generic estimate kernel takes (it launches the append itself)
       hist = nullptr;
+      ho = quest::Handoff{};
       rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                                     QUEST_EST_META_STABLE | QUEST_EST_META_ORDERED, ap, (cudaStream_t)stream);
     }
     if (rc) return rc;
     // payload ids = the sequence's page table, shared by all heads (row stride 0)
-    rc = hist ? quest::topk_from_hist(scores, hist, kv_indices, 0, topk_idx, num_qo_heads, len, k, quest::BatchArgs{}, 1, (cudaStream_t)stream)
+    rc = hist ? quest::topk_from_hist(scores, hist, kv_indices, 0, topk_idx, num_qo_heads, len, k, quest::BatchArgs{}, 1, (cudaStream_t)stream, ho)
               : quest_topk(scores, kv_indices, 0, nullptr, topk_idx, num_qo_heads, len, k, stream);
   }
   if (rc) return rc;
+  if (ho.epoch)
+    return quest::decode_run_handoff(q, o, kv_data, topk_idx, k, kv_last_page_idx, kv_last_page_len, num_qo_heads, num_kv_heads,
+                                     head_dim, page_size, pages_per_chunk, workspace, (cudaStream_t)stream);
   return quest_decode_run(q, o, nullptr, kv_data, topk_idx, k, k, kv_last_page_idx, kv_last_page_len, num_qo_heads, num_kv_heads,
                           head_dim, page_size, pages_per_chunk, workspace, workspace_bytes, stream);
 }

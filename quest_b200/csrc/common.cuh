@@ -333,6 +333,28 @@ __device__ __forceinline__ void hist_count(uint32_t* __restrict__ hist, uint32_t
 //   ws_o_off(Hq, nchunks)       fp32 partial outputs [Hq][nchunks][D]
 // The zero-state words sit at fixed offsets so that launches with different chunk counts can share a workspace.
 constexpr size_t kWsSyncBytes = 4096;
+constexpr size_t kWsEpochOff = 64;  // layer step: the step counter of the page-id hand-over (inside the reserved, zero-initialised block)
+
+// Page-id hand-over of the layer step (top-k kernel -> decode kernel without a grid dependency).  The decode launch is released
+// as soon as the top-k CTAs are running; each (head, chunk) decode CTA polls ITS OWN slot of the split-KV partial-output area,
+// where the top-k CTA of that head deposits the chunk's page ids as 8-byte entries (tag : id).  The tag is a NaN bit pattern
+// that carries the step counter, so an entry can be told from a stale partial output (never NaN) or an older step without any
+// fence: an aligned 8-byte store is single-copy atomic.  Saves the grid completion + flush + launch latency between the two
+// kernels and one dependent L2 round trip.  epoch == nullptr: off (the decode kernel waits for the launch before it).
+struct Handoff {
+  uint32_t* epoch;      // workspace + kWsEpochOff: bumped once per step by the estimate launch
+  uint8_t* slots;       // workspace + ws_o_off(Hq, nchunks)
+  uint32_t nchunks, ppc, slot_bytes;  // slot of (head, chunk) at slots + (head * nchunks + chunk) * slot_bytes; ppc * 8 <= slot_bytes
+};
+__device__ __forceinline__ uint32_t handoff_tag(uint32_t epoch) { return 0xfff00000u | (epoch & 0xfffffu); }
+__device__ __forceinline__ void st_relaxed_u64(void* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const void* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
 __host__ __device__ inline size_t ws_ticket_off() { return kWsSyncBytes; }
 constexpr uint32_t kHistBinShift = 5;                               // bin = 16-bit key >> 5
 constexpr uint32_t kHistBins = 1u << (16 - kHistBinShift);          // 2048

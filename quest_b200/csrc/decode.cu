@@ -56,7 +56,7 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
               const __half* __restrict__ kv_, const int32_t* __restrict__ indices_, uint32_t idx_stride,
               uint32_t n_sel, uint32_t last_page_idx_, uint32_t last_page_len_, uint32_t Hkv, uint32_t G,
               uint32_t P, uint32_t p_magic, uint32_t ppc, float sm_scale_log2, uint8_t* __restrict__ ws_,
-              const BatchArgs ba, float* __restrict__ o32) {
+              const BatchArgs ba, float* __restrict__ o32, const uint32_t* __restrict__ ho_epoch, unsigned int* __restrict__ err_word) {
   const __half* __restrict__ q = q_;
   __half* __restrict__ o = o_;
   float* __restrict__ lse = lse_;
@@ -99,11 +99,41 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
   D_STAMP(0);
   const int32_t* idx_row = indices + (size_t)h * idx_stride;
   uint32_t qh[4];  // this lane's 8 q dims as packed halves: q.k runs on mixed-precision FMAs (fp16 x fp16 + fp32, exact products)
-  pdl_wait();  // q, the page ids (top-k kernel) and the last page's new row (append) come from earlier kernels
-  D_STAMP(1);
-  for (uint32_t i = tid; i < npg; i += kThreads)
-    s_pages[i] = pg0 + i < n_sel ? (int32_t)ld_ordered32(idx_row + pg0 + i) : (int32_t)last_page_idx;
-  {
+  if (ho_epoch == nullptr) {
+    pdl_wait();  // q, the page ids (top-k kernel) and the last page's new row (append) come from earlier kernels
+    D_STAMP(1);
+    for (uint32_t i = tid; i < npg; i += kThreads)
+      s_pages[i] = pg0 + i < n_sel ? (int32_t)ld_ordered32(idx_row + pg0 + i) : (int32_t)last_page_idx;
+  } else {
+    // Page-id hand-over (common.cuh, Handoff): no grid dependency.  This launch was released by the top-k kernel once that had
+    // waited for the estimate launch, so q, the appended K/V row and the step counter are complete and visible; the chunk's
+    // page ids arrive as tagged 8-byte entries in this CTA's own partial-output slot, which it overwrites at its end.
+    D_STAMP(1);
+    {
+      const uint4 raw = ld_ordered16(q + (size_t)h * D + lir * 8);  // in flight while the ids are awaited
+      qh[0] = raw.x, qh[1] = raw.y, qh[2] = raw.z, qh[3] = raw.w;
+    }
+    const uint32_t tag = handoff_tag(ld_ordered32(ho_epoch));
+    const uint8_t* slot = ws + ws_o_off(Hq, nchunks) + (size_t)(h * nchunks + chunk) * (D * sizeof(float));
+    for (uint32_t i = tid; i < npg; i += kThreads) {
+      int32_t pid = (int32_t)last_page_idx;
+      if (pg0 + i < n_sel) {
+        unsigned long long v = ld_relaxed_u64(slot + i * 8u);
+        for (uint32_t spins = 0; (uint32_t)(v >> 32) != tag; ++spins) {
+          if (spins > (1u << 22)) {  // seconds: the top-k launch never delivered -- fail loudly, attend to nothing for this id
+            device_error_raise(err_word, QUEST_DEVERR_STEP);
+            v = 0xffffffffull;  // id -1
+            break;
+          }
+          __nanosleep(20);
+          v = ld_relaxed_u64(slot + i * 8u);
+        }
+        pid = (int32_t)(uint32_t)v;
+      }
+      s_pages[i] = pid;
+    }
+  }
+  if (ho_epoch == nullptr) {
     const uint4 raw = ld_ordered16(q + (size_t)h * D + lir * 8);
     qh[0] = raw.x, qh[1] = raw.y, qh[2] = raw.z, qh[3] = raw.w;
   }
@@ -343,7 +373,8 @@ template <int D>
 static int launch_decode(const void* q, void* o, float* lse, const void* kv, const int32_t* indices,
                          uint32_t idx_stride, uint32_t n_sel, uint32_t last_page_idx, uint32_t last_page_len,
                          uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t ppc, void* ws, cudaStream_t stream,
-                         const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, float* o32 = nullptr) {
+                         const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, float* o32 = nullptr,
+                         const uint32_t* ho_epoch = nullptr) {
   const uint32_t nchunks = (n_sel + 1 + ppc - 1) / ppc;
   const uint32_t npg_max = ppc < n_sel + 1 ? ppc : n_sel + 1;
   const size_t smem = (size_t)npg_max * sizeof(int32_t);
@@ -362,9 +393,25 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
   auto kern = decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS>;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, lse,
                                      (const __half*)kv, indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv,
-                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba, o32);
+                                     Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba, o32, ho_epoch,
+                                     ho_epoch ? device_error_word() : nullptr);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
+}
+
+// Layer step with the page-id hand-over (capi.cu): the decode launch takes its page ids from the slots the top-k kernel fills.
+// Usable when the chunk's ids fit its partial-output slot and the plan has more than one chunk.
+bool decode_handoff_fits(uint32_t n_sel, uint32_t D, uint32_t ppc) { return ppc * 8u <= D * sizeof(float) && n_sel + 1 > ppc; }
+int decode_run_handoff(const void* q, void* o, const void* kv, const int32_t* indices, uint32_t n_sel, uint32_t last_page_idx,
+                       uint32_t last_page_len, uint32_t Hq, uint32_t Hkv, uint32_t D, uint32_t P, uint32_t ppc, void* ws,
+                       cudaStream_t s) {
+  const uint32_t* epoch = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(ws) + kWsEpochOff);
+  switch (D) {
+    case 64: return launch_decode<64>(q, o, nullptr, kv, indices, n_sel, n_sel, last_page_idx, last_page_len, Hq, Hkv, P, ppc, ws, s, BatchArgs{}, 1, nullptr, epoch);
+    case 128: return launch_decode<128>(q, o, nullptr, kv, indices, n_sel, n_sel, last_page_idx, last_page_len, Hq, Hkv, P, ppc, ws, s, BatchArgs{}, 1, nullptr, epoch);
+    case 256: return launch_decode<256>(q, o, nullptr, kv, indices, n_sel, n_sel, last_page_idx, last_page_len, Hq, Hkv, P, ppc, ws, s, BatchArgs{}, 1, nullptr, epoch);
+    default: return QUEST_ERR_UNSUPPORTED;
+  }
 }
 
 // descriptor mode (quest_decode_layer_step_batch)

@@ -184,7 +184,8 @@ __global__ void __launch_bounds__(kTileWarps * 32, kG == 104 ? 1 : 2)
 estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uint32_t len_,
                      const __half* __restrict__ meta_, const int32_t* __restrict__ meta_indices_,
                      uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t p_magic /* ceil(2^32/P), 0 for P=1 */,
-                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap_, const BatchArgs ba, uint32_t* __restrict__ hist_) {
+                     uint32_t meta_stable, uint32_t g_shift, const AppendArgs ap_, const BatchArgs ba, uint32_t* __restrict__ hist_,
+                     uint32_t* __restrict__ epoch) {
   // descriptor mode: blockIdx.y = sequence; lengths, page tables and pools come from its device record
   const __half* __restrict__ q = q_;
   __half* __restrict__ o = o_;
@@ -287,6 +288,9 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
 
   if (meta_stable && !carries_append) pdl_wait();
   E_STAMP(2);  // the launch before this one has completed
+  // layer step with the page-id hand-over (common.cuh, Handoff): one thread opens the step; nothing reads the counter before the
+  // top-k kernel, which waits for this whole launch
+  if (epoch != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) *epoch = *epoch + 1u;
   constexpr int kQR = kGr ? kGr : 1;  // q rows a lane keeps in registers
   uint32_t qh[kQR][4], mk[kQR][4];
   if (kG == 1 || kGr) {
@@ -437,7 +441,7 @@ template <int D>
 static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void* meta, const int32_t* meta_indices,
                                 uint32_t Hq, uint32_t Hkv, uint32_t P, uint32_t flags, const AppendArgs& ap,
                                 cudaStream_t stream, const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1,
-                                uint32_t* hist = nullptr) {
+                                uint32_t* hist = nullptr, uint32_t* epoch = nullptr) {
   // descriptor mode (ba.descs): `len` is an upper bound over the batch (sizes the grid and the page-table staging)
   constexpr uint32_t T_r = kTileWarps * (32 / (D / 8));
   static int num_sms = 0;
@@ -486,7 +490,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   cfg.numAttrs = 1;
   const uint32_t p_magic = P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P);
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta, meta_indices,
-                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap, ba, hist);
+                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap, ba, hist, epoch);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -542,20 +546,20 @@ namespace quest {
 int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_data, const int32_t* meta_indices,
                       uint32_t num_qo_heads, uint32_t num_kv_heads, uint32_t head_dim, uint32_t page_size,
                       uint32_t flags, const AppendArgs& ap, cudaStream_t s, const BatchArgs& ba, uint32_t batch,
-                      uint32_t* hist) {
+                      uint32_t* hist, uint32_t* epoch) {
   if ((size_t)num_qo_heads * head_dim * 6 > 160 * 1024) return QUEST_ERR_UNSUPPORTED;
   {  // product path: the tile kernel, whenever the kv heads divide its row tile
     const uint32_t T_r = kTileWarps * (32 / (head_dim / 8));
     const bool force_rows = debug_option(QUEST_DBG_EST_ROWS) != 0;  // test hook: the generic kernel on tile-kernel shapes
     if (!force_rows && len && T_r % num_kv_heads == 0 && (head_dim == 64 || head_dim == 128 || head_dim == 256)) {
       switch (head_dim) {
-        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist);
-        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist);
-        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist);
+        case 64: return launch_estimate_tile<64>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist, epoch);
+        case 128: return launch_estimate_tile<128>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist, epoch);
+        default: return launch_estimate_tile<256>(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, page_size, flags, ap, s, ba, batch, hist, epoch);
       }
     }
   }
-  if (ba.descs != nullptr || hist != nullptr || (flags & kEstMetaFp8)) return QUEST_ERR_UNSUPPORTED;  // tile kernel only
+  if (ba.descs != nullptr || hist != nullptr || epoch != nullptr || (flags & kEstMetaFp8)) return QUEST_ERR_UNSUPPORTED;  // tile kernel only
   if (ap.k != nullptr) {  // generic path: append as its own launch
     const int rc = quest_append_decode(ap.k, ap.v, ap.kv, ap.kv_indices, ap.num_kv_pages, ap.kv_last_len, ap.meta,
                                        meta_indices, ap.num_meta_pages, ap.meta_last_len, num_kv_heads, head_dim,
@@ -588,7 +592,7 @@ extern "C" int quest_estimate(const void* q, void* o, uint32_t len, const void* 
   if (len == 0) return QUEST_OK;
   quest::AppendArgs none = {};
   return quest::estimate_dispatch(q, o, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
-                                  flags, none, (cudaStream_t)stream, quest::BatchArgs{}, 1, nullptr);
+                                  flags, none, (cudaStream_t)stream, quest::BatchArgs{}, 1, nullptr, nullptr);
 }
 
 // fp8 metadata (no counterpart in the reference, whose metadata is fp16 only): the same estimate over
@@ -603,5 +607,5 @@ extern "C" int quest_estimate_fp8(const void* q, void* o, uint32_t len, const vo
   quest::AppendArgs none = {};
   return quest::estimate_dispatch(q, o, len, meta8_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
                                   (flags & QUEST_EST_META_STABLE) | quest::kEstMetaFp8, none, (cudaStream_t)stream,
-                                  quest::BatchArgs{}, 1, nullptr);
+                                  quest::BatchArgs{}, 1, nullptr, nullptr);
 }

@@ -240,7 +240,8 @@ __device__ unsigned long long g_topk_hist_clk[256 * 4];
 template <int G>
 __global__ void __launch_bounds__(kHistThreads)
 topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ hist_, const int32_t* __restrict__ in_idx_,
-                 uint32_t in_stride_, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_, const BatchArgs ba) {
+                 uint32_t in_stride_, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_, const BatchArgs ba,
+                 const Handoff ho) {
   constexpr int NK = 4 * G, W = kHistThreads / 32;
   constexpr uint32_t BPT = kHistBins / kHistThreads;  // 4 bins = two packed words per thread
   static_assert(BPT == 4, "one 8-byte load of bin totals per thread");
@@ -250,13 +251,14 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
   int32_t* __restrict__ out_idx = out_idx_;
   uint32_t* __restrict__ hist = hist_;
   uint32_t in_stride = in_stride_, len = len_, k = k_;
-#if QUEST_TRIG_TOPK
-  pdl_trigger();
-#endif
+  // hand-over mode: the decode launch may start now; its CTAs poll for the ids this kernel deposits (common.cuh, Handoff)
+  // (releasing it later, once the threshold bin is known, measured the same: 18.15 against 18.13 us per layer step)
+  if (QUEST_TRIG_TOPK || ho.epoch != nullptr) pdl_trigger();
   if (t < 32) s_sub[t] = 0;
   TH_STAMP(0);
   pdl_wait();  // scores and bin totals come from the estimate kernel
   TH_STAMP(1);
+  const unsigned long long tag = ho.epoch != nullptr ? (unsigned long long)handoff_tag(ld_ordered32(ho.epoch)) << 32 : 0ull;
   if (ba.descs != nullptr) {  // descriptor mode, as in topk_fast_kernel
     const SeqDesc* d = ba.descs + blockIdx.y;
     len = d->num_kv_pages - 1;
@@ -369,7 +371,14 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
     const bool in = (uint32_t)j < nvalid;
     const bool gt = in && key[j] + bump > tau, eq = in && key[j] + bump == tau;
     const uint32_t pos = gt_before + min(eq_before, need2);
-    if ((gt || (eq && eq_before < need2)) && pos < k) out[pos] = pay[j];  // pos < k always, unless the totals were not at rest
+    if ((gt || (eq && eq_before < need2)) && pos < k) {  // pos < k always, unless the totals were not at rest
+      out[pos] = pay[j];
+      if (ho.epoch != nullptr) {
+        const uint32_t chunk = pos / ho.ppc;
+        st_relaxed_u64(ho.slots + (size_t)(head * ho.nchunks + chunk) * ho.slot_bytes + (pos - chunk * ho.ppc) * 8u,
+                       tag | (uint32_t)pay[j]);
+      }
+    }
     gt_before += gt;
     eq_before += eq;
   }
@@ -385,7 +394,7 @@ extern "C" int quest_debug_topk_hist_clocks(unsigned long long* host_out, uint32
 template <int G>
 static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
                             uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream,
-                            const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1) {
+                            const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, const Handoff& ho = Handoff{}) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(num_heads, batch);
   cfg.blockDim = dim3(kHistThreads);
@@ -395,7 +404,7 @@ static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* i
   attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba, ho);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -403,10 +412,11 @@ static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* i
 // Layer step: rows whose bin totals the estimate kernel has published in `hist` (max_len bounds every row).
 bool topk_hist_covers(uint32_t max_len) { return max_len <= 16u * kHistThreads && debug_option(QUEST_DBG_TOPK_NO_HIST) == 0; }
 int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
-                   uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s) {
-  if (max_len <= 4u * kHistThreads) return launch_topk_hist<1>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch);
-  if (max_len <= 8u * kHistThreads) return launch_topk_hist<2>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch);
-  if (max_len <= 16u * kHistThreads) return launch_topk_hist<4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch);
+                   uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s,
+                   const Handoff& ho) {
+  if (max_len <= 4u * kHistThreads) return launch_topk_hist<1>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
+  if (max_len <= 8u * kHistThreads) return launch_topk_hist<2>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
+  if (max_len <= 16u * kHistThreads) return launch_topk_hist<4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
   return QUEST_ERR_UNSUPPORTED;
 }
 
@@ -485,7 +495,7 @@ extern "C" int quest_debug_topk_hist(const void* scores, const int32_t* in_idx, 
   if (!scores || !out_idx || !hist || !num_heads || k > len || !quest::topk_hist_covers(len)) return QUEST_ERR_BAD_ARG;
   cudaStream_t s = (cudaStream_t)stream;
   quest::hist_build_kernel<<<dim3(8, num_heads), 256, 0, s>>>((const __half*)scores, (uint32_t*)hist, len);
-  return quest::topk_from_hist(scores, (uint32_t*)hist, in_idx, in_idx_row_stride, out_idx, num_heads, len, k, quest::BatchArgs{}, 1, s);
+  return quest::topk_from_hist(scores, (uint32_t*)hist, in_idx, in_idx_row_stride, out_idx, num_heads, len, k, quest::BatchArgs{}, 1, s, quest::Handoff{});
 }
 
 extern "C" uint32_t quest_topk_max_len(void) { return quest::kTopkMaxLen; }

@@ -30,6 +30,8 @@ def main():
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     lib = K.load_library()
+    if os.environ.get("QUEST_NO_HANDOFF"):  # A/B: the layer step's decode launch waits for the top-k launch
+        lib.quest_debug_set_option(K.DBG_NO_HANDOFF, 1)
     Hq, Hkv, L = a.hq, a.hkv, a.layers
     ic = qu.InferenceController(L, Hq, D, P, a.budget // P, a.ctx, torch.float16, dev, num_kv_heads=Hkv)
     fill(ic, L, a.ctx - 1, Hkv, dev)
