@@ -410,13 +410,14 @@ static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* i
 }
 
 // Layer step: rows whose bin totals the estimate kernel has published in `hist` (max_len bounds every row).
-bool topk_hist_covers(uint32_t max_len) { return max_len <= 16u * kHistThreads && debug_option(QUEST_DBG_TOPK_NO_HIST) == 0; }
+bool topk_hist_covers(uint32_t max_len) { return max_len <= 32u * kHistThreads && debug_option(QUEST_DBG_TOPK_NO_HIST) == 0; }
 int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
                    uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s,
                    const Handoff& ho) {
   if (max_len <= 4u * kHistThreads) return launch_topk_hist<1>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
   if (max_len <= 8u * kHistThreads) return launch_topk_hist<2>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
   if (max_len <= 16u * kHistThreads) return launch_topk_hist<4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
+  if (max_len <= 32u * kHistThreads) return launch_topk_hist<8>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
   return QUEST_ERR_UNSUPPORTED;
 }
 
