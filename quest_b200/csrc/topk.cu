@@ -238,7 +238,7 @@ __device__ unsigned long long g_topk_hist_clk[256 * 4];
 #endif
 
 template <int G>
-__global__ void __launch_bounds__(kHistThreads)
+__global__ void __launch_bounds__(kHistThreads, (G >= 4 && G <= 6) ? 2 : 0)  // two rows per SM while 64 registers hold the keys (batched steps: rows > SMs)
 topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ hist_, const int32_t* __restrict__ in_idx_,
                  uint32_t in_stride_, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_, const BatchArgs ba,
                  const Handoff ho) {
@@ -417,6 +417,9 @@ int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, ui
   if (max_len <= 4u * kHistThreads) return launch_topk_hist<1>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
   if (max_len <= 8u * kHistThreads) return launch_topk_hist<2>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
   if (max_len <= 16u * kHistThreads) return launch_topk_hist<4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
+  // in-between bounds: a batch just past 8192 pages (BASELINE configs[3]: 8193) pays for the keys per thread it is compiled for
+  if (max_len <= 20u * kHistThreads) return launch_topk_hist<5>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
+  if (max_len <= 24u * kHistThreads) return launch_topk_hist<6>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
   if (max_len <= 32u * kHistThreads) return launch_topk_hist<8>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
   return QUEST_ERR_UNSUPPORTED;
 }

@@ -15,7 +15,7 @@ import torch
 from quest_b200 import _kernels
 from quest_b200.utils.controller import InferenceController
 
-_BUCKETS = (1024, 2048, 4096, 8192, 16384)  # row lengths of the register-resident top-k variants
+_BUCKETS = (1024, 2048, 4096, 8192, 10240, 12288, 16384)  # row lengths of the bin-total / register-resident top-k variants
 
 
 class BatchDecodeStep:
