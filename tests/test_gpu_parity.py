@@ -671,3 +671,63 @@ def test_error_behaviour_matches_reference_checks():
     with pytest.raises(RuntimeError, match="CHECK_GE"):
         K.topk_filtering(torch.zeros(H, 4, dtype=torch.float16, device=DEV), torch.zeros(H, 4, dtype=torch.int32, device=DEV),
                          torch.zeros(H, 9, dtype=torch.float16, device=DEV), torch.zeros(H, 9, dtype=torch.int32, device=DEV), None, 9)
+
+
+def test_layer_step_handoff_stress():
+    """The page-id hand-over (top-k kernel -> polling decode CTAs, csrc/common.cuh Handoff) over many back-to-back steps that share
+    ONE workspace, alternating two budgets (two chunk layouts over the same partial-output area) and replayed from a CUDA graph:
+    every step's selected ids and output must equal, bit for bit, the same steps run with the decode launch waiting for the
+    top-k launch (DBG_NO_HANDOFF), and no device error may be raised."""
+    import ctypes
+    H, D, P, kv_len = 32, 128, 16, 9000
+    oc, gc, k, v, rng = make_pair(kv_len, P, H, D, seed=77)
+    lib = K.load_library()
+    n_pages = len(oc.kv_indices)
+    n = n_pages - 1
+    kvi, kvp, mi, mp = gc.tables()
+    budgets = [128, 40]
+    plans = []
+    for b in budgets:
+        ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
+        assert lib.quest_decode_plan(b - 1, H, H, D, P, 148, ctypes.byref(ppc), ctypes.byref(nch)) == 0
+        plans.append((b - 1, ppc.value, nch.value))
+    ws = torch.zeros(max(lib.quest_decode_workspace_bytes(H, D, p[2]) for p in plans), dtype=torch.uint8, device=DEV)
+    steps = 24
+    qs = torch.randn(steps, 1, H, D, device=DEV).half()
+    scores = torch.empty(H, n, dtype=torch.float16, device=DEV)
+
+    def run(no_handoff):
+        outs = torch.zeros(steps, 1, H, D, dtype=torch.float16, device=DEV)
+        ids = [torch.full((H, plans[i % 2][0]), -7, dtype=torch.int32, device=DEV) for i in range(steps)]
+        ws.zero_()
+        with K.debug_option(K.DBG_NO_HANDOFF, 1 if no_handoff else 0):
+            def chain():
+                st = torch.cuda.current_stream().cuda_stream
+                for i in range(steps):
+                    kk, ppc, _ = plans[i % 2]
+                    assert lib.quest_sparse_decode_step(qs[i].data_ptr(), outs[i].data_ptr(), gc.kv.data_ptr(), kvi.data_ptr(), n,
+                                                        oc.kv_indices[-1], oc.last_page_len, gc.meta.data_ptr(), mi.data_ptr(),
+                                                        scores.data_ptr(), ids[i].data_ptr(), kk, H, H, D, P, ppc, ws.data_ptr(),
+                                                        ws.numel(), st) == 0
+            chain()  # eager
+            torch.cuda.synchronize()
+            eager = outs.clone()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side):
+                    chain()
+                for _ in range(5):
+                    g.replay()
+            side.synchronize()
+            torch.cuda.synchronize()
+        assert torch.equal(eager, outs)
+        return outs.clone(), [x.clone() for x in ids]
+
+    o_ref, i_ref = run(True)
+    o_new, i_new = run(False)
+    assert lib.quest_device_error() == 0
+    assert torch.equal(o_ref, o_new)
+    for a, b in zip(i_ref, i_new):
+        assert torch.equal(a, b) and int(a.min()) >= 0

@@ -87,3 +87,38 @@ def test_argument_checks_of_the_batched_and_peer_entry_points_need_no_gpu():
     off_rec, off_flags, total = SeqShardedDecode._peer_layout(lib, 32, 128, 511, 8)
     assert off_rec == 2 * 8 * 32 * 512 * 2 and off_flags >= off_rec + 2 * 8 * (32 * 128 + 32) * 4
     assert off_flags % 16 == 0 and total >= off_flags + 2 * 8 * 4
+
+
+def test_argument_checks_of_the_round2_entry_points_need_no_gpu():
+    """quest_rope_append_prefill / quest_prefill_layer_step (row f-3) and the fp8 metadata entry points (row f-4) reject bad
+    arguments on the host, before any CUDA call."""
+    import ctypes
+
+    import quest_b200._kernels as K
+    lib = K.load_library()
+    one = ctypes.c_void_p(16)
+    prod = [one, one, one, 2, one, one, 1, 2, one, one, 1]  # q k v append_len kv idx pages last_len meta midx meta_pages
+    assert lib.quest_rope_append_prefill(*prod, 1, 1, 96, 16, 1.0, 1e4, 0, None) == -2   # head_dim not built
+    assert lib.quest_rope_append_prefill(*prod, 1, 1, 128, 16, 0.0, 1e4, 0, None) == -1  # rope_scale must be positive
+    assert lib.quest_rope_append_prefill(*prod, 1, 1, 128, 16, 1.0, -1.0, 0, None) == -1
+    assert lib.quest_rope_append_prefill(None, *prod[1:], 1, 1, 128, 16, 1.0, 1e4, 0, None) == -1
+    bad = list(prod)
+    bad[3] = 40  # more new tokens than the cache holds
+    assert lib.quest_rope_append_prefill(*bad, 1, 1, 128, 16, 1.0, 1e4, 0, None) == -1
+    bad = list(prod)
+    bad[7] = 17  # last page longer than a page
+    assert lib.quest_rope_append_prefill(*bad, 1, 1, 128, 16, 1.0, 1e4, 0, None) == -1
+    none_new = list(prod)
+    none_new[3] = 0  # nothing to append: a no-op
+    assert lib.quest_rope_append_prefill(*none_new, 1, 1, 128, 16, 1.0, 1e4, 0, None) == 0
+    layer = [one, one, one, None, 2, one, one, 1, 2, one, one, 1]  # o missing
+    assert lib.quest_prefill_layer_step(*layer, 1, 1, 128, 16, 1.0, 1e4, 0, None) == -1
+    # fp8 metadata
+    assert lib.quest_metadata_to_fp8(one, one, 3, 2, one, 1, 128, 16, None) == -1
+    assert lib.quest_metadata_to_fp8(one, one, 0, 1, one, 1, 96, 16, None) == -2
+    assert lib.quest_metadata_to_fp8(one, one, 5, 5, one, 1, 128, 16, None) == 0  # empty range
+    assert lib.quest_estimate_fp8(one, one, 4, None, one, 1, 1, 128, 16, 0, None) == -1
+    assert lib.quest_estimate_fp8(one, one, 4, one, one, 3, 2, 128, 16, 0, None) == -1
+    assert lib.quest_estimate_fp8(one, one, 0, one, one, 1, 1, 128, 16, 0, None) == 0
+    step = [one, one, one, one, one, one, 4, 0, 1, one, None, one, 1, 4, one, one, 2, 1, 1, 128, 16, 4, one, 1 << 20, None]
+    assert lib.quest_decode_layer_step_fp8(*step) == -1  # no e4m3 pool
