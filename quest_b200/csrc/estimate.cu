@@ -178,7 +178,8 @@ __device__ unsigned long long g_est_clk[1024 * 4];
 // Groups of 4 in registers: 16 registers of q + 16 of sign masks do not fit the 64-register budget of two 16-warp CTAs per SM,
 // so that instantiation runs one CTA per SM at up to 128 registers.  Measured alternatives (32q/8kv, 128K: 11.9 us with one lane
 // row per q head): this layout 10.2 us; the same with the ring in shared memory (per-lane cp.async slots, 192 KB in flight per
-// SM) 12.45 us; two CTAs per SM with the masks rebuilt by PRMT spills (profiles/r02_gqa_estimate.txt).
+// SM) 12.45 us; a register ring of 8 stages with the masks rebuilt by PRMT (128 KB in flight at one CTA per SM) 11.3 us;
+// two CTAs per SM with the masks rebuilt by PRMT spills (profiles/r02_b_experiments.md).
 template <int D, int kOrdered, int kG>
 __global__ void __launch_bounds__(kTileWarps * 32, kG == 104 ? 1 : 2)
 estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uint32_t len_,
