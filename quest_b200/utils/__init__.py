@@ -87,6 +87,11 @@ def append_kv(k: torch.Tensor, v: torch.Tensor, iController: InferenceController
         iController.metadata_last_page_idx,
         iController.layout,
     )
+    if iController.fp8_metadata:  # e4m3 copies of the entries of every page this append touched
+        n_pages = iController.kv_indices_with_last.size(0)
+        first = (iController.kv_cache.seqlen - seq_len) // iController.page_size
+        _kernels.metadata_to_fp8(iController.metadata_cache.buf_layer(layer_idx), iController.metadata_indices, first, n_pages,
+                                 iController.meta8[layer_idx])
 
 
 def prefill_forward(q: torch.Tensor, iController: InferenceController, layer_idx: int,
@@ -130,6 +135,10 @@ def prefill_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iContr
         1e4 if rope_theta is None else rope_theta,
         write_back_k,
     )
+    if iController.fp8_metadata:
+        first = (iController.kv_cache.seqlen - k.size(0)) // iController.page_size
+        _kernels.metadata_to_fp8(iController.metadata_cache.buf_layer(layer_idx), iController.metadata_indices, first,
+                                 iController.kv_indices_with_last.size(0), iController.meta8[layer_idx])
     _nvtx.range_pop()
     return o
 
@@ -137,6 +146,9 @@ def prefill_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iContr
 def decode_estimate(q: torch.Tensor, iController: InferenceController, layer_idx: int) -> torch.Tensor:
     """Upper-bound attention score per page and head, last page excluded (reference __init__.py:171-205)."""
     o = torch.empty((iController.num_heads, iController.metadata_cache.seqlen - 1), dtype=q.dtype, device=q.device)
+    if iController.fp8_metadata:
+        _kernels.estimate_attn_score_fp8(q, o, iController.meta8[layer_idx], iController.metadata_indices)
+        return o
     _kernels.estimate_attn_score(
         q,
         o,
@@ -187,7 +199,7 @@ def decode_sparse_attn(q: torch.Tensor, iController: InferenceController, layer_
 class _BoundStep:
     """Everything of a decode_layer_step call that does not change between the layers of one token: validated once
     per begin_forward, so that the per-layer cost is a handful of data_ptr() calls and one ctypes call."""
-    __slots__ = ("fn", "mid", "tail", "kv_ptrs", "meta_ptrs", "qshape", "kshape", "dtype", "device")
+    __slots__ = ("fn", "mid", "tail", "kv_ptrs", "meta_ptrs", "qshape", "kshape", "dtype", "device")  # meta_ptrs: tuples of pointers
 
     def __init__(self, ic: InferenceController, q, k, v):
         w = ic._decode_handler._wrapper
@@ -197,12 +209,15 @@ class _BoundStep:
         args = w.layer_step_args(q, k, v, torch.empty_like(q), L, ic.kv_indices_with_last, ic.kv_cache.last_page_len,
                                  ic.kv_last_page_idx, ic.metadata_cache.buf_layer(0), ic.metadata_indices,
                                  ic.metadata_cache.last_page_len, scores, ic.topk_dindices_buffer)
-        self.fn = _kernels.load_library().quest_decode_layer_step
+        lib = _kernels.load_library()
+        self.fn = lib.quest_decode_layer_step_fp8 if ic.fp8_metadata else lib.quest_decode_layer_step
         self.mid = args[5:9]     # kv_indices, num_kv_pages, last idx, last len
         self.tail = args[10:]    # meta_indices ... workspace_bytes (stream appended per call)
         layers = range(ic.kv_cache.pool.num_layers)
         self.kv_ptrs = [ic.kv_cache.buf_layer(i).data_ptr() for i in layers]
-        self.meta_ptrs = [ic.metadata_cache.buf_layer(i).data_ptr() for i in layers]
+        # (metadata pool,) or (metadata pool, its e4m3 copy): the fp8 entry point takes both, in this order
+        self.meta_ptrs = [(ic.metadata_cache.buf_layer(i).data_ptr(),) + ((ic.meta8[i].data_ptr(),) if ic.fp8_metadata else ())
+                          for i in layers]
         self.qshape, self.kshape, self.dtype, self.device = q.shape, k.shape, q.dtype, q.device
 
 
@@ -238,7 +253,7 @@ def decode_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iContro
     _nvtx.range_push("topk")
     _nvtx.range_push("approx_attn")
     rc = st.fn(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), st.kv_ptrs[layer_idx], *st.mid,
-               st.meta_ptrs[layer_idx], *st.tail, torch.cuda.current_stream().cuda_stream)
+               *st.meta_ptrs[layer_idx], *st.tail, torch.cuda.current_stream().cuda_stream)
     _nvtx.range_pop(), _nvtx.range_pop(), _nvtx.range_pop(), _nvtx.range_pop()
     if rc:
         _kernels._rc(rc, "decode_layer_step")

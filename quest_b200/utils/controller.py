@@ -17,14 +17,20 @@ class InferenceController:
     def __init__(self, num_layers, num_heads, head_dim, page_size,
                  page_budget,  # Real page budget including the last page
                  max_seq_len,  # Real max for allocating kv / metadata
-                 dtype, device, num_kv_heads=None):
+                 dtype, device, num_kv_heads=None, fp8_metadata=False):
         # num_kv_heads (extension): GQA pools hold num_kv_heads heads while estimate/top-k/decode run per q head.
+        # fp8_metadata (extension, off by default): keep an e4m3 copy of the page metadata, rounded
+        # outward, and score from it -- the estimate streams half the bytes; scores are upper bounds of the reference's, not
+        # bit-identical to them.  The reference has fp16 metadata only.
         max_kv_pages_num = (max_seq_len + page_size - 1) // page_size
         self.num_kv_heads = num_heads if num_kv_heads is None else num_kv_heads
         self.kv_cache = KvCache(num_layers=num_layers, num_heads=self.num_kv_heads, head_dim=head_dim,
                                 max_seq_len=max_seq_len, page_size=page_size, dtype=dtype, device=device)
         self.metadata_cache = KvCache(num_layers=num_layers, num_heads=self.num_kv_heads, head_dim=head_dim,
                                       max_seq_len=max_kv_pages_num, page_size=page_size, dtype=dtype, device=device)
+        self.fp8_metadata = bool(fp8_metadata)
+        self.meta8 = torch.zeros((num_layers,) + tuple(self.metadata_cache.buf_layer(0).shape), dtype=torch.uint8,
+                                 device=device) if self.fp8_metadata else None  # [layers, meta pages, 2, page, kv heads, dim]
         self.layout = TensorLayout.NHD
         self.device = device
         self.dtype = dtype

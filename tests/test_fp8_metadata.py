@@ -152,3 +152,46 @@ def test_fp8_argument_checks():
     assert lib.quest_metadata_to_fp8(None, idx.data_ptr(), 0, 1, z.data_ptr(), 1, 128, 16, None) == -1
     assert lib.quest_estimate_fp8(z.data_ptr(), z.data_ptr(), 4, None, idx.data_ptr(), 1, 1, 128, 16, 0, None) == -1
     assert lib.quest_estimate_fp8(z.data_ptr(), z.data_ptr(), 4, z.data_ptr(), idx.data_ptr(), 3, 2, 128, 16, 0, None) == -1
+
+
+@gpu
+def test_fp8_flag_on_the_operator_surface():
+    """InferenceController(fp8_metadata=True): prefill through append_kv, then decode tokens once with the four operators and
+    once with decode_layer_step on a twin controller -- same scores (the fp8 estimate), same selected pages, same output; the
+    e4m3 pool equals the outward rounding of the fp16 pool for every page."""
+    import quest_b200.utils as qu
+    L, H, D, P, budget, n0 = 2, 32, 128, 16, 32, 1000
+    rng = np.random.default_rng(5)
+    a = qu.InferenceController(L, H, D, P, budget, 2048, torch.float16, torch.device(DEV), fp8_metadata=True)
+    b = qu.InferenceController(L, H, D, P, budget, 2048, torch.float16, torch.device(DEV), fp8_metadata=True)
+    k0 = torch.from_numpy(rng.standard_normal((n0, H, D), dtype=np.float32).astype(np.float16)).to(DEV)
+    v0 = torch.from_numpy(rng.standard_normal((n0, H, D), dtype=np.float32).astype(np.float16)).to(DEV)
+    for ic in (a, b):
+        ic.prepare_metadata(n0), ic.begin_forward(n0)
+        for l in range(L):
+            qu.append_kv(k0, v0, ic, l)
+        ic.end_forward()
+    for step in range(20):  # crosses a page boundary
+        q = torch.randn(1, H, D, device=DEV).half()
+        k1, v1 = torch.randn(1, H, D, device=DEV).half(), torch.randn(1, H, D, device=DEV).half()
+        a.prepare_metadata(1), a.begin_forward(1)
+        b.prepare_metadata(1), b.begin_forward(1)
+        for l in range(L):
+            qu.append_kv(k1, v1, a, l)
+            sc = qu.decode_estimate(q, a, l)
+            qu.decode_topk(sc, a)
+            o1 = qu.decode_sparse_attn(q, a, l, a.topk_dindices_buffer)
+            o2 = qu.decode_layer_step(q, k1, v1, b, l)
+            assert torch.equal(o1, o2), (step, l)
+            assert torch.equal(a.topk_dindices_buffer, b.topk_dindices_buffer)
+        a.end_forward(), b.end_forward()
+    torch.cuda.synchronize()
+    n_pages = len(a.kv_cache.indicies)
+    for ic in (a, b):
+        for l in range(L):
+            meta = ic.metadata_cache.buf_layer(l).cpu().numpy()
+            got = ic.meta8[l].cpu().numpy()
+            want = orc.metadata_to_fp8(meta)
+            for j in range(n_pages):
+                m, e = ic.metadata_cache.indicies[j // P], j % P
+                np.testing.assert_array_equal(orc.E4M3_VALUES[got[m, :, e]], orc.E4M3_VALUES[want[m, :, e]])
