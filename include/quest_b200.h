@@ -292,6 +292,22 @@ int quest_decode_layer_step_fp8(const void* q, const void* k_new, const void* v_
                                 uint32_t page_size, uint32_t pages_per_chunk, void* workspace,
                                 size_t workspace_bytes, void* stream);
 
+/* ---- estimate + selection with scores out (phase 1 of the sequence-sharded step) ------------------------------------
+ * No counterpart in the reference (it has no multi-GPU path; SURVEY.md section 8 row e).  quest_estimate over the first `len`
+ * pages of the table (optionally carrying append_kv of one new token like quest_decode_layer_step: k_new != NULL), then the k
+ * best pages per q head selected from the bin totals the estimate publishes: their scores (fp16) into out_val and their
+ * payload ids (kv_indices[page]) into out_idx, rows out_val_stride / out_idx_stride elements apart (0 = k), in ascending page
+ * order as quest_topk.  flags: QUEST_EST_META_* as for quest_estimate.  workspace: a quest_decode_workspace_bytes() block,
+ * zero when first used.  QUEST_ERR_UNSUPPORTED (nothing launched): shapes / lengths the bin-total path does not take --
+ * use quest_append_decode + quest_estimate + quest_topk. */
+int quest_estimate_select(const void* q, const void* k_new, const void* v_new, void* kv_data, const int32_t* kv_indices,
+                          uint32_t num_kv_pages, uint32_t kv_last_page_len, void* meta_data,
+                          const int32_t* meta_indices, uint32_t num_meta_pages, uint32_t meta_last_page_len,
+                          uint32_t len, void* scores, void* out_val, uint32_t out_val_stride, int32_t* out_idx,
+                          uint32_t out_idx_stride, uint32_t k, uint32_t num_qo_heads, uint32_t num_kv_heads,
+                          uint32_t head_dim, uint32_t page_size, uint32_t flags, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
 /* ---- combine of partial attention states (sequence-sharded multi-GPU path) ----------------------
  * Merges n partial states (o_i fp32 [n, num_heads, head_dim] normalised, lse_i fp32 [n, num_heads]
  * base-2) into o fp16 [num_heads, head_dim]: flashinfer state.cuh:53-62 / cascade.cuh:279-340.

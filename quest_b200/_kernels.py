@@ -49,6 +49,8 @@ SIGNATURES = {
     "quest_estimate_fp8": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _u32, _vp]),
     "quest_decode_layer_step_fp8": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _i32p, _u32, _u32, _u32, _vp, _vp, _i32p, _u32, _u32, _vp,
                                                _i32p, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
+    "quest_estimate_select": (_c.c_int, [_vp, _vp, _vp, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _vp, _vp, _u32, _i32p,
+                                         _u32, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_merge_states": (_c.c_int, [_vp, _vp, _u32, _u32, _vp, _vp, _u32, _u32, _vp]),
     "quest_peer_staging_bytes": (_sz, [_u32, _u32, _u32]),
     "quest_peer_allgather": (_c.c_int, [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _u32, _u32, _u32, _vp]),

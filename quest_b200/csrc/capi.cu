@@ -16,7 +16,7 @@ int estimate_dispatch(const void* q, void* o, uint32_t len, const void* meta_dat
 bool topk_hist_covers(uint32_t max_len);  // topk.cu
 int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
                    uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s,
-                   const Handoff& ho = Handoff{});  // topk.cu
+                   const Handoff& ho = Handoff{}, const HistOut& xo = HistOut{});  // topk.cu
 bool decode_handoff_fits(uint32_t n_sel, uint32_t D, uint32_t ppc);  // decode.cu
 int decode_run_handoff(const void* q, void* o, const void* kv, const int32_t* indices, uint32_t n_sel, uint32_t last_page_idx,
                        uint32_t last_page_len, uint32_t Hq, uint32_t Hkv, uint32_t D, uint32_t P, uint32_t ppc, void* ws,
@@ -272,4 +272,39 @@ extern "C" int quest_prefill_layer_step(void* q, void* k, const void* v, void* o
   if (rc != QUEST_OK) return rc;
   return quest_prefill(q, o, append_len, kv_data, kv_indices, num_kv_pages, kv_last_page_len, 1, num_qo_heads, num_kv_heads,
                        head_dim, page_size, stream);
+}
+
+// estimate (optionally carrying the step's append_kv) + selection from the bin totals, with the selected SCORES as well as the
+// payload ids and with output row strides: phase 1 of the sequence-sharded step (quest_b200.parallel.SeqShardedDecode.candidates),
+// where a rank's best pages travel as scores and its ids go into its columns of the global payload row.  Two launches chained
+// with programmatic dependent launch instead of append + estimate + top-k + two copies.  No counterpart in the reference (it
+// has no multi-GPU path); the kernels are those of quest_decode_layer_step.
+extern "C" int quest_estimate_select(const void* q, const void* k_new, const void* v_new, void* kv_data, const int32_t* kv_indices,
+                                     uint32_t num_kv_pages, uint32_t kv_last_page_len, void* meta_data,
+                                     const int32_t* meta_indices, uint32_t num_meta_pages, uint32_t meta_last_page_len,
+                                     uint32_t len, void* scores, void* out_val, uint32_t out_val_stride, int32_t* out_idx,
+                                     uint32_t out_idx_stride, uint32_t k, uint32_t num_qo_heads, uint32_t num_kv_heads,
+                                     uint32_t head_dim, uint32_t page_size, uint32_t flags, void* workspace,
+                                     size_t workspace_bytes, void* stream) {
+  if (!q || !meta_data || !meta_indices || !scores || !out_idx || !kv_indices) return QUEST_ERR_BAD_ARG;
+  if (!num_qo_heads || !num_kv_heads || !page_size || num_qo_heads % num_kv_heads) return QUEST_ERR_BAD_ARG;
+  if (k == 0 || k > len || len > num_kv_pages) return QUEST_ERR_BAD_ARG;
+  if ((out_val_stride && out_val_stride < k) || (out_idx_stride && out_idx_stride < k)) return QUEST_ERR_BAD_ARG;
+  quest::AppendArgs ap = {};
+  if (k_new != nullptr) {
+    if (!v_new || !kv_data || !num_kv_pages || !num_meta_pages) return QUEST_ERR_BAD_ARG;
+    if (kv_last_page_len < 1 || kv_last_page_len > page_size || meta_last_page_len < 1 || meta_last_page_len > page_size)
+      return QUEST_ERR_BAD_ARG;
+    ap = {(const __half*)k_new, (const __half*)v_new, (__half*)kv_data, kv_indices, (__half*)meta_data,
+          num_kv_pages, kv_last_page_len, num_meta_pages, meta_last_page_len, nullptr};
+  }
+  uint32_t* hist = quest::step_hist(workspace, workspace_bytes, num_qo_heads, len);
+  if (!hist) return QUEST_ERR_UNSUPPORTED;  // no room for the bin totals / rows beyond their reach: the caller uses the separate ops
+  int rc = quest::estimate_dispatch(q, scores, len, meta_data, meta_indices, num_qo_heads, num_kv_heads, head_dim, page_size,
+                                    flags & (QUEST_EST_META_ORDERED | QUEST_EST_META_STABLE), ap, (cudaStream_t)stream,
+                                    quest::BatchArgs{}, 1, hist);
+  if (rc) return rc;  // QUEST_ERR_UNSUPPORTED before anything was launched: shapes only the generic estimate kernel takes
+  const quest::HistOut xo = {(uint16_t*)out_val, out_val_stride, out_idx_stride};
+  return quest::topk_from_hist(scores, hist, kv_indices, 0, out_idx, num_qo_heads, len, k, quest::BatchArgs{}, 1, (cudaStream_t)stream,
+                               quest::Handoff{}, xo);
 }

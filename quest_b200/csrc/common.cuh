@@ -346,6 +346,13 @@ struct Handoff {
   uint8_t* slots;       // workspace + ws_o_off(Hq, nchunks)
   uint32_t nchunks, ppc, slot_bytes;  // slot of (head, chunk) at slots + (head * nchunks + chunk) * slot_bytes; ppc * 8 <= slot_bytes
 };
+// Optional outputs of the bin-total top-k beyond the dense [heads, k] id list: the selected scores themselves (fp16 bits) and row
+// strides in elements (0 = k), so that a caller can have both written straight into a slice of a larger array (the sequence-
+// sharded step's candidate message and payload row).
+struct HistOut {
+  uint16_t* val;
+  uint32_t val_stride, idx_stride;
+};
 __device__ __forceinline__ uint32_t handoff_tag(uint32_t epoch) { return 0xfff00000u | (epoch & 0xfffffu); }
 __device__ __forceinline__ void st_relaxed_u64(void* p, unsigned long long v) {
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");

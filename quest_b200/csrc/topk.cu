@@ -241,7 +241,7 @@ template <int G>
 __global__ void __launch_bounds__(kHistThreads, (G >= 4 && G <= 6) ? 2 : 0)  // two rows per SM while 64 registers hold the keys (batched steps: rows > SMs)
 topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ hist_, const int32_t* __restrict__ in_idx_,
                  uint32_t in_stride_, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_, const BatchArgs ba,
-                 const Handoff ho) {
+                 const Handoff ho, const HistOut xo) {
   constexpr int NK = 4 * G, W = kHistThreads / 32;
   constexpr uint32_t BPT = kHistBins / kHistThreads;  // 4 bins = two packed words per thread
   static_assert(BPT == 4, "one 8-byte load of bin totals per thread");
@@ -274,7 +274,10 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
   const uint2 hv = *hp;
   *hp = make_uint2(0u, 0u);
   if (k > len) {
-    for (uint32_t i = len + t; i < k_; i += kHistThreads) out_idx[(size_t)head * k_ + i] = -1;
+    for (uint32_t i = len + t; i < k_; i += kHistThreads) {
+      out_idx[(size_t)head * (xo.idx_stride ? xo.idx_stride : k_) + i] = -1;
+      if (xo.val != nullptr) xo.val[(size_t)head * (xo.val_stride ? xo.val_stride : k_) + i] = 0xfc00u;  // -inf: sorts last
+    }
     k = len;
   }
   if (k == 0) return;
@@ -365,7 +368,8 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
   for (int w = 0; w < W; ++w)
     if ((uint32_t)w < warp) before += s_wtot2[w];
   uint32_t gt_before = before >> 16, eq_before = before & 0xffffu;
-  int32_t* out = out_idx + (size_t)head * k_;
+  int32_t* out = out_idx + (size_t)head * (xo.idx_stride ? xo.idx_stride : k_);
+  uint16_t* outv = xo.val != nullptr ? xo.val + (size_t)head * (xo.val_stride ? xo.val_stride : k_) : nullptr;
 #pragma unroll
   for (int j = 0; j < NK; ++j) {
     const bool in = (uint32_t)j < nvalid;
@@ -373,6 +377,7 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
     const uint32_t pos = gt_before + min(eq_before, need2);
     if ((gt || (eq && eq_before < need2)) && pos < k) {  // pos < k always, unless the totals were not at rest
       out[pos] = pay[j];
+      if (outv != nullptr) outv[pos] = (key[j] & 0x8000u) ? (uint16_t)(key[j] & 0x7fffu) : (uint16_t)~key[j];  // score_key undone
       if (ho.epoch != nullptr) {
         const uint32_t chunk = pos / ho.ppc;
         st_relaxed_u64(ho.slots + (size_t)(head * ho.nchunks + chunk) * ho.slot_bytes + (pos - chunk * ho.ppc) * 8u,
@@ -394,7 +399,8 @@ extern "C" int quest_debug_topk_hist_clocks(unsigned long long* host_out, uint32
 template <int G>
 static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
                             uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream,
-                            const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, const Handoff& ho = Handoff{}) {
+                            const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, const Handoff& ho = Handoff{},
+                            const HistOut& xo = HistOut{}) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(num_heads, batch);
   cfg.blockDim = dim3(kHistThreads);
@@ -404,7 +410,7 @@ static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* i
   attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba, ho);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba, ho, xo);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -413,14 +419,14 @@ static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* i
 bool topk_hist_covers(uint32_t max_len) { return max_len <= 32u * kHistThreads && debug_option(QUEST_DBG_TOPK_NO_HIST) == 0; }
 int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
                    uint32_t num_heads, uint32_t max_len, uint32_t k, const BatchArgs& ba, uint32_t batch, cudaStream_t s,
-                   const Handoff& ho) {
-  if (max_len <= 4u * kHistThreads) return launch_topk_hist<1>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
-  if (max_len <= 8u * kHistThreads) return launch_topk_hist<2>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
-  if (max_len <= 16u * kHistThreads) return launch_topk_hist<4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
+                   const Handoff& ho, const HistOut& xo) {
+  if (max_len <= 4u * kHistThreads) return launch_topk_hist<1>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
+  if (max_len <= 8u * kHistThreads) return launch_topk_hist<2>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
+  if (max_len <= 16u * kHistThreads) return launch_topk_hist<4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
   // in-between bounds: a batch just past 8192 pages (BASELINE configs[3]: 8193) pays for the keys per thread it is compiled for
-  if (max_len <= 20u * kHistThreads) return launch_topk_hist<5>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
-  if (max_len <= 24u * kHistThreads) return launch_topk_hist<6>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
-  if (max_len <= 32u * kHistThreads) return launch_topk_hist<8>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho);
+  if (max_len <= 20u * kHistThreads) return launch_topk_hist<5>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
+  if (max_len <= 24u * kHistThreads) return launch_topk_hist<6>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
+  if (max_len <= 32u * kHistThreads) return launch_topk_hist<8>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
   return QUEST_ERR_UNSUPPORTED;
 }
 
@@ -499,7 +505,7 @@ extern "C" int quest_debug_topk_hist(const void* scores, const int32_t* in_idx, 
   if (!scores || !out_idx || !hist || !num_heads || k > len || !quest::topk_hist_covers(len)) return QUEST_ERR_BAD_ARG;
   cudaStream_t s = (cudaStream_t)stream;
   quest::hist_build_kernel<<<dim3(8, num_heads), 256, 0, s>>>((const __half*)scores, (uint32_t*)hist, len);
-  return quest::topk_from_hist(scores, (uint32_t*)hist, in_idx, in_idx_row_stride, out_idx, num_heads, len, k, quest::BatchArgs{}, 1, s, quest::Handoff{});
+  return quest::topk_from_hist(scores, (uint32_t*)hist, in_idx, in_idx_row_stride, out_idx, num_heads, len, k, quest::BatchArgs{}, 1, s, quest::Handoff{}, quest::HistOut{});
 }
 
 extern "C" uint32_t quest_topk_max_len(void) { return quest::kTopkMaxLen; }

@@ -125,11 +125,12 @@ class SeqShardedDecode:
 
     def __init__(self, ic, num_qo_heads: int, world: int, rank: int, page_budget: int,
                  group: Optional[dist.ProcessGroup] = None, exchange: str = "nccl",
-                 peer_buffers: Optional[Sequence[torch.Tensor]] = None):
+                 peer_buffers: Optional[Sequence[torch.Tensor]] = None, fused_candidates: bool = True):
         """exchange: "nccl" (all_gather_into_tensor) or "peer" (quest_peer_allgather: one kernel per exchange that
         stores into every rank's symmetric-memory staging area over NVLink and waits on flag words).
         peer_buffers: for a single process that plays all ranks on one device (tests): the ranks' exchange areas as
-        uint8 tensors of peer_area_bytes() each, in rank order; by default the areas are torch symmetric memory."""
+        uint8 tensors of peer_area_bytes() each, in rank order; by default the areas are torch symmetric memory.
+        fused_candidates: phase 1 as one quest_estimate_select call (False: append + estimate + top-k as separate operators)."""
         from quest_b200 import _kernels
         self._K = _kernels
         self.lib = _kernels.load_library()
@@ -139,6 +140,8 @@ class SeqShardedDecode:
         self.has_last = self.r == self.R - 1
         self.dev = ic.device
         self._key = None
+        self.fused_candidates = bool(fused_candidates)
+        self._ids_in_payload = False
         sms = torch.cuda.get_device_properties(self.dev).multi_processor_count
         ppc, nch = ctypes.c_uint32(), ctypes.c_uint32()
         _kernels._rc(self.lib.quest_decode_plan(self.k, self.Hq, self.Hkv, self.D, self.P, sms, ctypes.byref(ppc),
@@ -254,6 +257,25 @@ class SeqShardedDecode:
         rank's exchange-1 message, fp16 [Hq, c]."""
         ic, lib, rc = self.ic, self.lib, self._K._rc
         kv, meta = ic.kv_cache.buf_layer(layer), ic.metadata_cache.buf_layer(layer)
+        self._ids_in_payload = False
+        if self.c_loc and self.fused_candidates:
+            # one call, two launches: estimate (carrying the append on the last rank) publishing bin totals, then the selection
+            # from them with the scores written into this rank's exchange-1 message and the ids straight into its columns of the
+            # global payload row (quest_estimate_select) -- instead of append + estimate + top-k + two copies
+            app = self.has_last and k_new is not None
+            code = lib.quest_estimate_select(
+                q.data_ptr(), k_new.data_ptr() if app else None, v_new.data_ptr() if app else None, kv.data_ptr(),
+                ic.kv_indices_with_last.data_ptr(), ic.kv_indices_with_last.numel(), ic.kv_cache.last_page_len, meta.data_ptr(),
+                ic.metadata_indices.data_ptr(), ic.metadata_indices.numel(), ic.metadata_cache.last_page_len, self.n_local,
+                self.scores.data_ptr(), self.cand_s.data_ptr(), self.c_max, self.pay[:, self.r].data_ptr(), self.R * self.c_max,
+                self.c_loc, self.Hq, self.Hkv, self.D, self.P, self._K.EST_META_ORDERED | self._K.EST_META_STABLE,
+                self.ws.data_ptr(), self.ws.numel(), self._st())
+            if code == 0:
+                self._ids_in_payload = True
+                return self.cand_s
+            if code != -2:  # -2: a shape / length the bin-total path does not take (nothing was launched): separate ops below
+                rc(code, "estimate + select")
+            self.fused_candidates = False
         if self.has_last and k_new is not None:
             rc(lib.quest_append_decode(k_new.data_ptr(), v_new.data_ptr(), kv.data_ptr(), ic.kv_indices_with_last.data_ptr(),
                                        ic.kv_indices_with_last.numel(), ic.kv_cache.last_page_len, meta.data_ptr(),
@@ -276,7 +298,7 @@ class SeqShardedDecode:
             return self.sel[:, :0]
         if gathered is not None:  # None: all_s already holds [Hq, R, c] (peer exchange unpacks straight into it)
             self.all_s.copy_(gathered.permute(1, 0, 2))
-        if self.c_loc:
+        if self.c_loc and not self._ids_in_payload:
             self.pay[:, self.r, :self.c_loc].copy_(self.cand_p)
         n = self.R * self.c_max
         self._K._rc(self.lib.quest_topk(self.all_s.data_ptr(), self.pay.data_ptr(), n, None, self.sel.data_ptr(), self.Hq,

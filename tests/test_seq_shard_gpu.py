@@ -22,7 +22,7 @@ DEV = "cuda:0"
 ATTN_ATOL = 2e-3  # north_star: fp16 attention output max abs error
 
 
-def _run_case(seed, kv_len, Hq, Hkv, D, P, budget, world, steps=3, ties=False, exchange="emulated"):
+def _run_case(seed, kv_len, Hq, Hkv, D, P, budget, world, steps=3, ties=False, exchange="emulated", fused=True):
     dev = torch.device(DEV)
     k, v, dec = sc.seeded_case(seed, kv_len, Hq, Hkv, D, steps)
     if ties:  # repeat a block of keys: equal metadata -> equal scores across shards, the tie rule decides
@@ -38,10 +38,10 @@ def _run_case(seed, kv_len, Hq, Hkv, D, P, budget, world, steps=3, ties=False, e
         probe = par.SeqShardedDecode(ics[0], Hq, 1, 0, budget)
         nbytes = par.SeqShardedDecode._peer_layout(probe.lib, Hq, D, budget - 1, world)[2]
         areas = [torch.zeros(nbytes, dtype=torch.uint8, device=dev) for _ in range(world)]
-        shards = [par.SeqShardedDecode(ics[r], Hq, world, r, budget, exchange="peer", peer_buffers=areas) for r in range(world)]
+        shards = [par.SeqShardedDecode(ics[r], Hq, world, r, budget, exchange="peer", peer_buffers=areas, fused_candidates=fused) for r in range(world)]
         streams = [torch.cuda.Stream() for _ in range(world)]
     else:
-        shards = [par.SeqShardedDecode(ics[r], Hq, world, r, budget) for r in range(world)]
+        shards = [par.SeqShardedDecode(ics[r], Hq, world, r, budget, fused_candidates=fused) for r in range(world)]
     for q, k1, v1 in dec:
         q, k1, v1 = q.to(dev), k1.to(dev), v1.to(dev)
         # single-GPU truth
@@ -238,3 +238,11 @@ def test_two_rank_nccl():
     r = subprocess.run(cmd, cwd=root, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "seqshard nccl ok" in r.stdout
+
+
+@pytest.mark.parametrize("exchange", ["emulated", "peer"])
+def test_separate_operator_candidates_path(exchange):
+    """fused_candidates=False: phase 1 as append + estimate + top-k + copies (the path shapes outside the bin-total top-k take);
+    the default (one quest_estimate_select call) is what every other test here runs."""
+    _run_case(5, 3000, 32, 32, 128, 16, 24, 3, exchange=exchange, fused=False)
+    _run_case(6, 2049, 32, 8, 128, 16, 16, 2, ties=True, exchange=exchange, fused=False)

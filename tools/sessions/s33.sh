@@ -1,0 +1,8 @@
+#!/usr/bin/env bash
+# sequence-sharded step with the fused candidates phase (quest_estimate_select): single-GPU shard emulation tests, then configs[4]
+set -u
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_seq_shard_gpu.py -m gpu -x -q 2>&1 | tail -3
+for ex in peer nccl; do
+  timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 1 --master-addr 127.0.0.1 --master-port 29536 tools/bench_configs.py --config 5 --exchange $ex --steps 20 --warmup 5 2>&1 | grep -v Warning | tail -1 | python -c 'import json,sys; d=json.loads(sys.stdin.read()); print(d.get("parallelism","")[:40], {k: round(v,2) for k,v in d.items() if k.endswith("us_per_layer")})'
+done
