@@ -107,26 +107,44 @@ def _check(cond, msg):
         raise RuntimeError(msg)
 
 
+# The checks below run on every operator call of the op-by-op path (16 tensors per layer step): messages are only built on
+# failure (an f-string argument would be formatted on every call; tools/four_ops_profile.py).
 def _check_input(x, name):
-    _check(isinstance(x, torch.Tensor), f"{name} must be a tensor")
-    _check(x.is_cuda, f"{name} must be a CUDA tensor")
-    _check(x.is_contiguous(), f"{name} must be contiguous")
+    if not isinstance(x, torch.Tensor):
+        raise RuntimeError(f"{name} must be a tensor")
+    if not x.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if not x.is_contiguous():
+        raise RuntimeError(f"{name} must be contiguous")
 
 
 def _check_rows(x, name):
     """2-D index tensor: contiguous, or one row broadcast to all heads (stride 0 view)."""
-    _check(isinstance(x, torch.Tensor) and x.is_cuda, f"{name} must be a CUDA tensor")
-    _check(x.dim() == 2, f"{name} must be a 2D tensor")
-    _check(x.size(1) <= 1 or x.stride(1) == 1, f"{name} must be contiguous")
-    _check(x.size(0) <= 1 or x.size(1) == 0 or x.stride(0) in (0, x.size(1)), f"{name} must be contiguous")
-    return 0 if (x.size(0) > 1 and x.stride(0) == 0) else x.size(1)
+    if not (isinstance(x, torch.Tensor) and x.is_cuda):
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if x.dim() != 2:
+        raise RuntimeError(f"{name} must be a 2D tensor")
+    rows, cols = x.shape
+    s0, s1 = x.stride()
+    if not ((cols <= 1 or s1 == 1) and (rows <= 1 or cols == 0 or s0 in (0, cols))):
+        raise RuntimeError(f"{name} must be contiguous")
+    return 0 if (rows > 1 and s0 == 0) else cols
 
 
 def _check_half(x, op):
-    _check(x.dtype == torch.float16, f"{op} failed to dispatch with dtype {x.dtype}")
+    if x.dtype != torch.float16:
+        raise RuntimeError(f"{op} failed to dispatch with dtype {x.dtype}")
+
+
+# torch.cuda.current_stream() builds a Stream object behind several device-index lookups (about 5 us a call, four calls per
+# layer on the op-by-op path); the raw handle of the current device's current stream is one C call.
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_cur_device = getattr(torch._C, "_cuda_getDevice", None)
 
 
 def _stream():
+    if _raw_stream is not None and _cur_device is not None:
+        return _raw_stream(_cur_device())
     return torch.cuda.current_stream().cuda_stream
 
 
@@ -150,8 +168,9 @@ _NHD = 0
 
 
 def _check_layout(layout, op):
-    _check(int(layout) == _NHD, f"{op}: only the NHD layout is built (the reference controller always uses NHD, "
-                                "quest/utils/controller.py:38)")
+    if int(layout) != _NHD:
+        raise RuntimeError(f"{op}: only the NHD layout is built (the reference controller always uses NHD, "
+                           "quest/utils/controller.py:38)")
 
 
 def apply_rope_in_place(q, k, past_kv_len, rope_scale, rope_theta):
@@ -184,7 +203,8 @@ def topk_filtering(estimated_value, estimated_indices, d_out, indices_out, buf, 
     H, n = estimated_value.shape
     _check(estimated_indices.size(1) == n, "CHECK_EQ(num_pages, estimated_indices.size(1)) failed")
     _check(estimated_indices.size(0) == H, "CHECK_EQ(num_heads, estimated_indices.size(0)) failed")
-    _check(n >= page_budget, f"CHECK_GE(num_pages, page_budget) failed. {n} vs {page_budget}")
+    if n < page_budget:
+        raise RuntimeError(f"CHECK_GE(num_pages, page_budget) failed. {n} vs {page_budget}")
     _check(estimated_indices.dtype == torch.int32, "CHECK_EQ(estimated_indices.scalar_type(), torch::kInt32) failed")
     _check(d_out.size(1) == page_budget, "CHECK_EQ(page_budget, d_out.size(1)) failed")
     _check(indices_out.size(1) == page_budget, "CHECK_EQ(page_budget, indices_out.size(1)) failed")
@@ -196,9 +216,12 @@ def topk_filtering(estimated_value, estimated_indices, d_out, indices_out, buf, 
 
 
 def _pool_dims(data, name):
-    _check(data.dim() == 5, f"{name} must be a 5D tensor")
-    _check(data.size(1) == 2, f"CHECK_EQ({name}.size(1), 2) failed")
-    return data.size(2), data.size(3), data.size(4)  # page_size, heads, head_dim (NHD)
+    if data.dim() != 5:
+        raise RuntimeError(f"{name} must be a 5D tensor")
+    _, two, P, H, D = data.shape
+    if two != 2:
+        raise RuntimeError(f"CHECK_EQ({name}.size(1), 2) failed")
+    return P, H, D  # page_size, heads, head_dim (NHD)
 
 
 EST_META_STABLE, EST_META_ORDERED = 1, 2  # include/quest_b200.h QUEST_EST_*
@@ -221,7 +244,8 @@ def estimate_attn_score(q, o, metadata_data, metadata_indices, metadata_indptr, 
     _check(Hq % Hkv == 0, "num_qo_heads must be a multiple of num_kv_heads")
     _check(o.dim() == 2 and o.size(0) == Hq, "o must be [num_heads, num_pages - 1]")
     n_entries = (metadata_indices.size(0) - 1) * P + int(metadata_last_page_len) - 1
-    _check(o.size(1) == n_entries, f"o.size(1) must equal the number of scored pages {n_entries}")
+    if o.size(1) != n_entries:
+        raise RuntimeError(f"o.size(1) must equal the number of scored pages {n_entries}")
     _check_half(q, "Estimate_attn_score")
     _rc(load_library().quest_estimate(q.data_ptr(), o.data_ptr(), o.size(1), metadata_data.data_ptr(),
                                       metadata_indices.data_ptr(), Hq, Hkv, D, P, int(flags), _stream()), "estimate_attn_score")
@@ -237,11 +261,14 @@ def _append_checks(k, v, kv_data, kv_indices, kv_indptr, metadata_data, metadata
     _check(k.dim() == 3, "k must be a 3D tensor"), _check(v.dim() == 3, "v must be a 3D tensor")
     for t, n in ((kv_indices, "kv_indices"), (metadata_indices, "metadata_indices"), (kv_indptr, "kv_indptr"),
                  (metadata_indptr, "metadata_indptr")):
-        _check(t.dtype == torch.int32, f"CHECK_EQ({n}.scalar_type(), torch::kInt32) failed")
+        if not (t.dtype == torch.int32):
+            raise RuntimeError(f"CHECK_EQ({n}.scalar_type(), torch::kInt32) failed")
     P, H, D = _pool_dims(kv_data, "kv_data")
     _check(_pool_dims(metadata_data, "metadata_data") == (P, H, D), "metadata_data must share page_size/heads/dim with kv_data")
-    _check(k.size(1) == H, f"CHECK_EQ(kv_data.size(3), num_heads) failed. {H} vs {k.size(1)}")
-    _check(k.size(2) == D, f"CHECK_EQ(kv_data.size(4), head_dim) failed. {D} vs {k.size(2)}")
+    if not (k.size(1) == H):
+        raise RuntimeError(f"CHECK_EQ(kv_data.size(3), num_heads) failed. {H} vs {k.size(1)}")
+    if not (k.size(2) == D):
+        raise RuntimeError(f"CHECK_EQ(kv_data.size(4), head_dim) failed. {D} vs {k.size(2)}")
     _check(v.shape == k.shape, "CHECK_EQ(seq_len, v.size(0)) failed")
     _check_half(k, op)
     return P, H, D
@@ -252,7 +279,8 @@ def append_kv_cache_decode(k, v, kv_data, kv_indices, kv_indptr, kv_last_page_le
     """reference quest/ops/csrc/page.cu:6-99"""
     P, H, D = _append_checks(k, v, kv_data, kv_indices, kv_indptr, metadata_data, metadata_indices, metadata_indptr,
                              layout, "Append_kv_cache_decode")
-    _check(k.size(0) == 1, f"CHECK_EQ(k.size(0), 1) failed. {k.size(0)} vs 1")
+    if not (k.size(0) == 1):
+        raise RuntimeError(f"CHECK_EQ(k.size(0), 1) failed. {k.size(0)} vs 1")
     _rc(load_library().quest_append_decode(k.data_ptr(), v.data_ptr(), kv_data.data_ptr(), kv_indices.data_ptr(),
                                            kv_indices.size(0), int(kv_last_page_len), metadata_data.data_ptr(),
                                            metadata_indices.data_ptr(), metadata_indices.size(0),
@@ -264,7 +292,8 @@ def append_kv_cache_prefill(k, v, kv_data, kv_indices, kv_indptr, kv_last_page_l
     """reference quest/ops/csrc/page.cu:101-210"""
     P, H, D = _append_checks(k, v, kv_data, kv_indices, kv_indptr, metadata_data, metadata_indices, metadata_indptr,
                              layout, "Append_kv_cache_prefill")
-    _check(k.size(0) >= 2, f"CHECK_GE(k.size(0), 2) failed. {k.size(0)} vs 2")
+    if not (k.size(0) >= 2):
+        raise RuntimeError(f"CHECK_GE(k.size(0), 2) failed. {k.size(0)} vs 2")
     _rc(load_library().quest_append_prefill(k.data_ptr(), v.data_ptr(), k.size(0), kv_data.data_ptr(),
                                             kv_indices.data_ptr(), kv_indices.size(0), int(kv_last_page_len),
                                             metadata_data.data_ptr(), metadata_indices.data_ptr(),

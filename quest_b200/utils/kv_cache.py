@@ -89,8 +89,12 @@ class KvCache:
         return self._indicies
 
     def buf_layer(self, layer_idx: int):
-        assert layer_idx < self.pool.num_layers
-        return self._pool.buf[layer_idx]
+        # one view per layer, made once: indexing the pool tensor builds a new view object on every call, four times per
+        # layer and token on the op-by-op path (reference kv_cache.py:112-114 indexes every time)
+        views = self.__dict__.get("_layer_views")
+        if views is None:
+            views = self._layer_views = [self._pool.buf[i] for i in range(self._pool.num_layers)]
+        return views[layer_idx]
 
     def append_seq(self, seq_len: int) -> int:
         """Reserve space for tokens and return number of new pages"""
