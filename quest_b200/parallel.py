@@ -250,7 +250,7 @@ class SeqShardedDecode:
         self.pay = torch.full((Hq, R, c), -1, dtype=torch.int32, device=self.dev)
 
     def _st(self):
-        return torch.cuda.current_stream().cuda_stream
+        return self._K._stream()
 
     def candidates(self, q: torch.Tensor, k_new: Optional[torch.Tensor], v_new: Optional[torch.Tensor], layer: int):
         """Phase 1.  q: [1, Hq, D] fp16; k_new, v_new: [1, Hkv, D] (used on the last rank only).  Returns this

@@ -253,7 +253,7 @@ def decode_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iContro
     _nvtx.range_push("topk")
     _nvtx.range_push("approx_attn")
     rc = st.fn(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), st.kv_ptrs[layer_idx], *st.mid,
-               *st.meta_ptrs[layer_idx], *st.tail, torch.cuda.current_stream().cuda_stream)
+               *st.meta_ptrs[layer_idx], *st.tail, _kernels._stream())
     _nvtx.range_pop(), _nvtx.range_pop(), _nvtx.range_pop(), _nvtx.range_pop()
     if rc:
         _kernels._rc(rc, "decode_layer_step")

@@ -86,7 +86,7 @@ class BatchDecodeStep:
         """apply_rope_in_place for the new token of every sequence at its own position: q [B, Hq, D], k [B, Hkv, D]."""
         _kernels._rc(self.lib.quest_rope_decode_batch(q.data_ptr(), k.data_ptr(), self.d_desc.data_ptr(), self.B, self.Hq,
                                                       self.Hkv, self.D, float(rope_scale), float(rope_theta),
-                                                      torch.cuda.current_stream().cuda_stream), "rope_decode_batch")
+                                                      _kernels._stream()), "rope_decode_batch")
 
     def layer_step(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, layer: int,
                    out: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -100,7 +100,7 @@ class BatchDecodeStep:
             q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), self.d_desc.data_ptr(), self.B,
             layer * self.layer_stride_kv, layer * self.layer_stride_meta, self.max_kv_pages, self.scores.data_ptr(),
             self.score_stride, self.topk.data_ptr(), self.k, self.Hq, self.Hkv, self.D, self.P, self.ppc, self.ws.data_ptr(),
-            self.ws_seq, torch.cuda.current_stream().cuda_stream)
+            self.ws_seq, _kernels._stream())
         if rc:
             _kernels._rc(rc, "decode_layer_step_batch")
         return o
