@@ -168,11 +168,17 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
   uint32_t pg_ld = warp, i_ld = 0, okm = 0;
   const uint8_t* ptr = kvb;
   uint32_t nv_ld = 0;  // valid tokens of the page under the cursor
+  // A list entry with nothing to read -- id < 0: a selected page another sequence shard holds; the forced last page on a shard
+  // that does not hold it (last_page_len 0) -- is stepped over, not walked with its loads switched off: on one of 8 shards 7 of
+  // 8 entries are such pages, and walking them cost the softmax arithmetic of a full list (18.6 -> 12.6 us per layer there;
+  // squeezing the chunk's list in shared memory first, so that its warps share the entries evenly, measured no better: 14.4 us --
+  // what is left is the spread of the entries with rows over the chunks, profiles/r02_b_experiments.md).
+  auto has_rows = [&](uint32_t pg) { return s_pages[pg] >= 0 && (pg < n_sel_local || last_page_len > 0); };
   auto open_page = [&]() {
+    while (pg_ld < npg && !has_rows(pg_ld)) pg_ld += kWarps;
     if (pg_ld < npg) {
-      const int32_t pid = s_pages[pg_ld];  // < 0: a selected page another sequence shard holds -> no rows
-      ptr = kvb + (uint64_t)(uint32_t)pid * page_bytes;
-      nv_ld = pid < 0 ? 0u : (pg_ld < n_sel_local ? P : last_page_len);
+      ptr = kvb + (uint64_t)(uint32_t)s_pages[pg_ld] * page_bytes;
+      nv_ld = pg_ld < n_sel_local ? P : last_page_len;
     } else {
       nv_ld = 0;
     }
@@ -219,7 +225,8 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
     }
   };
   // token-loads this warp must consume: its pages x n_tl (warp-uniform; the shuffles use the full mask)
-  const uint32_t my_pages = npg > warp ? (npg - warp + kWarps - 1) / kWarps : 0;
+  uint32_t my_pages = 0;
+  for (uint32_t pg = warp; pg < npg; pg += kWarps) my_pages += has_rows(pg) ? 1u : 0u;
   const uint32_t my_tl = my_pages * n_tl;
 #pragma unroll
   for (int st = 0; st < kRing; ++st) issue(st);
