@@ -360,7 +360,8 @@ void quest_device_error_clear(void);
 #define QUEST_DBG_TOPK_NO_HIST 6     /* 1: layer step selects with the stand-alone top-k kernels (no bin totals) */
 #define QUEST_DBG_EST_PER_Q 7        /* 1: GQA groups of 2 / 4 use one lane row per q head (the round-1 layout)  */
 #define QUEST_DBG_NO_HANDOFF 8       /* 1: layer step without the page-id hand-over (decode waits for the top-k launch) */
-#define QUEST_DBG_COUNT 9
+#define QUEST_DBG_NO_ROW_COMPACT 9   /* 1: quest_decode_run_partial walks the sparse list chunk by chunk (no row compaction) */
+#define QUEST_DBG_COUNT 10
 int quest_debug_set_option(int option, int value);
 
 /* Counters for bench/tests: number of kernels this library has launched since load / last reset. */

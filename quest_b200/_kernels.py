@@ -83,7 +83,7 @@ def load_library():
 
 
 # include/quest_b200.h QUEST_DBG_*: explicit test / A-B switches (the library never reads the environment)
-DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC, DBG_TOPK_NO_HIST, DBG_EST_PER_Q, DBG_NO_HANDOFF = range(9)
+DBG_PDL_OFF, DBG_EST_ROWS, DBG_PREFILL_IMPL, DBG_PREFILL_P_SMEM, DBG_TOPK_NO_CLUSTER, DBG_TOPK_GENERIC, DBG_TOPK_NO_HIST, DBG_EST_PER_Q, DBG_NO_HANDOFF, DBG_NO_ROW_COMPACT = range(10)
 DEVERR_PREFILL, DEVERR_PEER, DEVERR_STEP = 1, 2, 4
 
 

@@ -50,7 +50,11 @@ __device__ __forceinline__ uint32_t div_p(uint32_t t, uint32_t p_magic) { return
 // 2 warp-wide K loads + 2 V loads (a lane group of D/8 lanes owns one 16-byte-per-lane token row), with
 // the next item's loads issued before the current item is consumed: 8 independent 128-bit loads per lane
 // stay in flight, ~128 KB per SM at 8 CTAs/SM, and the softmax arithmetic hides under them.
-template <int D, int kThreads, int kMinBlocks>
+// kRowCompact (the sequence-sharded step's attend phase, where most list entries are -1 = pages another shard holds): every CTA of a
+// head scans the head's WHOLE list, counts the entries with rows and takes an equal share of them -- entry j of the squeezed
+// list goes to chunk j / ceil(n / chunks) -- instead of the entries at its positions in the sparse list, whose number of
+// rows varies from chunk to chunk (Poisson around total / shards per chunk) with the slowest chunk setting the head's time.
+template <int D, int kThreads, int kMinBlocks, bool kRowCompact = false>
 __global__ void __launch_bounds__(kThreads, kMinBlocks)
 decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __restrict__ lse_,
               const __half* __restrict__ kv_, const int32_t* __restrict__ indices_, uint32_t idx_stride,
@@ -99,7 +103,51 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
   D_STAMP(0);
   const int32_t* idx_row = indices + (size_t)h * idx_stride;
   uint32_t qh[4];  // this lane's 8 q dims as packed halves: q.k runs on mixed-precision FMAs (fp16 x fp16 + fp32, exact products)
-  if (ho_epoch == nullptr) {
+  uint32_t n_rows = npg, last_pos = 0xffffffffu;  // kRowCompact: this chunk's share of the squeezed list, and where the last page sits in it
+  if (kRowCompact) {
+    __shared__ uint32_t s_scan[kWarps + 1];
+    pdl_wait();
+    D_STAMP(1);
+    const uint32_t per = (total_pages + kThreads - 1) / kThreads;  // consecutive entries per thread
+    const uint32_t i0 = min(tid * per, total_pages), i1 = min(i0 + per, total_pages);
+    auto entry = [&](uint32_t i) -> int32_t {
+      return i < n_sel ? (int32_t)ld_ordered32(idx_row + i) : (last_page_len ? (int32_t)last_page_idx : -1);
+    };
+    uint32_t cnt = 0;
+    for (uint32_t i = i0; i < i1; ++i) cnt += entry(i) >= 0 ? 1u : 0u;
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const uint32_t a = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= (uint32_t)off) incl += a;
+    }
+    if (lane == 31) s_scan[warp] = incl;
+    if (tid == 0) s_scan[kWarps] = 0xffffffffu;
+    __syncthreads();
+    uint32_t ci = incl - cnt, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      ci += (uint32_t)w < warp ? s_scan[w] : 0u;
+      tot += s_scan[w];
+    }
+    const uint32_t share = (tot + nchunks - 1) / nchunks;
+    const uint32_t lo = min(chunk * share, tot), hi = min(lo + share, tot);
+    for (uint32_t i = i0; i < i1; ++i) {  // second pass: the list is in L1 / L2 now
+      const int32_t pid = entry(i);
+      if (pid >= 0) {
+        if (ci >= lo && ci < hi) {
+          s_pages[ci - lo] = pid;
+          if (i == n_sel) s_scan[kWarps] = ci - lo;  // the forced last page: last_page_len tokens
+        }
+        ++ci;
+      }
+    }
+    const uint4 raw = ld_ordered16(q + (size_t)h * D + lir * 8);
+    qh[0] = raw.x, qh[1] = raw.y, qh[2] = raw.z, qh[3] = raw.w;
+    __syncthreads();
+    n_rows = hi - lo;
+    last_pos = s_scan[kWarps];
+  } else if (ho_epoch == nullptr) {
     pdl_wait();  // q, the page ids (top-k kernel) and the last page's new row (append) come from earlier kernels
     D_STAMP(1);
     for (uint32_t i = tid; i < npg; i += kThreads)
@@ -133,7 +181,7 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
       s_pages[i] = pid;
     }
   }
-  if (ho_epoch == nullptr) {
+  if (!kRowCompact && ho_epoch == nullptr) {
     const uint4 raw = ld_ordered16(q + (size_t)h * D + lir * 8);
     qh[0] = raw.x, qh[1] = raw.y, qh[2] = raw.z, qh[3] = raw.w;
   }
@@ -173,12 +221,13 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
   // 8 entries are such pages, and walking them cost the softmax arithmetic of a full list (18.6 -> 12.6 us per layer there;
   // squeezing the chunk's list in shared memory first, so that its warps share the entries evenly, measured no better: 14.4 us --
   // what is left is the spread of the entries with rows over the chunks, profiles/r02_b_experiments.md).
-  auto has_rows = [&](uint32_t pg) { return s_pages[pg] >= 0 && (pg < n_sel_local || last_page_len > 0); };
+  const uint32_t n_list = kRowCompact ? n_rows : npg;  // entries of s_pages this CTA walks
+  auto has_rows = [&](uint32_t pg) { return kRowCompact || (s_pages[pg] >= 0 && (pg < n_sel_local || last_page_len > 0)); };
   auto open_page = [&]() {
-    while (pg_ld < npg && !has_rows(pg_ld)) pg_ld += kWarps;
-    if (pg_ld < npg) {
+    while (pg_ld < n_list && !has_rows(pg_ld)) pg_ld += kWarps;
+    if (pg_ld < n_list) {
       ptr = kvb + (uint64_t)(uint32_t)s_pages[pg_ld] * page_bytes;
-      nv_ld = pg_ld < n_sel_local ? P : last_page_len;
+      nv_ld = kRowCompact ? (pg_ld == last_pos ? last_page_len : P) : (pg_ld < n_sel_local ? P : last_page_len);
     } else {
       nv_ld = 0;
     }
@@ -226,7 +275,7 @@ decode_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, float* __r
   };
   // token-loads this warp must consume: its pages x n_tl (warp-uniform; the shuffles use the full mask)
   uint32_t my_pages = 0;
-  for (uint32_t pg = warp; pg < npg; pg += kWarps) my_pages += has_rows(pg) ? 1u : 0u;
+  for (uint32_t pg = warp; pg < n_list; pg += kWarps) my_pages += has_rows(pg) ? 1u : 0u;
   const uint32_t my_tl = my_pages * n_tl;
 #pragma unroll
   for (int st = 0; st < kRing; ++st) issue(st);
@@ -397,7 +446,9 @@ static int launch_decode(const void* q, void* o, float* lse, const void* kv, con
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const float sm_scale_log2 = kLog2e / sqrtf((float)D);
-  auto kern = decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS>;
+  // partial (fp32) output = a sequence shard's attend phase: its list is mostly -1 entries
+  const bool row_compact = o32 != nullptr && ba.descs == nullptr && ho_epoch == nullptr && nchunks > 1 && debug_option(QUEST_DBG_NO_ROW_COMPACT) == 0;
+  auto kern = row_compact ? decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS, true> : decode_kernel<D, kDecThreads, QUEST_DEC_MINBLOCKS, false>;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, lse,
                                      (const __half*)kv, indices, idx_stride, n_sel, last_page_idx, last_page_len, Hkv,
                                      Hq / Hkv, P, div_magic(P), ppc, sm_scale_log2, (uint8_t*)ws, ba, o32, ho_epoch,

@@ -245,4 +245,6 @@ def test_separate_operator_candidates_path(exchange):
     """fused_candidates=False: phase 1 as append + estimate + top-k + copies (the path shapes outside the bin-total top-k take);
     the default (one quest_estimate_select call) is what every other test here runs."""
     _run_case(5, 3000, 32, 32, 128, 16, 24, 3, exchange=exchange, fused=False)
-    _run_case(6, 2049, 32, 8, 128, 16, 16, 2, ties=True, exchange=exchange, fused=False)
+    import quest_b200._kernels as K
+    with K.debug_option(K.DBG_NO_ROW_COMPACT, 1):  # ... and the attend phase walking the sparse list chunk by chunk
+        _run_case(6, 2049, 32, 8, 128, 16, 16, 2, ties=True, exchange=exchange, fused=False)
