@@ -231,6 +231,12 @@ int quest_decode_layer_step_batch(const void* q, const void* k_new, const void* 
 int quest_rope_decode_batch(void* q, void* k, const QuestSeqDesc* descs, uint32_t batch, uint32_t num_qo_heads,
                             uint32_t num_kv_heads, uint32_t head_dim, float rope_scale, float rope_theta, void* stream);
 
+/* Device-side record updater: advances every record by one token (page / metadata-page roll-over, last-page lengths, RoPE
+ * position), so that a captured step whose first node this is replays over a run of tokens the host has reserved in advance
+ * (page ids already in the device tables) with no host work in between.  Replaces the per-token host rebuild of
+ * quest/utils/controller.py:72-129 for such runs. */
+int quest_seq_desc_advance(QuestSeqDesc* descs, uint32_t batch, uint32_t page_size, void* stream);
+
 /* ---- paged causal prefill ----------------------------------------------------------------------
  * Replaces prefill_with_paged_kv_cache (bsk_ops.h:78-86, batch_prefill.cu:27-117, prefill.cuh:674-1115).
  * q, o: [qo_len, num_qo_heads, head_dim]; the KV sequence is the num_kv_pages pages of kv_indices

@@ -40,6 +40,7 @@ SIGNATURES = {
     "quest_decode_layer_step_batch": (_c.c_int, [_vp, _vp, _vp, _vp, _vp, _u32, _sz, _sz, _u32, _vp, _sz, _i32p, _u32, _u32, _u32,
                                                  _u32, _u32, _u32, _vp, _sz, _vp]),
     "quest_rope_decode_batch": (_c.c_int, [_vp, _vp, _vp, _u32, _u32, _u32, _u32, _f32, _f32, _vp]),
+    "quest_seq_desc_advance": (_c.c_int, [_vp, _u32, _u32, _vp]),
     "quest_prefill": (_c.c_int, [_vp, _vp, _u32, _vp, _i32p, _u32, _u32, _c.c_int, _u32, _u32, _u32, _u32, _vp]),
     "quest_rope_append_prefill": (_c.c_int, [_vp, _vp, _vp, _u32, _vp, _i32p, _u32, _u32, _vp, _i32p, _u32, _u32, _u32, _u32, _u32,
                                              _f32, _f32, _u32, _vp]),

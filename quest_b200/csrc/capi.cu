@@ -308,3 +308,38 @@ extern "C" int quest_estimate_select(const void* q, const void* k_new, const voi
   return quest::topk_from_hist(scores, hist, kv_indices, 0, out_idx, num_qo_heads, len, k, quest::BatchArgs{}, 1, (cudaStream_t)stream,
                                quest::Handoff{}, xo);
 }
+
+// Device-side record updater for the descriptor-driven step: advances every sequence's record by one token -- a page fills, the
+// next one (whose id the host already put into the device page table when it reserved the tokens) becomes the last page, the
+// metadata entry / page counters follow, the RoPE position moves on.  With it as the first node of the captured step, a run of
+// pre-reserved tokens replays without any host work between tokens (quest_b200.utils.batch.BatchDecodeStep.run_ahead / advance).
+// The reference rebuilds these quantities on the host for every token (quest/utils/controller.py:72-129).
+namespace quest {
+__global__ void seq_desc_advance_kernel(SeqDesc* __restrict__ descs, uint32_t batch, uint32_t P) {
+  pdl_wait();
+  const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  SeqDesc d = descs[b];
+  if (d.kv_last_page_len >= P) {       // the new token opens a page ...
+    d.num_kv_pages += 1;
+    d.kv_last_page_len = 1;
+    if (d.meta_last_page_len >= P) {   // ... whose metadata entry opens a metadata page
+      d.num_meta_pages += 1;
+      d.meta_last_page_len = 1;
+    } else {
+      d.meta_last_page_len += 1;
+    }
+  } else {
+    d.kv_last_page_len += 1;
+  }
+  d.rope_pos += 1;
+  descs[b] = d;
+}
+}  // namespace quest
+
+extern "C" int quest_seq_desc_advance(QuestSeqDesc* descs, uint32_t batch, uint32_t page_size, void* stream) {
+  if (!descs || !batch || !page_size) return QUEST_ERR_BAD_ARG;
+  quest::seq_desc_advance_kernel<<<(batch + 63) / 64, 64, 0, (cudaStream_t)stream>>>(reinterpret_cast<quest::SeqDesc*>(descs), batch,
+                                                                                  page_size);
+  QUEST_RETURN_LAUNCH();
+}

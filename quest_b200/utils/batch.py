@@ -82,6 +82,23 @@ class BatchDecodeStep:
         """Pinned host records -> device records on the current stream (capturable)."""
         self.d_desc.copy_(self.h_desc, non_blocking=True)
 
+    def run_ahead(self, tokens: int):
+        """Reserve the next `tokens` tokens of every sequence NOW (pages allocated, device page tables filled) and leave the device
+        records at the last token that exists, so that a step whose first call is advance() can be replayed `tokens` times with
+        no host work in between: the records move on the device (quest_seq_desc_advance).  The controllers' host state is then
+        `tokens` ahead of the device until the run has been replayed in full."""
+        self.update_host()   # records of the state before the run (update_host reads the controllers as they are)
+        self.upload()
+        for ic in self.ics:
+            ic.prepare_metadata(int(tokens))
+            ic.sync_tables()
+        if not self.fits():
+            raise RuntimeError("the run outgrows max_kv_pages; build a new BatchDecodeStep")
+
+    def advance(self):
+        """One token further on the device (capturable): call it first in the step of a run_ahead() run."""
+        _kernels._rc(self.lib.quest_seq_desc_advance(self.d_desc.data_ptr(), self.B, self.P, _kernels._stream()), "seq_desc_advance")
+
     def rope(self, q: torch.Tensor, k: torch.Tensor, rope_scale: float = 1.0, rope_theta: float = 1e4):
         """apply_rope_in_place for the new token of every sequence at its own position: q [B, Hq, D], k [B, Hkv, D]."""
         _kernels._rc(self.lib.quest_rope_decode_batch(q.data_ptr(), k.data_ptr(), self.d_desc.data_ptr(), self.B, self.Hq,

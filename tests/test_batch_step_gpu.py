@@ -176,3 +176,61 @@ def test_one_graph_replayed_across_tokens_and_page_boundaries():
         graph.replay()
         _check_token(step, ics_a, ics_b, out, L, want_o, want_sel, want_sc, topks, scs)
     assert len(ics_b[0].metadata_cache.indicies) == 17  # sequence 0 crossed 4096 tokens = 256 pages = 16 metadata pages
+
+
+def test_run_ahead_graph_with_device_side_record_updater():
+    """40 tokens reserved in advance (run_ahead), then ONE captured graph -- advance() (quest_seq_desc_advance), RoPE, the layer
+    steps -- replayed 40 times with no host work on the records: outputs and selected pages of every token match the
+    eager per-sequence path, and once the run is over the pools do too."""
+    lens, Hq, Hkv, D, P, budget, L, T, rope_scale = (4090, 1000, 2500), 32, 32, 128, 16, 32, 2, 40, 8.0
+    ics_a, ics_b = _twin_controllers(lens, L, Hq, Hkv, D, P, budget, T, seed=3)
+    B = len(lens)
+    step = BatchDecodeStep(ics_b, max_kv_pages=max(lens) // P + T // P + 4)
+    q = torch.zeros(B, L, Hq, D, dtype=torch.float16, device=DEV)
+    k = torch.zeros(B, L, Hkv, D, dtype=torch.float16, device=DEV)
+    v = torch.zeros(B, L, Hkv, D, dtype=torch.float16, device=DEV)
+    qr, kr = torch.empty_like(q), torch.empty_like(k)
+    out = torch.empty(B, L, Hq, D, dtype=torch.float16, device=DEV)
+    topks = [torch.empty_like(step.topk) for _ in range(L)]
+
+    def body():
+        step.advance()
+        qr.copy_(q), kr.copy_(k)
+        for l in range(L):
+            ql, kl = qr[:, l].contiguous(), kr[:, l].contiguous()
+            step.rope(ql, kl, rope_scale=rope_scale)
+            out[:, l].copy_(step.layer_step(ql, kl, v[:, l].contiguous(), l))
+            topks[l].copy_(step.topk)
+
+    step.run_ahead(T)
+    torch.cuda.synchronize()
+    graph = None
+    g = torch.Generator().manual_seed(11)
+    for t in range(T):
+        q.copy_(torch.randn(B, L, Hq, D, generator=g).half())
+        k.copy_(torch.randn(B, L, Hkv, D, generator=g).half())
+        v.copy_(torch.randn(B, L, Hkv, D, generator=g).half())
+        want_o, want_sel, want_sc = _reference_token(ics_a, q, k, v, L, rope_scale)
+        if graph is None:  # capture only (a captured launch does not run); every token, the first included, is a replay
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=s):
+                body()
+            torch.cuda.current_stream().wait_stream(s)
+        graph.replay()
+        torch.cuda.synchronize()
+        err = (out.float() - want_o.view(B, L, Hq, D).float()).abs().max().item()
+        assert err <= ATTN_ATOL, (t, err)   # the batched plan splits the pages differently from the per-sequence one
+        for b in range(B):   # selected pages, in list positions: the device tables hold the whole run, so map through them
+            tab = {int(p): i for i, p in enumerate(ics_b[b].kv_cache.indicies)}
+            for l in range(L):
+                got = [sorted(tab[int(x)] for x in r if x >= 0) for r in topks[l][b].cpu().numpy()]
+                assert got == want_sel[b][l], (t, b, l)
+    # the run is over: host and device agree again; the pools hold what the eager path wrote
+    for b in range(B):
+        ia, ib = ics_a[b], ics_b[b]
+        assert ia.kv_cache.seqlen == ib.kv_cache.seqlen and len(ia.kv_cache.indicies) == len(ib.kv_cache.indicies)
+        for j, (pa, pb) in enumerate(zip(ia.kv_cache.indicies, ib.kv_cache.indicies)):
+            n = P if j < len(ia.kv_cache.indicies) - 1 else ia.kv_cache.last_page_len
+            assert torch.equal(ia.kv_cache.pool.buf[:, pa, :, :n].view(torch.int16), ib.kv_cache.pool.buf[:, pb, :, :n].view(torch.int16)), (b, j)

@@ -122,3 +122,7 @@ def test_argument_checks_of_the_round2_entry_points_need_no_gpu():
     assert lib.quest_estimate_fp8(one, one, 0, one, one, 1, 1, 128, 16, 0, None) == 0
     step = [one, one, one, one, one, one, 4, 0, 1, one, None, one, 1, 4, one, one, 2, 1, 1, 128, 16, 4, one, 1 << 20, None]
     assert lib.quest_decode_layer_step_fp8(*step) == -1  # no e4m3 pool
+    # device-side record updater
+    assert lib.quest_seq_desc_advance(None, 1, 16, None) == -1
+    assert lib.quest_seq_desc_advance(one, 0, 16, None) == -1
+    assert lib.quest_seq_desc_advance(one, 1, 0, None) == -1
