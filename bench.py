@@ -228,16 +228,19 @@ class Workload:
         qu, ic = self.qu, self.ic
         self.d_qkv.copy_(self.h_qkv, non_blocking=True)
         ic.begin_forward(1)
+        outs = []
         for l in range(L):
             q, k, v, out = self.e2e_views[l]
             if E2E_FOUR_OPS:  # the reference's call sequence (QuestAttention.py:100-150), op by op
                 qu.append_kv(k, v, ic, l)
                 s = qu.decode_estimate(q, ic, l)
                 qu.decode_topk(s, ic)
-                self.d_out[l] = qu.decode_sparse_attn(q, ic, l, ic.topk_dindices_buffer)
+                outs.append(qu.decode_sparse_attn(q, ic, l, ic.topk_dindices_buffer))  # a fresh tensor per call, as the reference's
             else:             # the same four ops as one native call
                 qu.decode_layer_step(q, k, v, ic, l, out=out)
         ic.end_forward()
+        if outs:
+            torch.cat(outs, out=self.d_out.view(L, *outs[0].shape[1:]))
         self.h_out.copy_(self.d_out, non_blocking=True)
 
 

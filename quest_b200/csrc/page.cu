@@ -213,9 +213,21 @@ extern "C" int quest_append_decode(const void* k, const void* v, void* kv_data, 
     return QUEST_ERR_BAD_ARG;
   const uint32_t row_vecs = num_heads * head_dim / 8;
   const uint32_t threads = 256, grid = (row_vecs + threads - 1) / threads;
-  quest::append_decode_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(
-      (const __half*)k, (const __half*)v, (__half*)kv_data, kv_indices, num_kv_pages, kv_last_page_len,
-      (__half*)meta_data, meta_indices, num_meta_pages, meta_last_page_len, row_vecs, page_size);
+  // programmatic launch: on the op-by-op path this kernel follows the previous layer's decode kernel, which releases its
+  // dependents before its merge tail; the kernel waits (griddepcontrol.wait) before it touches memory
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(threads);
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, quest::append_decode_kernel, (const __half*)k, (const __half*)v, (__half*)kv_data,
+                                     kv_indices, num_kv_pages, kv_last_page_len, (__half*)meta_data, meta_indices, num_meta_pages,
+                                     meta_last_page_len, row_vecs, page_size);
+  if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
 

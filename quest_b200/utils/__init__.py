@@ -67,10 +67,45 @@ def rms_norm_forward(input: torch.Tensor, weight: torch.Tensor, epsilon: float) 
     return o
 
 
+class _BoundOps:
+    """What the four decode operators pass to the library that does not change between the layers of one token.  The first
+    call of each operator after begin_forward goes through quest_b200._kernels (every check the reference's extension makes)
+    and, once that call has succeeded, leaves its constant arguments here; the same operator on the other layers then checks
+    only the tensors the caller hands in and makes the library call directly.  A tensor that does not look like the first
+    layer's sends the call down the checked route again, which raises the reference's message.  Dropped by begin_forward.
+    (The four calls per layer of quest/models/QuestAttention.py:100-150: 1.79 -> 1.11 ms per 32-layer token, tools/four_ops_profile.py.)"""
+    __slots__ = ("lib", "kv_ptrs", "meta_ptrs", "append", "estimate", "topk", "attn")
+
+    def __init__(self, ic: InferenceController):
+        self.lib = _kernels.load_library()
+        self.kv_ptrs, self.meta_ptrs = ic.layer_ptrs()
+        self.append = self.estimate = self.topk = self.attn = None
+
+
+def _ops_of(ic: InferenceController) -> _BoundOps:
+    ops = ic._ops
+    if ops is None:
+        ops = ic._ops = _BoundOps(ic)
+    return ops
+
+
+def _looks_like(t, shape, dtype, device) -> bool:
+    return t.shape == shape and t.dtype == dtype and t.device == device and t.is_contiguous()
+
+
 def append_kv(k: torch.Tensor, v: torch.Tensor, iController: InferenceController, layer_idx: int):
     """Append k/v ``[N, H, D]`` to the KV cache and update the page min/max metadata; dispatches to the
     prefill (N > 1) or decode (N == 1) kernel (reference __init__.py:69-125)."""
     seq_len = k.size(0)
+    ops = iController._ops
+    if ops is not None and ops.append is not None:
+        shape, dtype, device, kv_args, meta_args = ops.append
+        if _looks_like(k, shape, dtype, device) and _looks_like(v, shape, dtype, device):
+            rc = ops.lib.quest_append_decode(k.data_ptr(), v.data_ptr(), ops.kv_ptrs[layer_idx], *kv_args,
+                                             ops.meta_ptrs[layer_idx], *meta_args, _kernels._stream())
+            if rc:
+                _kernels._rc(rc, "append_kv_cache_decode")
+            return
     f = _kernels.append_kv_cache_prefill if seq_len > 1 else _kernels.append_kv_cache_decode
     f(
         k,
@@ -87,6 +122,12 @@ def append_kv(k: torch.Tensor, v: torch.Tensor, iController: InferenceController
         iController.metadata_last_page_idx,
         iController.layout,
     )
+    if seq_len == 1 and not iController.fp8_metadata:
+        ic = iController
+        _ops_of(ic).append = (k.shape, k.dtype, k.device,
+                              (ic.kv_indices_with_last.data_ptr(), ic.kv_indices_with_last.size(0), int(ic.kv_cache.last_page_len)),
+                              (ic.metadata_indices.data_ptr(), ic.metadata_indices.size(0), int(ic.metadata_cache.last_page_len),
+                               ic.num_kv_heads, ic.head_dim, ic.page_size))
     if iController.fp8_metadata:  # e4m3 copies of the entries of every page this append touched
         n_pages = iController.kv_indices_with_last.size(0)
         first = (iController.kv_cache.seqlen - seq_len) // iController.page_size
@@ -145,6 +186,15 @@ def prefill_layer_step(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, iContr
 
 def decode_estimate(q: torch.Tensor, iController: InferenceController, layer_idx: int) -> torch.Tensor:
     """Upper-bound attention score per page and head, last page excluded (reference __init__.py:171-205)."""
+    ops = iController._ops
+    if ops is not None and ops.estimate is not None:
+        shape, dtype, device, oshape, args = ops.estimate
+        if _looks_like(q, shape, dtype, device):
+            o = torch.empty(oshape, dtype=dtype, device=device)
+            rc = ops.lib.quest_estimate(q.data_ptr(), o.data_ptr(), oshape[1], ops.meta_ptrs[layer_idx], *args, _kernels._stream())
+            if rc:
+                _kernels._rc(rc, "estimate_attn_score")
+            return o
     o = torch.empty((iController.num_heads, iController.metadata_cache.seqlen - 1), dtype=q.dtype, device=q.device)
     if iController.fp8_metadata:
         _kernels.estimate_attn_score_fp8(q, o, iController.meta8[layer_idx], iController.metadata_indices)
@@ -161,12 +211,27 @@ def decode_estimate(q: torch.Tensor, iController: InferenceController, layer_idx
         # the controller's metadata pool is only ever written by append_kv, which keeps max >= min
         _kernels.EST_META_ORDERED,
     )
+    ic, ops = iController, _ops_of(iController)
+    # in a decode token (this begin_forward has seen append_kv of one token) the only metadata entry written since the last
+    # synchronisation point is the last page's, which is never scored: the other layers' launches may have their first loads in
+    # flight while the append kernel in front of them still runs (QUEST_EST_META_STABLE, as in decode_layer_step)
+    flags = _kernels.EST_META_ORDERED | (_kernels.EST_META_STABLE if ops.append is not None else 0)
+    ops.estimate = (q.shape, q.dtype, q.device, tuple(o.shape),
+                    (ic.metadata_indices.data_ptr(), ic.num_heads, ic.num_kv_heads, ic.head_dim, ic.page_size, flags))
     return o
 
 
 def decode_topk(estimated_attn_score: torch.Tensor, iController: InferenceController):
     """Select the page_budget-1 highest-scoring pages per head into iController.topk_dindices_buffer
     (reference __init__.py:207-237)."""
+    ops = iController._ops
+    if ops is not None and ops.topk is not None:
+        shape, dtype, device, args = ops.topk
+        if _looks_like(estimated_attn_score, shape, dtype, device):
+            rc = ops.lib.quest_topk(estimated_attn_score.data_ptr(), *args, _kernels._stream())
+            if rc:
+                _kernels._rc(rc, "topk_filtering")
+            return
     page_budet = iController.inference_page_budget - 1  # excluding the last page
     _kernels.topk_filtering(
         estimated_attn_score,
@@ -176,11 +241,24 @@ def decode_topk(estimated_attn_score: torch.Tensor, iController: InferenceContro
         iController.topk_buf,
         page_budet,
     )
+    ic, e = iController, estimated_attn_score
+    _ops_of(ic).topk = (e.shape, e.dtype, e.device,
+                        (ic.kv_indices_without_last.data_ptr(), _kernels._check_rows(ic.kv_indices_without_last, "estimated_indices"),
+                         ic.topk_dout_buffer.data_ptr(), ic.topk_dindices_buffer.data_ptr(), e.size(0), e.size(1), page_budet))
 
 
 def decode_sparse_attn(q: torch.Tensor, iController: InferenceController, layer_idx: int, topk_indices: torch.Tensor,
                        rope_scale: Optional[float] = None, rope_theta: Optional[float] = None) -> torch.Tensor:
     """Attention over the selected pages plus the last page (reference __init__.py:239-276)."""
+    ops = iController._ops
+    if ops is not None and ops.attn is not None:
+        shape, dtype, device, ids, pre, post = ops.attn
+        if topk_indices is ids and _looks_like(q, shape, dtype, device):
+            o = torch.empty_like(q)
+            rc = ops.lib.quest_decode_run(q.data_ptr(), o.data_ptr(), None, ops.kv_ptrs[layer_idx], *pre, *post, _kernels._stream())
+            if rc:
+                _kernels._rc(rc, "BatchDecodeWithPagedKVCache")
+            return o
     o = torch.empty_like(q, dtype=q.dtype, device=q.device)
     iController._decode_handler.forward(
         q,
@@ -193,6 +271,13 @@ def decode_sparse_attn(q: torch.Tensor, iController: InferenceController, layer_
         rope_scale,
         rope_theta,
     )
+    ic, w = iController, iController._decode_handler._wrapper
+    n_sel, Hq, Hkv, D, P = w._plan
+    ppc, _ = w._planned(n_sel, Hq, Hkv, D, P, q.device)
+    _ops_of(ic).attn = (q.shape, q.dtype, q.device, topk_indices,
+                        (topk_indices.data_ptr(), _kernels._check_rows(topk_indices, "paged_kv_indices"), n_sel,
+                         int(ic.kv_last_page_idx), int(ic.kv_cache.last_page_len)),
+                        (Hq, Hkv, D, P, ppc, w._ws.data_ptr(), w._ws.numel()))
     return o
 
 
@@ -213,11 +298,11 @@ class _BoundStep:
         self.fn = lib.quest_decode_layer_step_fp8 if ic.fp8_metadata else lib.quest_decode_layer_step
         self.mid = args[5:9]     # kv_indices, num_kv_pages, last idx, last len
         self.tail = args[10:]    # meta_indices ... workspace_bytes (stream appended per call)
-        layers = range(ic.kv_cache.pool.num_layers)
-        self.kv_ptrs = [ic.kv_cache.buf_layer(i).data_ptr() for i in layers]
-        # (metadata pool,) or (metadata pool, its e4m3 copy): the fp8 entry point takes both, in this order
-        self.meta_ptrs = [(ic.metadata_cache.buf_layer(i).data_ptr(),) + ((ic.meta8[i].data_ptr(),) if ic.fp8_metadata else ())
-                          for i in layers]
+        self.kv_ptrs, meta = ic.layer_ptrs()
+        if ic._step_meta is None:
+            # (metadata pool,) or (metadata pool, its e4m3 copy): the fp8 entry point takes both, in this order
+            ic._step_meta = [(m,) + ((ic.meta8[i].data_ptr(),) if ic.fp8_metadata else ()) for i, m in enumerate(meta)]
+        self.meta_ptrs = ic._step_meta
         self.qshape, self.kshape, self.dtype, self.device = q.shape, k.shape, q.dtype, q.device
 
 

@@ -49,6 +49,9 @@ class InferenceController:
         self._indptr_cache = {}
         self._topk_cache = {}
         self._step = None  # bound arguments of decode_layer_step, valid until the next begin_forward
+        self._ops = None   # bound arguments of the four decode operators (quest_b200.utils._BoundOps), same lifetime
+        self._pool_ptrs = None
+        self._step_meta = None
 
         self.kv_indices_with_last = None
         self.kv_indices_without_last = None
@@ -72,6 +75,7 @@ class InferenceController:
 
     # Called once per forwarding in all layers: reserve KV pages and metadata entries.
     def prepare_metadata(self, seq_len: int):
+        self._ops = self._step = None  # lengths change: whatever was bound for the last token is void
         appended_new_pages = self.kv_cache.append_seq(seq_len)
         _ = self.metadata_cache.append_seq(appended_new_pages)
 
@@ -113,6 +117,7 @@ class InferenceController:
     # Prepare metadata used for inference under certain PAGE_BUDGET (called per budget change).
     def begin_forward(self, seq_len: int, updateTensor: bool = True):
         self._step = None
+        self._ops = None
         kv_ids = self.kv_cache.indicies
         if updateTensor:
             self.sync_tables()
@@ -157,7 +162,16 @@ class InferenceController:
 
     # Release the split-KV plan (reference frees handler buffers here).
     def end_forward(self):
+        self._ops = None
         self._decode_handler.end_forward()
+
+    def layer_ptrs(self):
+        """(kv pool pointers, metadata pool pointers) per layer; the pools never move."""
+        if self._pool_ptrs is None:
+            layers = range(self.kv_cache.pool.num_layers)
+            self._pool_ptrs = ([self.kv_cache.buf_layer(i).data_ptr() for i in layers],
+                               [self.metadata_cache.buf_layer(i).data_ptr() for i in layers])
+        return self._pool_ptrs
 
     def need_estimate(self) -> bool:
         if self.inference_page_budget is None:
@@ -166,5 +180,6 @@ class InferenceController:
         return cur_page_nums > self.inference_page_budget
 
     def clean_states(self):
+        self._ops = self._step = None
         self.kv_cache.release()
         self.metadata_cache.release()

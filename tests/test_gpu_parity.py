@@ -359,6 +359,58 @@ def test_decode_layer_step_operator_equals_four_ops(kv_len, budget):
             assert torch.equal(pa[:-1], pb[:-1]) and torch.equal(pa[-1, :, :ca.last_page_len], pb[-1, :, :ca.last_page_len])
 
 
+@pytest.mark.parametrize("Hq,Hkv", [(32, 32), (32, 8)])
+def test_four_operators_bound_after_the_first_layer(Hq, Hkv):
+    """The four decode operators keep their per-token arguments after the first layer's (fully checked) calls and go to the
+    library directly on the other layers (quest_b200.utils._BoundOps): same pools, scores, ids and output as the one-call
+    layer step on a twin controller on every layer, over tokens that cross a page boundary; a tensor that does not look like
+    the first layer's still gets the reference's error message; nothing stays bound across begin_forward."""
+    L, D, P, budget, kv_len = 3, 128, 16, 9, 1006
+    g = torch.Generator().manual_seed(Hkv)
+    rnd = lambda *s: torch.randn(*s, generator=g).half().to(DEV)
+    ics = [qu.InferenceController(L, Hq, D, P, budget, 2048, torch.float16, torch.device(DEV), num_kv_heads=Hkv) for _ in range(2)]
+    k0, v0 = rnd(L, kv_len, Hkv, D), rnd(L, kv_len, Hkv, D)
+    for ic in ics:
+        ic.prepare_metadata(kv_len), ic.begin_forward(kv_len)
+        for l in range(L):
+            qu.append_kv(k0[l], v0[l], ic, l)
+        ic.end_forward()
+        assert ic._ops is None   # a prompt binds nothing
+    a, b = ics
+    for step in range(20):
+        a.prepare_metadata(1), a.begin_forward(1)
+        b.prepare_metadata(1), b.begin_forward(1)
+        for l in range(L):
+            tq, tk, tv = rnd(1, Hq, D), rnd(1, Hkv, D), rnd(1, Hkv, D)
+            qu.append_kv(tk, tv, a, l)
+            sc = qu.decode_estimate(tq, a, l)
+            qu.decode_topk(sc, a)
+            o1 = qu.decode_sparse_attn(tq, a, l, a.topk_dindices_buffer)
+            if l >= 1:
+                assert all(x is not None for x in (a._ops.append, a._ops.estimate, a._ops.topk, a._ops.attn))
+            o2 = qu.decode_layer_step(tq, tk, tv, b, l)
+            assert torch.equal(o1, o2), (step, l)
+            assert torch.equal(a.topk_dindices_buffer, b.topk_dindices_buffer), (step, l)
+            n = len(b.kv_cache.indicies) - 1
+            assert torch.equal(sc.view(torch.int16), b._scores_buffer(n).view(torch.int16)), (step, l)
+        if step == 7:  # bound by now: the checked route still answers for tensors that do not fit
+            with pytest.raises(RuntimeError, match="contiguous"):
+                qu.append_kv(rnd(1, D, Hkv).transpose(1, 2), tv, a, 1)
+            with pytest.raises(RuntimeError, match="CHECK_EQ"):
+                qu.decode_estimate(rnd(1, Hq, D // 2), a, 1)
+            with pytest.raises(RuntimeError):
+                qu.decode_topk(sc[:, :-1], a)
+            with pytest.raises(RuntimeError, match="dtype"):
+                qu.decode_sparse_attn(tq.float(), a, 1, a.topk_dindices_buffer)
+        a.end_forward(), b.end_forward()
+        assert a._ops is None
+    for ca, cb in ((a.kv_cache, b.kv_cache), (a.metadata_cache, b.metadata_cache)):
+        idx = torch.tensor(ca.indicies, device=DEV)
+        for l in range(L):
+            pa, pb = ca.buf_layer(l)[idx].view(torch.int16), cb.buf_layer(l)[idx].view(torch.int16)
+            assert torch.equal(pa[:-1], pb[:-1]) and torch.equal(pa[-1, :, :ca.last_page_len], pb[-1, :, :ca.last_page_len])
+
+
 def assert_workspace_at_rest(ws, Hq):
     """Reserved words, merge tickets and the selection's bin totals are zero after every step (they reset themselves); the one
     word that moves is the step counter of the page-id hand-over at byte 64 (csrc/common.cuh, kWsEpochOff)."""

@@ -28,6 +28,15 @@ def main():
         wl.e2e_step()
         torch.cuda.synchronize()
     print(f"four-operator path: {(time.perf_counter() - t0) / n * 1e3:.3f} ms per token (32 layers)")
+    # host-bound or device-bound?  enqueue 20 tokens without waiting: the host's share is the time until the last call returned
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(n):
+        wl.e2e_step()
+    t1 = time.perf_counter()
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    print(f"back to back: host enqueue {(t1 - t0) / n * 1e3:.3f} ms per token, device done after {(t2 - t0) / n * 1e3:.3f} ms per token")
     pr = cProfile.Profile()
     pr.enable()
     for _ in range(n):
