@@ -229,7 +229,10 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   const uint32_t G = kGr ? (uint32_t)kGr : kG ? (uint32_t)kG : Hq / Hkv;
   const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lir = lane % LPR, rsub = lane / LPR;
-  const uint32_t HV = kG == 1 ? Hq : Hkv;               // heads a pass walks per page: q heads (kG = 1) or kv heads
+  constexpr int kQR = kGr ? kGr : 1;                    // q rows a lane keeps in registers
+  // lane rows a pass walks per page: one per q head (kG = 1), one per kQR q heads (registers; g_shift > 0: 2^g_shift lane
+  // rows of the same warp-wide load share a kv-head row), one per kv head (kG = 0)
+  const uint32_t HV = (kG == 1 || kGr) ? Hq / kQR : Hkv;
   const uint32_t PPP = T_r / HV;                        // pages per CTA pass
   const uint32_t rt = warp * RPL + rsub;                // this lane's row in the pass
   const uint32_t pg_in = rt / HV, kvh = rt - pg_in * HV;  // kG = 1: kvh is the lane's q head
@@ -246,7 +249,7 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   constexpr bool kF8 = kOrdered == 2;
   constexpr uint32_t kEB = kF8 ? 1 : 2;  // bytes per bound
   const uint32_t row_bytes = Hkv * D * kEB, slab_bytes = P * row_bytes;
-  const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + (size_t)(kG == 1 ? kvh >> g_shift : kvh) * (D * kEB) + lir * (8 * kEB);
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(meta) + (size_t)((kG == 1 || kGr) ? kvh >> g_shift : kvh) * (D * kEB) + lir * (8 * kEB);
 
   // append_kv of the step's new token rides on one extra CTA of this launch.  The entry it updates (the last
   // page's) is not one of the scored ones; the decode kernel two launches later reads the new K/V row.
@@ -292,7 +295,6 @@ estimate_tile_kernel(const __half* __restrict__ q_, __half* __restrict__ o_, uin
   // layer step with the page-id hand-over (common.cuh, Handoff): one thread opens the step; nothing reads the counter before the
   // top-k kernel, which waits for this whole launch
   if (epoch != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) *epoch = *epoch + 1u;
-  constexpr int kQR = kGr ? kGr : 1;  // q rows a lane keeps in registers
   uint32_t qh[kQR][4], mk[kQR][4];
   if (kG == 1 || kGr) {
 #pragma unroll
@@ -457,8 +459,16 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   const bool per_q = !in_regs && (G & (G - 1)) == 0 && T_r % Hq == 0;  // one q head per lane row (MHA, other power-of-two groups)
   uint32_t g_shift = 0;
   while ((1u << g_shift) < G) ++g_shift;
-  const uint32_t PPP = T_r / (per_q ? Hq : Hkv);
-  const uint32_t occ = (in_regs && G == 4) ? 1u : 2u;  // resident CTAs per SM
+  // A group of 4 either sits in one lane row (4 q rows + sign masks = 32 registers: one CTA per SM) or is split over the two lane
+  // rows of one warp-wide load with two q rows each (64 registers, two CTAs per SM, 1.4x the instructions).  Alone the first is
+  // faster (10.3 vs 10.9 us, 32q/8kv at 128K); inside a layer step the second is (31.25 vs 31.7 us at 128K, 16.4 vs 16.9 us at 32K:
+  // twice the CTAs take the slots the launch before frees).  profiles/r02_b_experiments.md section 12.
+  const int layout = debug_option(QUEST_DBG_EST_PER_Q);
+  const bool in_step = batch == 1 && (ap.k != nullptr || hist != nullptr);
+  const bool split4 = in_regs && G == 4 && T_r % (Hq / 2) == 0 && (layout == 2 || (layout == 0 && in_step && !(flags & kEstMetaFp8)));  // e4m3 pool: the split is slower in the step too
+  const uint32_t in_reg_rows = split4 ? 2u : G;   // q rows per lane row
+  const uint32_t PPP = T_r / (per_q ? Hq : in_regs ? Hq / in_reg_rows : Hkv);
+  const uint32_t occ = (in_regs && G == 4 && !split4) ? 1u : 2u;  // resident CTAs per SM
   uint32_t grid = occ * num_sms / batch;  // CTAs per sequence
   if (grid < 8) grid = 8;
   grid -= (ap.k != nullptr ? 1u : 0u);  // scanning CTAs
@@ -473,7 +483,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   if (f8 && ba.descs != nullptr) return QUEST_ERR_UNSUPPORTED;  // the descriptor records name the fp16 pool only
   const bool ord = flags & QUEST_EST_META_ORDERED;
 #define QUEST_EST_KERN(KG) (f8 ? estimate_tile_kernel<D, 2, KG> : ord ? estimate_tile_kernel<D, 1, KG> : estimate_tile_kernel<D, 0, KG>)
-  auto kern = per_q ? QUEST_EST_KERN(1) : !in_regs ? QUEST_EST_KERN(0) : G == 2 ? QUEST_EST_KERN(102) : QUEST_EST_KERN(104);
+  auto kern = per_q ? QUEST_EST_KERN(1) : !in_regs ? QUEST_EST_KERN(0) : (G == 2 || split4) ? QUEST_EST_KERN(102) : QUEST_EST_KERN(104);
 #undef QUEST_EST_KERN
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -491,7 +501,7 @@ static int launch_estimate_tile(const void* q, void* o, uint32_t len, const void
   cfg.numAttrs = 1;
   const uint32_t p_magic = P <= 1 ? 0u : (uint32_t)((0x100000000ull + P - 1) / P);
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, (const __half*)q, (__half*)o, len, (const __half*)meta, meta_indices,
-                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : 0u, ap, ba, hist, epoch);
+                                     Hq, Hkv, P, p_magic, flags & QUEST_EST_META_STABLE, per_q ? g_shift : split4 ? 1u : 0u, ap, ba, hist, epoch);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }

@@ -128,12 +128,13 @@ def test_estimate_bitexact_shapes_and_gqa(Hq, Hkv, D, P, kv_len, flags):
     np.testing.assert_array_equal(bits(o), orc.estimate_scores(q[0], oc.meta_pool, oc.meta_indices, n, Hq).view(np.int16))
 
 
-@pytest.mark.parametrize("per_q", [0, 1])
+@pytest.mark.parametrize("per_q", [0, 1, 2, 3])
 @pytest.mark.parametrize("Hq,Hkv,D,P,kv_len", [(32, 8, 128, 16, 5000), (16, 8, 128, 16, 1300), (8, 4, 64, 16, 700), (16, 4, 256, 16, 900),
                                                 (16, 2, 128, 16, 777), (64, 8, 128, 16, 2100)])
 def test_estimate_bitexact_gqa_layouts(Hq, Hkv, D, P, kv_len, per_q):
     """Groups of 2 and 4 keep the group's q rows in registers and score each kv row once per q head (mixed-precision FMAs);
-    DBG_EST_PER_Q = 1 selects the one-q-head-per-lane-row layout for the same shapes (the layout groups of 8 always use)."""
+    DBG_EST_PER_Q = 1 selects the one-q-head-per-lane-row layout for the same shapes (the layout groups of 8 always use), 2 / 3 the
+    two layouts of a group of 4 (split over two lane rows / whole group in one)."""
     oc, gc, k, v, rng = make_pair(kv_len, P, Hkv, D, seed=kv_len + Hq)
     q = rng.standard_normal((1, Hq, D), dtype=np.float32).astype(np.float16)
     n = len(oc.kv_indices) - 1

@@ -32,6 +32,8 @@ def main():
     lib = K.load_library()
     if os.environ.get("QUEST_NO_HANDOFF"):  # A/B: the layer step's decode launch waits for the top-k launch
         lib.quest_debug_set_option(K.DBG_NO_HANDOFF, 1)
+    if os.environ.get("QUEST_EST_PER_Q"):  # A/B of the GQA estimate layouts (include/quest_b200.h, QUEST_DBG_EST_PER_Q)
+        lib.quest_debug_set_option(K.DBG_EST_PER_Q, int(os.environ["QUEST_EST_PER_Q"]))
     Hq, Hkv, L = a.hq, a.hkv, a.layers
     ic = qu.InferenceController(L, Hq, D, P, a.budget // P, a.ctx, torch.float16, dev, num_kv_heads=Hkv)
     fill(ic, L, a.ctx - 1, Hkv, dev)
