@@ -237,7 +237,10 @@ __device__ unsigned long long g_topk_hist_clk[256 * 4];
 #define TH_STAMP(i) do { } while (0)
 #endif
 
-template <int G>
+// kOwn: nobody has published bin totals (stand-alone quest_topk, the global selection of the sequence-sharded step): the CTA
+// counts its register-resident keys into 2048 shared-memory bins first -- one pass of shared-memory atomics instead of the four
+// radix passes of the register select -- and goes on as above.
+template <int G, bool kOwn = false>
 __global__ void __launch_bounds__(kHistThreads, (G >= 4 && G <= 6) ? 2 : 0)  // two rows per SM while 64 registers hold the keys (batched steps: rows > SMs)
 topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ hist_, const int32_t* __restrict__ in_idx_,
                  uint32_t in_stride_, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_, const BatchArgs ba,
@@ -246,6 +249,7 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
   constexpr uint32_t BPT = kHistBins / kHistThreads;  // 4 bins = two packed words per thread
   static_assert(BPT == 4, "one 8-byte load of bin totals per thread");
   __shared__ uint32_t s_wtot[W], s_wtot2[W], s_sub[32], s_bstar, s_need1;
+  __shared__ __align__(16) uint32_t s_bins[kOwn ? kHistBins : 4];
   const uint32_t head = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int32_t* __restrict__ in_idx = in_idx_;
   int32_t* __restrict__ out_idx = out_idx_;
@@ -270,9 +274,14 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
     if (len > (uint32_t)(NK * kHistThreads)) len = NK * kHistThreads;  // never: the host sizes the variant by its bound
   }
   // this thread's bins [2048 - 4(t+1), 2048 - 4t): read, and put back to zero for the next step
-  uint2* hp = reinterpret_cast<uint2*>(hist + (size_t)head * (kHistBins / 2) + (kHistBins - BPT * (t + 1)) / 2);
-  const uint2 hv = *hp;
-  *hp = make_uint2(0u, 0u);
+  uint2 hv = make_uint2(0u, 0u);
+  if (!kOwn) {
+    uint2* hp = reinterpret_cast<uint2*>(hist + (size_t)head * (kHistBins / 2) + (kHistBins - BPT * (t + 1)) / 2);
+    hv = *hp;
+    *hp = make_uint2(0u, 0u);
+  } else {
+    *reinterpret_cast<uint4*>(s_bins + BPT * t) = make_uint4(0u, 0u, 0u, 0u);
+  }
   if (k > len) {
     for (uint32_t i = len + t; i < k_; i += kHistThreads) {
       out_idx[(size_t)head * (xo.idx_stride ? xo.idx_stride : k_) + i] = -1;
@@ -297,7 +306,16 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
   const bool all = k >= len;  // every page of the row
   if (!all) {
     // ---- threshold bin: the inclusive scan over threads counts the keys in a thread's bins and all higher ones
-    const uint32_t c[BPT] = {hv.x & 0xffffu, hv.x >> 16, hv.y & 0xffffu, hv.y >> 16};  // ascending bins
+    uint32_t c[BPT] = {hv.x & 0xffffu, hv.x >> 16, hv.y & 0xffffu, hv.y >> 16};  // ascending bins
+    if (kOwn) {
+      __syncthreads();  // bins zeroed
+#pragma unroll
+      for (int j = 0; j < NK; ++j)
+        if ((uint32_t)j < nvalid) atomicAdd(&s_bins[key[j] >> kHistBinShift], 1u);
+      __syncthreads();
+      const uint4 cv = *reinterpret_cast<const uint4*>(s_bins + kHistBins - BPT * (t + 1));
+      c[0] = cv.x, c[1] = cv.y, c[2] = cv.z, c[3] = cv.w;
+    }
     const uint32_t mine = c[0] + c[1] + c[2] + c[3];
     uint32_t incl = mine;
 #pragma unroll
@@ -396,7 +414,7 @@ extern "C" int quest_debug_topk_hist_clocks(unsigned long long* host_out, uint32
 }
 #endif
 
-template <int G>
+template <int G, bool kOwn = false>
 static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
                             uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream,
                             const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, const Handoff& ho = Handoff{},
@@ -410,7 +428,7 @@ static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* i
   attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba, ho, xo);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G, kOwn>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba, ho, xo);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
@@ -428,6 +446,20 @@ int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, ui
   if (max_len <= 24u * kHistThreads) return launch_topk_hist<6>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
   if (max_len <= 32u * kHistThreads) return launch_topk_hist<8>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
   return QUEST_ERR_UNSUPPORTED;
+}
+
+// Stand-alone rows of up to 4096 scores: the same one-pass selection over bin totals the CTA counts itself (32 heads, graph:
+// 3.8 -> 3.1 us at 2047 scores, 6.2 -> 4.6 us at 4095; at 8191 the 4-CTA cluster kernel stays ahead, 6.7 against 7.7 us).
+static bool topk_own_hist_covers(uint32_t len) { return len <= 8u * kHistThreads && topk_hist_covers(len); }
+static int topk_own_hist(const void* scores, const int32_t* in_idx, uint32_t in_stride, void* out_val, int32_t* out_idx,
+                         uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t s) {
+  const HistOut xo = {(uint16_t*)out_val, 0u, 0u};
+  const BatchArgs ba = {};
+  const Handoff ho = {};
+#define QUEST_OWN(G) launch_topk_hist<G, true>(scores, nullptr, in_idx, in_stride, out_idx, num_heads, len, k, s, ba, 1, ho, xo)
+  if (len <= 4u * kHistThreads) return QUEST_OWN(1);
+  return QUEST_OWN(2);
+#undef QUEST_OWN
 }
 
 // A cluster pays off while all its CTAs (512 threads at 40 registers: 3 per SM) run in one wave; beyond that the single-CTA rows
@@ -518,6 +550,9 @@ extern "C" int quest_topk(const void* scores, const int32_t* in_idx, uint32_t in
   if (len > quest::kTopkMaxLen) return QUEST_ERR_UNSUPPORTED;
   cudaStream_t s = (cudaStream_t)stream;
   const bool no_fast = quest::debug_option(QUEST_DBG_TOPK_GENERIC) != 0;  // test hook: force the generic kernels
+  // one pass over self-counted bin totals (QUEST_DBG_TOPK_NO_HIST = 1: the register radix / cluster kernels below)
+  if (!no_fast && quest::topk_own_hist_covers(len) && quest::debug_option(QUEST_DBG_TOPK_NO_CLUSTER) == 0)
+    return quest::topk_own_hist(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 1024) return quest::launch_topk_fast<8, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 2048) return quest::launch_topk_fast<16, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && quest::topk_use_cluster()) {

@@ -175,12 +175,24 @@ def run_topk(scores, payload, k):
 
 @pytest.mark.parametrize("n,k", [(13, 2), (24, 24), (77, 19), (311, 69), (1024, 1024), (1025, 7), (1110, 251), (2047, 127), (2047, 1), (2048, 2048), (3001, 640), (4096, 1), (4097, 333),
                                  (8191, 255), (8192, 4095), (8193, 511), (12000, 300), (16384, 1023), (16385, 64), (65535, 511)])
-@pytest.mark.parametrize("dist", ["normal", "ties", "const"])
-def test_topk_exact(n, k, dist):
+@pytest.mark.parametrize("dist", ["normal", "narrow", "ties", "const"])
+@pytest.mark.parametrize("radix", [0, 1])
+def test_topk_exact(n, k, dist, radix):
+    """quest_topk on rows of up to 4096 scores selects in one pass over bin totals the CTA counts itself (topk_hist_kernel<G, true>);
+    radix = 1 (DBG_TOPK_NO_HIST) keeps the register radix kernels under test for those lengths; longer rows always use them."""
+    if radix and n > 4096:
+        pytest.skip("same kernels as radix = 0")
+    with K.debug_option(K.DBG_TOPK_NO_HIST, radix):
+        _topk_exact(n, k, dist)
+
+
+def _topk_exact(n, k, dist):
     H = 32 if n < 10000 else 4
     rng = np.random.default_rng(n * 7 + k)
     if dist == "normal":
         s = (rng.standard_normal((H, n)) * 30 + 100).astype(np.float16)
+    elif dist == "narrow":  # every score in one or two bins: the low key bits decide
+        s = (rng.random((H, n)) * 3.9 + 128).astype(np.float16)
     elif dist == "ties":  # few distinct values incl. +-0 and negatives: threshold ties everywhere
         s = rng.choice(np.array([-2.0, -0.0, 0.0, 0.5, 1.0, 1.5, 96.0], dtype=np.float16), size=(H, n))
     else:
