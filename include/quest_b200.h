@@ -363,7 +363,7 @@ void quest_device_error_clear(void);
 #define QUEST_DBG_PREFILL_P_SMEM 3   /* 1: TMA prefill hands P to the PV MMA through shared memory             */
 #define QUEST_DBG_TOPK_NO_CLUSTER 4  /* 1: one CTA per top-k row for every length                              */
 #define QUEST_DBG_TOPK_GENERIC 5     /* 1: shared-memory-key top-k kernel for every length                     */
-#define QUEST_DBG_TOPK_NO_HIST 6     /* 1: layer step selects with the stand-alone top-k kernels (no bin totals) */
+#define QUEST_DBG_TOPK_NO_HIST 6     /* 1: no selection from bin totals: the layer step and quest_topk use the register radix kernels */
 #define QUEST_DBG_EST_PER_Q 7        /* GQA estimate layout for groups of 2 / 4.  1: one lane row per q head (the round-1 layout); groups
                                         of 4 only: 2 = two lane rows x two q rows in registers, 3 = the whole group in one lane row
                                         (0 picks 2 inside a batch-1 layer step, 3 elsewhere)                        */
