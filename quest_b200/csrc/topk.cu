@@ -240,7 +240,12 @@ __device__ unsigned long long g_topk_hist_clk[256 * 4];
 // kOwn: nobody has published bin totals (stand-alone quest_topk, the global selection of the sequence-sharded step): the CTA
 // counts its register-resident keys into 2048 shared-memory bins first -- one pass of shared-memory atomics instead of the four
 // radix passes of the register select -- and goes on as above.
-template <int G, bool kOwn = false>
+// C > 1: the row is split over a thread-block cluster of C CTAs (2048*G positions each, in rank order).  Every CTA reads the same
+// bin totals and takes the same decisions; what depends on the other slices -- the threshold bin's low-bit counts, the (greater,
+// equal) totals of the lower ranks, with kOwn the bin counts themselves -- is read from their shared memory after a cluster
+// barrier (three in all, four with kOwn).  The integer work per row is what bounds a selection on one SM (8191 scores: 7.7 us in
+// one CTA), and a batch-1 step keeps only `heads` of the 148 SMs busy.
+template <int G, bool kOwn = false, int C = 1>
 __global__ void __launch_bounds__(kHistThreads, (G >= 4 && G <= 6) ? 2 : 0)  // two rows per SM while 64 registers hold the keys (batched steps: rows > SMs)
 topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ hist_, const int32_t* __restrict__ in_idx_,
                  uint32_t in_stride_, int32_t* __restrict__ out_idx_, uint32_t len_, uint32_t k_, const BatchArgs ba,
@@ -250,7 +255,11 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
   static_assert(BPT == 4, "one 8-byte load of bin totals per thread");
   __shared__ uint32_t s_wtot[W], s_wtot2[W], s_sub[32], s_bstar, s_need1;
   __shared__ __align__(16) uint32_t s_bins[kOwn ? kHistBins : 4];
-  const uint32_t head = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  __shared__ uint32_t s_tot;
+  namespace cg = cooperative_groups;
+  uint32_t rank = 0;
+  if constexpr (C > 1) rank = cg::this_cluster().block_rank();
+  const uint32_t head = blockIdx.x / C, n_heads = gridDim.x / C, t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int32_t* __restrict__ in_idx = in_idx_;
   int32_t* __restrict__ out_idx = out_idx_;
   uint32_t* __restrict__ hist = hist_;
@@ -269,29 +278,33 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
     in_idx = d->kv_indices;
     in_stride = 0;
     scores += (size_t)blockIdx.y * ba.score_stride;
-    out_idx += (size_t)blockIdx.y * gridDim.x * k_;
+    out_idx += (size_t)blockIdx.y * n_heads * k_;
     hist += (size_t)blockIdx.y * (ba.ws_stride / 4);
-    if (len > (uint32_t)(NK * kHistThreads)) len = NK * kHistThreads;  // never: the host sizes the variant by its bound
+    if (len > (uint32_t)(C * NK * kHistThreads)) len = C * NK * kHistThreads;  // never: the host sizes the variant by its bound
   }
   // this thread's bins [2048 - 4(t+1), 2048 - 4t): read, and put back to zero for the next step
   uint2 hv = make_uint2(0u, 0u);
+  uint2* hp = nullptr;
   if (!kOwn) {
-    uint2* hp = reinterpret_cast<uint2*>(hist + (size_t)head * (kHistBins / 2) + (kHistBins - BPT * (t + 1)) / 2);
+    hp = reinterpret_cast<uint2*>(hist + (size_t)head * (kHistBins / 2) + (kHistBins - BPT * (t + 1)) / 2);
     hv = *hp;
-    *hp = make_uint2(0u, 0u);
+    if (C == 1) *hp = make_uint2(0u, 0u);  // C > 1: rank 0, once every CTA of the cluster has read them
   } else {
     *reinterpret_cast<uint4*>(s_bins + BPT * t) = make_uint4(0u, 0u, 0u, 0u);
   }
   if (k > len) {
-    for (uint32_t i = len + t; i < k_; i += kHistThreads) {
+    for (uint32_t i = len + t; i < k_ && rank == 0; i += kHistThreads) {
       out_idx[(size_t)head * (xo.idx_stride ? xo.idx_stride : k_) + i] = -1;
       if (xo.val != nullptr) xo.val[(size_t)head * (xo.val_stride ? xo.val_stride : k_) + i] = 0xfc00u;  // -inf: sorts last
     }
     k = len;
   }
-  if (k == 0) return;
+  if (k == 0) {  // uniform over the cluster: nobody waits at a barrier
+    if (C > 1 && !kOwn && rank == 0) *hp = make_uint2(0u, 0u);
+    return;
+  }
   const uint16_t* s = scores + (size_t)head * len;
-  const uint32_t p0 = t * NK;
+  const uint32_t p0 = (rank * kHistThreads + t) * NK;
   // rows of an odd `len` are only 2-byte aligned: scalar loads, all independent
   uint32_t key[NK];
   int32_t pay[NK];
@@ -313,8 +326,19 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
       for (int j = 0; j < NK; ++j)
         if ((uint32_t)j < nvalid) atomicAdd(&s_bins[key[j] >> kHistBinShift], 1u);
       __syncthreads();
-      const uint4 cv = *reinterpret_cast<const uint4*>(s_bins + kHistBins - BPT * (t + 1));
-      c[0] = cv.x, c[1] = cv.y, c[2] = cv.z, c[3] = cv.w;
+      if constexpr (C > 1) {
+        cg::cluster_group cl = cg::this_cluster();
+        cl.sync();  // every slice counted
+        c[0] = c[1] = c[2] = c[3] = 0;
+#pragma unroll
+        for (int r = 0; r < C; ++r) {
+          const uint4 cv = *reinterpret_cast<const uint4*>(cl.map_shared_rank(s_bins, r) + kHistBins - BPT * (t + 1));
+          c[0] += cv.x, c[1] += cv.y, c[2] += cv.z, c[3] += cv.w;
+        }
+      } else {
+        const uint4 cv = *reinterpret_cast<const uint4*>(s_bins + kHistBins - BPT * (t + 1));
+        c[0] = cv.x, c[1] = cv.y, c[2] = cv.z, c[3] = cv.w;
+      }
     }
     const uint32_t mine = c[0] + c[1] + c[2] + c[3];
     uint32_t incl = mine;
@@ -348,8 +372,14 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
     for (int j = 0; j < NK; ++j)
       if ((uint32_t)j < nvalid && (key[j] >> kHistBinShift) == bstar) atomicAdd(&s_sub[key[j] & 31u], 1u);
     __syncthreads();
+    if constexpr (C > 1) cg::this_cluster().sync();  // every slice's low-bit counts are in place; every CTA has read the bin totals
     {  // every warp resolves the sub-bin by itself: lane i looks at sub-bin 31 - i
-      const uint32_t cs = s_sub[31 - lane];
+      uint32_t cs = s_sub[31 - lane];
+      if constexpr (C > 1) {
+        cs = 0;
+#pragma unroll
+        for (int r = 0; r < C; ++r) cs += cg::this_cluster().map_shared_rank(s_sub, r)[31 - lane];
+      }
       uint32_t inc = cs;
 #pragma unroll
       for (int off = 1; off < 32; off <<= 1) {
@@ -385,6 +415,15 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
 #pragma unroll
   for (int w = 0; w < W; ++w)
     if ((uint32_t)w < warp) before += s_wtot2[w];
+  if constexpr (C > 1) {  // + the (greater, equal) totals of the slices before this one
+    cg::cluster_group cl = cg::this_cluster();
+    if (t == kHistThreads - 1) s_tot = before + pk;
+    if (!kOwn && rank == 0) *hp = make_uint2(0u, 0u);  // all: no barrier has been passed yet, but nobody reads the totals either
+    cl.sync();
+#pragma unroll
+    for (int r = 0; r < C; ++r)
+      if ((uint32_t)r < rank) before += *cl.map_shared_rank(&s_tot, r);
+  }
   uint32_t gt_before = before >> 16, eq_before = before & 0xffffu;
   int32_t* out = out_idx + (size_t)head * (xo.idx_stride ? xo.idx_stride : k_);
   uint16_t* outv = xo.val != nullptr ? xo.val + (size_t)head * (xo.val_stride ? xo.val_stride : k_) : nullptr;
@@ -405,6 +444,7 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
     gt_before += gt;
     eq_before += eq;
   }
+  if constexpr (C > 1) cg::this_cluster().sync();  // nobody leaves while its shared memory may still be read
   TH_STAMP(2);
 }
 
@@ -414,24 +454,31 @@ extern "C" int quest_debug_topk_hist_clocks(unsigned long long* host_out, uint32
 }
 #endif
 
-template <int G, bool kOwn = false>
+template <int G, bool kOwn = false, int C = 1>
 static int launch_topk_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, uint32_t in_stride, int32_t* out_idx,
                             uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t stream,
                             const BatchArgs& ba = BatchArgs{}, uint32_t batch = 1, const Handoff& ho = Handoff{},
                             const HistOut& xo = HistOut{}) {
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(num_heads, batch);
+  cfg.gridDim = dim3(num_heads * C, batch);
   cfg.blockDim = dim3(kHistThreads);
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = quest::pdl_enabled();
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = C;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G, kOwn>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba, ho, xo);
+  cfg.numAttrs = C > 1 ? 2 : 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, topk_hist_kernel<G, kOwn, C>, (const uint16_t*)scores, hist, in_idx, in_stride, out_idx, len, k, ba, ho, xo);
   if (e != cudaSuccess) return (int)e;
   QUEST_RETURN_LAUNCH();
 }
+
+static bool topk_cluster_fits(uint32_t rows, uint32_t c);
+static bool topk_use_cluster();
 
 // Layer step: rows whose bin totals the estimate kernel has published in `hist` (max_len bounds every row).
 bool topk_hist_covers(uint32_t max_len) { return max_len <= 32u * kHistThreads && debug_option(QUEST_DBG_TOPK_NO_HIST) == 0; }
@@ -440,6 +487,11 @@ int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, ui
                    const Handoff& ho, const HistOut& xo) {
   if (max_len <= 4u * kHistThreads) return launch_topk_hist<1>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
   if (max_len <= 8u * kHistThreads) return launch_topk_hist<2>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
+  // rows of 4097 ... 16384 pages: one row over a cluster of 4 CTAs (2048 / 4096 positions each) while all clusters run in one wave
+  if (topk_use_cluster() && max_len <= 16u * kHistThreads && topk_cluster_fits(num_heads * batch, 4))
+    return launch_topk_hist<1, false, 4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
+  if (topk_use_cluster() && max_len <= 32u * kHistThreads && topk_cluster_fits(num_heads * batch, 4))
+    return launch_topk_hist<2, false, 4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
   if (max_len <= 16u * kHistThreads) return launch_topk_hist<4>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
   // in-between bounds: a batch just past 8192 pages (BASELINE configs[3]: 8193) pays for the keys per thread it is compiled for
   if (max_len <= 20u * kHistThreads) return launch_topk_hist<5>(scores, hist, in_idx, in_stride, out_idx, num_heads, max_len, k, s, ba, batch, ho, xo);
@@ -450,7 +502,10 @@ int topk_from_hist(const void* scores, uint32_t* hist, const int32_t* in_idx, ui
 
 // Stand-alone rows of up to 4096 scores: the same one-pass selection over bin totals the CTA counts itself (32 heads, graph:
 // 3.8 -> 3.1 us at 2047 scores, 6.2 -> 4.6 us at 4095; at 8191 the 4-CTA cluster kernel stays ahead, 6.7 against 7.7 us).
-static bool topk_own_hist_covers(uint32_t len) { return len <= 8u * kHistThreads && topk_hist_covers(len); }
+static bool topk_own_hist_covers(uint32_t len, uint32_t rows) {
+  if (!topk_hist_covers(len)) return false;
+  return len <= 8u * kHistThreads || (topk_use_cluster() && topk_cluster_fits(rows, 4));
+}
 static int topk_own_hist(const void* scores, const int32_t* in_idx, uint32_t in_stride, void* out_val, int32_t* out_idx,
                          uint32_t num_heads, uint32_t len, uint32_t k, cudaStream_t s) {
   const HistOut xo = {(uint16_t*)out_val, 0u, 0u};
@@ -458,8 +513,10 @@ static int topk_own_hist(const void* scores, const int32_t* in_idx, uint32_t in_
   const Handoff ho = {};
 #define QUEST_OWN(G) launch_topk_hist<G, true>(scores, nullptr, in_idx, in_stride, out_idx, num_heads, len, k, s, ba, 1, ho, xo)
   if (len <= 4u * kHistThreads) return QUEST_OWN(1);
-  return QUEST_OWN(2);
+  if (len <= 8u * kHistThreads) return QUEST_OWN(2);
 #undef QUEST_OWN
+  if (len <= 16u * kHistThreads) return launch_topk_hist<1, true, 4>(scores, nullptr, in_idx, in_stride, out_idx, num_heads, len, k, s, ba, 1, ho, xo);
+  return launch_topk_hist<2, true, 4>(scores, nullptr, in_idx, in_stride, out_idx, num_heads, len, k, s, ba, 1, ho, xo);
 }
 
 // A cluster pays off while all its CTAs (512 threads at 40 registers: 3 per SM) run in one wave; beyond that the single-CTA rows
@@ -551,7 +608,7 @@ extern "C" int quest_topk(const void* scores, const int32_t* in_idx, uint32_t in
   cudaStream_t s = (cudaStream_t)stream;
   const bool no_fast = quest::debug_option(QUEST_DBG_TOPK_GENERIC) != 0;  // test hook: force the generic kernels
   // one pass over self-counted bin totals (QUEST_DBG_TOPK_NO_HIST = 1: the register radix / cluster kernels below)
-  if (!no_fast && quest::topk_own_hist_covers(len) && quest::debug_option(QUEST_DBG_TOPK_NO_CLUSTER) == 0)
+  if (!no_fast && quest::topk_own_hist_covers(len, num_heads))
     return quest::topk_own_hist(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 1024) return quest::launch_topk_fast<8, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);
   if (!no_fast && len <= 2048) return quest::launch_topk_fast<16, 1>(scores, in_idx, in_idx_row_stride, out_val, out_idx, num_heads, len, k, s);

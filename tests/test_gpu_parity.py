@@ -178,9 +178,10 @@ def run_topk(scores, payload, k):
 @pytest.mark.parametrize("dist", ["normal", "narrow", "ties", "const"])
 @pytest.mark.parametrize("radix", [0, 1])
 def test_topk_exact(n, k, dist, radix):
-    """quest_topk on rows of up to 4096 scores selects in one pass over bin totals the CTA counts itself (topk_hist_kernel<G, true>);
-    radix = 1 (DBG_TOPK_NO_HIST) keeps the register radix kernels under test for those lengths; longer rows always use them."""
-    if radix and n > 4096:
+    """quest_topk on rows of up to 16384 scores selects in one pass over bin totals the CTA counts itself (topk_hist_kernel<G, true>;
+    beyond 4096 one row over a cluster of 4 / 8 CTAs); radix = 1 (DBG_TOPK_NO_HIST) keeps the register radix and radix-cluster
+    kernels under test for those lengths; longer rows always use them."""
+    if radix and n > 16384:
         pytest.skip("same kernels as radix = 0")
     with K.debug_option(K.DBG_TOPK_NO_HIST, radix):
         _topk_exact(n, k, dist)
@@ -210,9 +211,18 @@ def _topk_exact(n, k, dist):
 
 
 @pytest.mark.parametrize("n,k", [(13, 2), (24, 24), (77, 19), (311, 69), (1024, 1024), (1025, 7), (2047, 127), (2047, 1), (2048, 2048), (2049, 511),
-                                 (3001, 640), (4096, 1), (4097, 333), (8191, 255), (8192, 4095), (8192, 8191)])
+                                 (3001, 640), (4096, 1), (4097, 333), (6145, 6145), (8191, 255), (8192, 4095), (8192, 8191), (8193, 511),
+                                 (12000, 300), (12289, 12288), (16384, 1023)])
 @pytest.mark.parametrize("dist", ["normal", "narrow", "ties", "const"])
-def test_topk_from_bin_totals_exact(n, k, dist):
+@pytest.mark.parametrize("cluster", [1, 0])
+def test_topk_from_bin_totals_exact(n, k, dist, cluster):
+    if not cluster and n <= 4096:
+        pytest.skip("no cluster variant at this length")
+    with K.debug_option(K.DBG_TOPK_NO_CLUSTER, 1 - cluster):  # 0: rows beyond 4096 pages in one CTA (batched steps with many rows)
+        _topk_from_bin_totals_exact(n, k, dist)
+
+
+def _topk_from_bin_totals_exact(n, k, dist):
     """The layer step's top-k (topk_hist_kernel: threshold from the bin totals the estimate kernel publishes) on crafted
     rows: same positions and order as the oracle, bin totals back at zero afterwards.  "narrow": every score in one or two
     bins, so the low key bits decide; "ties"/"const": the tie quota decides."""

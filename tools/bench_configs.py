@@ -37,6 +37,15 @@ def peak():
         return 6650.0
 
 
+def apply_debug_env():
+    """QUEST_DBG="4=1,7=2": library A/B switches (include/quest_b200.h QUEST_DBG_*) for the tools; the library itself never reads
+    the environment."""
+    import quest_b200._kernels as K
+    for kv in filter(None, os.environ.get("QUEST_DBG", "").split(",")):
+        o, v = kv.split("=")
+        K.load_library().quest_debug_set_option(int(o), int(v))
+
+
 def timed(fn, steps, warmup, dist_on):
     for _ in range(warmup):
         fn()

@@ -34,6 +34,8 @@ def main():
         lib.quest_debug_set_option(K.DBG_NO_HANDOFF, 1)
     if os.environ.get("QUEST_EST_PER_Q"):  # A/B of the GQA estimate layouts (include/quest_b200.h, QUEST_DBG_EST_PER_Q)
         lib.quest_debug_set_option(K.DBG_EST_PER_Q, int(os.environ["QUEST_EST_PER_Q"]))
+    from tools.bench_configs import apply_debug_env
+    apply_debug_env()
     Hq, Hkv, L = a.hq, a.hkv, a.layers
     ic = qu.InferenceController(L, Hq, D, P, a.budget // P, a.ctx, torch.float16, dev, num_kv_heads=Hkv)
     fill(ic, L, a.ctx - 1, Hkv, dev)

@@ -22,6 +22,7 @@ def main():
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
+    bc.apply_debug_env()
     r = bc.measure(4, 0, a.world, dev, layers=2, streams=0, batched=1, steps=a.steps, warmup=a.warmup)
     print(json.dumps({k: r[k] for k in ("us_per_layer", "eager_us_per_layer", "graph_us_per_layer", "parallelism") if k in r}))
 
