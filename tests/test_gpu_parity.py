@@ -176,14 +176,16 @@ def run_topk(scores, payload, k):
 @pytest.mark.parametrize("n,k", [(13, 2), (24, 24), (77, 19), (311, 69), (1024, 1024), (1025, 7), (1110, 251), (2047, 127), (2047, 1), (2048, 2048), (3001, 640), (4096, 1), (4097, 333),
                                  (8191, 255), (8192, 4095), (8193, 511), (12000, 300), (16384, 1023), (16385, 64), (65535, 511)])
 @pytest.mark.parametrize("dist", ["normal", "narrow", "ties", "const"])
-@pytest.mark.parametrize("radix", [0, 1])
-def test_topk_exact(n, k, dist, radix):
+@pytest.mark.parametrize("radix", [0, 1, 2])
+def test_topk_exact(n, k, dist, radix):  # radix = 2: no cluster variants (rows beyond 4096: the single-CTA register radix kernels)
     """quest_topk on rows of up to 16384 scores selects in one pass over bin totals the CTA counts itself (topk_hist_kernel<G, true>;
     beyond 4096 one row over a cluster of 4 / 8 CTAs); radix = 1 (DBG_TOPK_NO_HIST) keeps the register radix and radix-cluster
     kernels under test for those lengths; longer rows always use them."""
     if radix and n > 16384:
         pytest.skip("same kernels as radix = 0")
-    with K.debug_option(K.DBG_TOPK_NO_HIST, radix):
+    if radix == 2 and not 4096 < n <= 16384:
+        pytest.skip("one CTA per row anyway")
+    with K.debug_option(K.DBG_TOPK_NO_HIST, int(radix == 1)), K.debug_option(K.DBG_TOPK_NO_CLUSTER, int(radix == 2)):
         _topk_exact(n, k, dist)
 
 
