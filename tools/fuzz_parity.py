@@ -2,7 +2,9 @@
 """Randomised differential runs of the GPU parity tests' own bodies (tests/test_gpu_parity.py, tests/test_prefill_fused_gpu.py,
 tests/test_fp8_metadata.py) over shapes the parametrised lists do not name: the layer step (with and without the page-id
 hand-over, with and without bin totals) against the four operator calls, the fused prefill producer against the three-call
-sequence, the fp8 layer step against its oracle.  python tools/fuzz_parity.py [--n 150] [--seed 0]"""
+sequence, the fp8 layer step against its oracle.  --topk N adds N random rows of 2 ... 16384 scores through the two top-k test bodies (quest_topk on self-counted bin
+totals, the layer step's selection from published totals) under every dispatch setting (cluster / single CTA / register radix).
+python tools/fuzz_parity.py [--n 150] [--topk 0] [--seed 0]"""
 import argparse
 import os
 import random
@@ -17,6 +19,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--n", type=int, default=150)
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--topk", type=int, default=0)
     a = ap.parse_args()
     import tests.test_fp8_metadata as t8
     import tests.test_gpu_parity as tp
@@ -52,7 +55,25 @@ def main():
             fails += 1
             print(f"FAIL #{i} {kind} Hq={Hq} Hkv={Hkv} D={D} P={P} kv_len={kv_len} budget={budget}: {type(e).__name__}: {str(e)[:200]}")
             traceback.print_exc(limit=3)
-    print(f"fuzz: {a.n} cases, {fails} failures")
+    import quest_b200._kernels as K
+    for i in range(a.topk):
+        n = rnd.choice([rnd.randint(2, 4096), rnd.randint(4097, 8192), rnd.randint(8193, 16384), rnd.choice([4097, 8191, 8192, 8193, 16383, 16384])])
+        k = rnd.choice([1, n, rnd.randint(1, n), rnd.randint(1, min(n, 1024))])
+        dist = rnd.choice(["normal", "normal", "narrow", "ties", "const"])
+        try:
+            for no_hist, no_cluster in ((0, 0), (0, 1), (1, 0)):
+                with K.debug_option(K.DBG_TOPK_NO_HIST, no_hist), K.debug_option(K.DBG_TOPK_NO_CLUSTER, no_cluster):
+                    tp._topk_exact(n, k, dist)
+            for no_cluster in (0, 1):
+                with K.debug_option(K.DBG_TOPK_NO_CLUSTER, no_cluster):
+                    tp._topk_from_bin_totals_exact(n, k, dist)
+        except BaseException as e:
+            if type(e).__name__ == "Skipped":
+                continue
+            fails += 1
+            print(f"FAIL topk #{i} n={n} k={k} dist={dist}: {type(e).__name__}: {str(e)[:200]}")
+            traceback.print_exc(limit=3)
+    print(f"fuzz: {a.n} + {a.topk} top-k cases, {fails} failures")
     sys.exit(1 if fails else 0)
 
 
