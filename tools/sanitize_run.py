@@ -9,7 +9,10 @@ Shapes are the smallest ones of the test lists that still reach each kernel vari
 top-k dispatches incl. the cluster kernels, hand-over and waiting layer step, split-KV decode, batched step, fp8 metadata, fused
 producer, prefill kernels, sequence-sharded step, static-scratch decode).  The bodies assert parity as in the suite, so a run also
 says whether the sanitizer's serialised execution changed a result.  Prints one line per case and a summary; exit code 1 on any
-failed case (the sanitizer's own findings come through its exit code / log)."""
+failed case (the sanitizer's own findings come through its exit code / log).
+
+Status: compute-sanitizer is closed on the GPU pool this repository was developed on (the wrapper there refuses to start), so no
+sanitizer run is on record under profiles/; without it the script is a 60-case smoke run of every kernel path in under a minute."""
 import argparse
 import os
 import sys
