@@ -11,6 +11,8 @@
 // kernel parks the top-k CTAs on SM slots the scan needs (21.7 -> 26.9); from the top-k kernel it changes nothing;
 // from the decode kernel it lets the next launch on the stream -- the next layer's estimate, whose first ring of
 // metadata loads does not depend on anything earlier -- start under the decode's merge tail (21.7 -> 20.0).
+// Round 2, with the page-id hand-over (the top-k kernel then releases the decode launch only from behind its wait, topk.cu):
+// QUEST_TRIG_EST=1 parks the 32 top-k CTAs as the first estimate CTAs retire, 18.37 -> 18.56 us (profiles/r02_b_experiments.md, 16).
 #ifndef QUEST_TRIG_EST
 #define QUEST_TRIG_EST 0
 #endif

@@ -266,10 +266,14 @@ topk_hist_kernel(const uint16_t* __restrict__ scores, uint32_t* __restrict__ his
   uint32_t in_stride = in_stride_, len = len_, k = k_;
   // hand-over mode: the decode launch may start now; its CTAs poll for the ids this kernel deposits (common.cuh, Handoff)
   // (releasing it later, once the threshold bin is known, measured the same: 18.15 against 18.13 us per layer step)
-  if (QUEST_TRIG_TOPK || ho.epoch != nullptr) pdl_trigger();
+  // With QUEST_TRIG_EST the estimate launch releases this kernel before it has completed: the decode CTAs of the hand-over, which
+  // wait for nothing, may then only be released from behind the wait below.
+  constexpr bool kReleaseLate = QUEST_TRIG_EST != 0;
+  if (!kReleaseLate && (QUEST_TRIG_TOPK || ho.epoch != nullptr)) pdl_trigger();
   if (t < 32) s_sub[t] = 0;
   TH_STAMP(0);
   pdl_wait();  // scores and bin totals come from the estimate kernel
+  if (kReleaseLate && (QUEST_TRIG_TOPK || ho.epoch != nullptr)) pdl_trigger();
   TH_STAMP(1);
   const unsigned long long tag = ho.epoch != nullptr ? (unsigned long long)handoff_tag(ld_ordered32(ho.epoch)) << 32 : 0ull;
   if (ba.descs != nullptr) {  // descriptor mode, as in topk_fast_kernel
